@@ -1,0 +1,111 @@
+/*
+ * stm_b200.h — C ABI of libstm_b200.so: the B200-native tree-expansion hot path of SoftTreeMax.
+ *
+ * Boundary rules:
+ *   - plain pointers and sizes only; no torch / C++ types cross this boundary;
+ *   - unless a function says "host", every data pointer is a DEVICE pointer owned by the caller
+ *     (PyTorch allocates, exactly as the reference passes `tensor.data_ptr()` integers into
+ *     torchcule, policies/cule_bfs.py:154-167); the ctx owns only its cartridge image, decode
+ *     table, intermediate-level pools and native-frame scratch;
+ *   - `stream` is a cudaStream_t passed as void*; all work is enqueued on it, no internal
+ *     streams, no host synchronisation unless stated;
+ *   - every entry point returns 0 (STM_OK) or a negative stm_status and never throws;
+ *     the message is available from stm_last_error();
+ *   - one ctx per device, not re-entrant;
+ *   - there is NO CPU fallback: without a CUDA device every compute entry point fails with
+ *     STM_ERR_CUDA.
+ */
+#ifndef STM_B200_H
+#define STM_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+#include "stm_state.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct stm_ctx stm_ctx;
+
+enum stm_status { STM_OK = 0, STM_ERR_ARG = -1, STM_ERR_CUDA = -2, STM_ERR_NOMEM = -3 };
+
+/* Replaces torchcule.atari.Rom(env_name) + Env(num_envs, device, action_set, ...) construction:
+ * policies/cule_bfs.py:29-39,55-62.  `rom` is a HOST pointer to desc->rom_size bytes. */
+int stm_ctx_create(stm_ctx **out, const stm_game_desc *desc, const uint8_t *rom, int device);
+int stm_ctx_destroy(stm_ctx *ctx);
+/* last error of `ctx`, or of the last failed stm_ctx_create when ctx == NULL */
+const char *stm_last_error(const stm_ctx *ctx);
+/* size of one env state blob (include/stm_state.h): S in the roofline arithmetic */
+size_t stm_state_bytes(const stm_ctx *ctx);
+/* size of the minimal action set: torchcule Rom.minimal_actions(), cule_bfs.py:29-31 */
+int stm_num_actions(const stm_ctx *ctx);
+
+/* Power-on state written to `states[0..n)`: replaces `super(AtariEnv, env).reset(0)`,
+ * cule_bfs.py:57.  rewards/done/lives may be NULL. */
+int stm_reset_states(stm_ctx *ctx, uint8_t *states, float *rewards, uint8_t *done, int32_t *lives,
+                     int n, void *stream);
+
+/* K1 — clone every env `fanout` times: child i <- parent i / fanout.
+ * Replaces `depth_env.expand(num_envs)` (cule_bfs.py:143) and `new_expand` (:81-96).
+ * src/dst must not overlap.  rewards/done/lives pairs may be NULL together. */
+int stm_expand(stm_ctx *ctx, const uint8_t *src_states, const float *src_rewards,
+               const uint8_t *src_done, const int32_t *src_lives, uint8_t *dst_states,
+               float *dst_rewards, uint8_t *dst_done, int32_t *dst_lives, int n_src, int fanout,
+               void *stream);
+
+/* K2 — one agent step for n envs = `frameskip` emulated frames, with the per-frame
+ * reward/done/lives update fused in.  Replaces the loop cule_bfs.py:152-158
+ * (`super(AtariEnv, env).step(...)` + `get_data(episodic_life, gamma**depth, done, rewards, lives)`).
+ *   actions  : n policy-action indices (0..A-1), or NULL for "env i takes action i % A"
+ *              (cule_bfs.py:144);
+ *   weight   : gamma ** depth, rewards[i] += weight * r_frame;
+ *   render   : non-zero -> the last two frames are kept as native 160x210 frames in the ctx
+ *              scratch for stm_frames (cule_bfs.py:162-167 `generate_frames` at skip index
+ *              frameskip-2 and frameskip-1).
+ * An env whose done flag is set on entry is frozen.  n must not exceed stm_max_step_envs(). */
+int stm_step(stm_ctx *ctx, uint8_t *states, const uint8_t *actions, int n, int frameskip,
+             int episodic_life, float weight, float *rewards, uint8_t *done, int32_t *lives,
+             int render, void *stream);
+/* how many envs one stm_step(render=1) + stm_frames pair can hold in the native-frame scratch;
+ * stm_set_scratch_envs changes it (reallocates; not for use inside a timed loop). */
+int stm_max_step_envs(const stm_ctx *ctx);
+int stm_set_scratch_envs(stm_ctx *ctx, int n_envs);
+
+/* K3 — observation kernel: grey + 84x84 bilinear resize of the two native frames left by the last
+ * stm_step(render=1), per-pixel max, and frame stacking:
+ *   child_stacks[i] = concat(parent_stacks[i / fanout][1:4], new_frame_i)       (u8, 4x84x84)
+ * Replaces generate_frames' grey/rescale stage + cule_bfs.py:168-172
+ * (`th.max`, `replicate_state`, `th.cat`).  fanout = 1 with parent == the env's own stack gives the
+ * plain frame-stack update of a root env (environments/cule_env.py:83,93). */
+int stm_frames(stm_ctx *ctx, const uint8_t *parent_stacks, uint8_t *child_stacks, int n, int fanout,
+               void *stream);
+
+/* Whole breadth-first expansion of n_roots roots to `depth` levels: cule_bfs.py:98-209, batched
+ * over roots (reference: one root per call).
+ *   root_states  n_roots x 256                 (cule_bfs.py:110-112)
+ *   root_stacks  n_roots x 4 x 84 x 84 u8      (cule_bfs.py:99)
+ *   leaf_stacks  n_roots x A^depth x 4 x 84 x 84 u8
+ *   leaf_rewards n_roots x A^depth f32, sign() applied when clip_reward (cule_bfs.py:204-206)
+ *   leaf_done    n_roots x A^depth u8 ; leaf_lives i32 ; leaf_states x256 — each may be NULL.
+ * Leaf j of root r sits at r*A^depth + j; its first action is j / A^(depth-1). */
+int stm_bfs(stm_ctx *ctx, const uint8_t *root_states, const uint8_t *root_stacks, int n_roots,
+            int depth, float gamma, int frameskip, int episodic_life, int clip_reward,
+            uint8_t *leaf_stacks, float *leaf_rewards, uint8_t *leaf_done, int32_t *leaf_lives,
+            uint8_t *leaf_states, void *stream);
+
+/* Same, with HOST buffers (pinned or pageable): copies roots host->device, runs stm_bfs, copies
+ * the leaves device->host and synchronises `stream` before returning.  This is the call a
+ * non-CUDA host program (the reference's Python loop, a cgo/JNI binding) makes. */
+int stm_bfs_host(stm_ctx *ctx, const uint8_t *root_states, const uint8_t *root_stacks, int n_roots,
+                 int depth, float gamma, int frameskip, int episodic_life, int clip_reward,
+                 uint8_t *leaf_stacks, float *leaf_rewards, uint8_t *leaf_done, int32_t *leaf_lives,
+                 void *stream);
+
+/* number of kernels this ctx has launched since creation (bench.py's gpu_launches) */
+long long stm_launch_count(const stm_ctx *ctx);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* STM_B200_H */

@@ -49,6 +49,8 @@ def lib():
         L.orc_frame.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
         L.orc_lives.argtypes = [C.c_void_p, C.c_void_p]
         L.orc_lives.restype = C.c_int
+        L.orc_terminal.argtypes = [C.c_void_p, C.c_void_p]
+        L.orc_terminal.restype = C.c_int
         L.orc_get_data.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_float, C.c_void_p, C.c_void_p, C.c_void_p]
         L.orc_render_obs.argtypes = [C.c_void_p, C.c_void_p]
         L.orc_agent_step.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_float,
@@ -112,6 +114,9 @@ class Game:
         s = np.zeros(STATE_BYTES, np.uint8)
         lib().orc_env_reset(self.h, _p(s))
         return s
+
+    def terminal(self, s):
+        return bool(lib().orc_terminal(self.h, _p(s)))
 
     def exec_one(self, s):
         lib().orc_exec_one(self.h, _p(s))
@@ -177,6 +182,9 @@ def make_roots(game, R, seed=1234, base_steps=64, spread=192):
             obs, *_ = game.agent_step(s, acts[t], done=done, reward=rew, lives=lives)
             frames = frames[1:] + [obs.copy()]
             t += 1
+            if game.terminal(s):     # game over: start a new episode, as the reference's env.reset() would
+                s = game.reset()
+                frames = [np.zeros((84, 84), np.uint8)] * 4
         snaps[n] = (s.copy(), np.stack(frames))
     roots = np.stack([snaps[base_steps + (i % spread)][0] for i in range(R)])
     stacks = np.stack([snaps[base_steps + (i % spread)][1] for i in range(R)])

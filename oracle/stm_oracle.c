@@ -795,6 +795,13 @@ int orc_lives(const orc_game *g, const uint8_t *blob)
     return (e->ram[g->d.lives_addr & 0x7F] >> g->d.lives_shift) & g->d.lives_mask;
 }
 
+int orc_terminal(const orc_game *g, const uint8_t *blob)
+{
+    const env_t *e = (const env_t *)blob;
+    if (g->d.term_addr == 0xFF) return 0;
+    return (e->ram[g->d.term_addr & 0x7F] & g->d.term_mask) == g->d.term_value;
+}
+
 /* restates torchcule get_data(episodic_life, weight, done, rewards, lives) as used at
    cule_bfs.py:157-158: rewards += weight*r_frame; done |= terminal | life lost; lives updated */
 void orc_get_data(const orc_game *g, uint8_t *blob, int episodic_life, float weight,

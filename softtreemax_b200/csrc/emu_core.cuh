@@ -1,0 +1,822 @@
+// emu_core.cuh — Atari 2600 (6507 + RIOT + TIA) core used by the batched step kernel (K2).
+//
+// One instance of Emu<M> is one environment, owned by one GPU thread.  The env state blob
+// (include/stm_state.h) lives in shared memory, word-interleaved across the block so that every
+// lane owns one bank; `M` is the memory policy that hides that layout.  The same source compiles
+// with a plain-array policy on the host, which is how tests/ cross-check it against the oracle
+// without a GPU (tests/tools/host_core.cpp) — the host build is a test aid, never a product path.
+//
+// Structure (deliberately unlike the oracle's big switch):
+//   - opcodes are decoded through a 256-entry table into (addressing mode, access kind, base
+//     cycles, operation class); lanes that run different opcodes with the same addressing mode or
+//     the same operation class share code, which bounds SIMT divergence to ~13 + ~60 paths;
+//   - the TIA is evaluated a 32-pixel word at a time from per-object bit masks (collisions are
+//     word ANDs, colours are layered byte selects), not pixel by pixel;
+//   - instruction fetch reads 4 ROM bytes with two aligned word loads and a funnel shift.
+//
+// Timing model: DESIGN.md §3 (identical to oracle/stm_oracle.c, which is the specification).
+// Reference call sites this replaces: policies/cule_bfs.py:154-158 (torchcule step + get_data).
+#pragma once
+#include <stdint.h>
+#include "../../include/stm_state.h"
+
+#ifdef __CUDACC__
+#define STM_DEV __device__ __forceinline__          /* member functions */
+#define STM_FN  __device__ __forceinline__          /* free functions   */
+#else
+#define STM_DEV inline
+#define STM_FN  static inline
+#endif
+
+namespace stm {
+
+// ---- decode table ----------------------------------------------------------------------------
+enum Mode : uint32_t { M_IMP, M_IMM, M_ZP, M_ZPX, M_ZPY, M_ABS, M_ABX, M_ABY, M_INX, M_INY, M_REL, M_IND, M_ACC };
+enum Kind : uint32_t { K_N, K_R, K_W, K_M };
+enum Cls : uint32_t {
+    C_NOP, C_LDA, C_LDX, C_LDY, C_LAX, C_STA, C_STX, C_STY, C_SAX, C_TAX, C_TAY, C_TXA, C_TYA, C_TSX,
+    C_TXS, C_PHA, C_PHP, C_PLA, C_PLP, C_AND, C_ORA, C_EOR, C_ADC, C_SBC, C_CMP, C_CPX, C_CPY, C_BIT,
+    C_ASL, C_LSR, C_ROL, C_ROR, C_INC, C_DEC, C_INX, C_INY, C_DEX, C_DEY, C_CLC, C_SEC, C_CLI, C_SEI,
+    C_CLV, C_CLD, C_SED, C_JMP, C_JSR, C_RTS, C_RTI, C_BRK, C_BRA, C_DCP, C_ISC, C_SLO, C_RLA, C_SRE,
+    C_RRA, C_ANC, C_ALR, C_SBX, C_COUNT
+};
+// entry = mode | kind<<4 | cycles<<6 | cls<<10
+static inline uint32_t pack_op(uint32_t mode, uint32_t kind, uint32_t cyc, uint32_t cls)
+{ return mode | (kind << 4) | (cyc << 6) | (cls << 10); }
+
+// Builds the 256-entry decode table from the regular structure of the 6502 opcode matrix
+// (op = aaabbbcc) plus the irregular column cc=00 and the single-byte instructions.
+static inline void build_decode_table(uint32_t *t)
+{
+    auto cyc_of = [](uint32_t mode, uint32_t kind) -> uint32_t {
+        switch (mode) {
+        case M_IMM: return 2;
+        case M_ZP:  return kind == K_M ? 5 : 3;
+        case M_ZPX: case M_ZPY: return kind == K_M ? 6 : 4;
+        case M_ABS: return kind == K_M ? 6 : 4;
+        case M_ABX: case M_ABY: return kind == K_M ? 7 : (kind == K_W ? 5 : 4);
+        case M_INX: return kind == K_M ? 8 : 6;
+        case M_INY: return kind == K_M ? 8 : (kind == K_W ? 6 : 5);
+        default: return 2;
+        }
+    };
+    auto set = [&](uint32_t op, uint32_t cls, uint32_t mode, uint32_t kind, int cyc = -1) {
+        t[op] = pack_op(mode, kind, cyc < 0 ? cyc_of(mode, kind) : (uint32_t)cyc, cls);
+    };
+    static const uint32_t MODE01[8] = { M_INX, M_ZP, M_IMM, M_ABS, M_INY, M_ZPX, M_ABY, M_ABX };
+    for (uint32_t op = 0; op < 256; op++) set(op, C_NOP, M_IMP, K_N, 2);
+    for (uint32_t aaa = 0; aaa < 8; aaa++) for (uint32_t bbb = 0; bbb < 8; bbb++) {
+        // cc = 01: accumulator ALU group
+        {
+            static const uint32_t CL[8] = { C_ORA, C_AND, C_EOR, C_ADC, C_STA, C_LDA, C_CMP, C_SBC };
+            uint32_t op = (aaa << 5) | (bbb << 2) | 1, cls = CL[aaa], mode = MODE01[bbb];
+            if (cls == C_STA && mode == M_IMM) set(op, C_NOP, M_IMM, K_R);
+            else set(op, cls, mode, cls == C_STA ? K_W : K_R);
+        }
+        // cc = 11: undocumented combinations of the two groups
+        {
+            static const uint32_t CL[8] = { C_SLO, C_RLA, C_SRE, C_RRA, C_SAX, C_LAX, C_DCP, C_ISC };
+            uint32_t op = (aaa << 5) | (bbb << 2) | 3, cls = CL[aaa], mode = MODE01[bbb];
+            if (mode == M_IMM) {
+                static const uint32_t IMMCL[8] = { C_ANC, C_ANC, C_ALR, C_NOP, C_NOP, C_NOP, C_SBX, C_SBC };
+                set(op, IMMCL[aaa], M_IMM, K_R);
+            } else if (cls == C_SAX) {
+                if (mode == M_ZPX) mode = M_ZPY;
+                if (mode == M_ABX) mode = M_ABY;
+                bool real = (bbb == 0 || bbb == 1 || bbb == 3 || bbb == 5);
+                set(op, real ? C_SAX : C_NOP, mode, K_W);       // 0x93/0x9B/0x9F: unstable -> no effect
+            } else if (cls == C_LAX) {
+                if (mode == M_ZPX) mode = M_ZPY;
+                if (mode == M_ABX) mode = M_ABY;
+                set(op, bbb == 6 ? C_NOP : C_LAX, mode, K_R);   // 0xBB LAS -> read only
+            } else set(op, cls, mode, K_M);
+        }
+        // cc = 10: read-modify-write group and the X register loads/stores
+        {
+            static const uint32_t CL[8] = { C_ASL, C_ROL, C_LSR, C_ROR, C_STX, C_LDX, C_DEC, C_INC };
+            uint32_t op = (aaa << 5) | (bbb << 2) | 2, cls = CL[aaa];
+            bool xreg = (cls == C_STX || cls == C_LDX);
+            switch (bbb) {
+            case 0: if (cls == C_LDX) set(op, C_LDX, M_IMM, K_R); else if (aaa >= 4) set(op, C_NOP, M_IMM, K_R); break;
+            case 1: set(op, cls, M_ZP, cls == C_STX ? K_W : (cls == C_LDX ? K_R : K_M)); break;
+            case 2: if (aaa < 4) set(op, cls, M_ACC, K_N, 2); break;
+            case 3: set(op, cls, M_ABS, cls == C_STX ? K_W : (cls == C_LDX ? K_R : K_M)); break;
+            case 5: set(op, cls, xreg ? M_ZPY : M_ZPX, cls == C_STX ? K_W : (cls == C_LDX ? K_R : K_M)); break;
+            case 7:
+                if (cls == C_STX) set(op, C_NOP, M_ABY, K_W);    // 0x9E SHX: no effect
+                else set(op, cls, xreg ? M_ABY : M_ABX, cls == C_LDX ? K_R : K_M);
+                break;
+            default: break;                                       // bbb 4: JAM, bbb 6: NOP/TXS/TSX below
+            }
+        }
+    }
+    // column cc = 00
+    static const uint32_t ZPNOP[] = { 0x04, 0x44, 0x64 }, ZPXNOP[] = { 0x14, 0x34, 0x54, 0x74, 0xD4, 0xF4 },
+                          ABXNOP[] = { 0x1C, 0x3C, 0x5C, 0x7C, 0xDC, 0xFC };
+    for (uint32_t o : ZPNOP) set(o, C_NOP, M_ZP, K_R);
+    for (uint32_t o : ZPXNOP) set(o, C_NOP, M_ZPX, K_R);
+    for (uint32_t o : ABXNOP) set(o, C_NOP, M_ABX, K_R);
+    set(0x0C, C_NOP, M_ABS, K_R); set(0x80, C_NOP, M_IMM, K_R);
+    set(0x9C, C_NOP, M_ABX, K_W);                                 // SHY: no effect
+    set(0x24, C_BIT, M_ZP, K_R);  set(0x2C, C_BIT, M_ABS, K_R);
+    set(0x84, C_STY, M_ZP, K_W);  set(0x8C, C_STY, M_ABS, K_W); set(0x94, C_STY, M_ZPX, K_W);
+    set(0xA0, C_LDY, M_IMM, K_R); set(0xA4, C_LDY, M_ZP, K_R);  set(0xAC, C_LDY, M_ABS, K_R);
+    set(0xB4, C_LDY, M_ZPX, K_R); set(0xBC, C_LDY, M_ABX, K_R);
+    set(0xC0, C_CPY, M_IMM, K_R); set(0xC4, C_CPY, M_ZP, K_R);  set(0xCC, C_CPY, M_ABS, K_R);
+    set(0xE0, C_CPX, M_IMM, K_R); set(0xE4, C_CPX, M_ZP, K_R);  set(0xEC, C_CPX, M_ABS, K_R);
+    set(0x4C, C_JMP, M_ABS, K_N, 3); set(0x6C, C_JMP, M_IND, K_N, 5);
+    set(0x20, C_JSR, M_ABS, K_N, 6); set(0x60, C_RTS, M_IMP, K_N, 6);
+    set(0x40, C_RTI, M_IMP, K_N, 6); set(0x00, C_BRK, M_IMP, K_N, 7);
+    for (uint32_t i = 0; i < 8; i++) set(0x10 | (i << 5), C_BRA, M_REL, K_N, 2);
+    set(0x08, C_PHP, M_IMP, K_N, 3); set(0x28, C_PLP, M_IMP, K_N, 4);
+    set(0x48, C_PHA, M_IMP, K_N, 3); set(0x68, C_PLA, M_IMP, K_N, 4);
+    set(0x88, C_DEY, M_IMP, K_N); set(0xA8, C_TAY, M_IMP, K_N); set(0xC8, C_INY, M_IMP, K_N); set(0xE8, C_INX, M_IMP, K_N);
+    set(0x18, C_CLC, M_IMP, K_N); set(0x38, C_SEC, M_IMP, K_N); set(0x58, C_CLI, M_IMP, K_N); set(0x78, C_SEI, M_IMP, K_N);
+    set(0x98, C_TYA, M_IMP, K_N); set(0xB8, C_CLV, M_IMP, K_N); set(0xD8, C_CLD, M_IMP, K_N); set(0xF8, C_SED, M_IMP, K_N);
+    set(0x8A, C_TXA, M_IMP, K_N); set(0x9A, C_TXS, M_IMP, K_N); set(0xAA, C_TAX, M_IMP, K_N); set(0xBA, C_TSX, M_IMP, K_N);
+    set(0xCA, C_DEX, M_IMP, K_N); set(0xEA, C_NOP, M_IMP, K_N);
+}
+
+// ---- game constants handed to the kernel ---------------------------------------------------------
+struct GameParams {
+    uint32_t rom_mask;        // byte mask inside one bank window (0x7FF / 0xFFF)
+    uint32_t bank_scheme, controller, n_actions;
+    uint8_t  actions[20];
+    uint8_t  score_addr[4], score2_addr[4];
+    uint8_t  lives_addr, lives_shift, lives_mask, term_addr, term_mask, term_value, pad0, pad1;
+};
+
+enum : uint32_t { FC = 1, FZ = 2, FI = 4, FD = 8, FB = 16, FU = 32, FV = 64, FN = 128 };
+
+// byte offsets of blob fields (checked against the struct in stm_kernels.cu)
+enum : uint32_t {
+    O_PC = 128, O_A = 130, O_X = 131, O_Y = 132, O_SP = 133, O_P = 134, O_BANK = 135, O_LINE = 136,
+    O_HCYC = 138, O_RX = 139, O_FRAME = 140, O_TIMER = 144, O_TSHIFT = 148, O_TFLAG = 149,
+    O_SWCHA_OUT = 150, O_SWACNT = 151, O_SWCHB_OUT = 152, O_SWBCNT = 153, O_ACTION = 154, O_FLAGS = 155,
+    O_CX = 156, O_CHARGE = 158, O_INPT_LATCH = 159, O_PADDLE = 160, O_POS = 162,
+    O_VSYNC = 168, O_VBLANK = 169, O_NUSIZ0 = 170, O_NUSIZ1 = 171, O_COLUP0 = 172, O_COLUP1 = 173,
+    O_COLUPF = 174, O_COLUBK = 175, O_CTRLPF = 176, O_REFP0 = 177, O_REFP1 = 178, O_PF0 = 179,
+    O_PF1 = 180, O_PF2 = 181, O_GRP0 = 182, O_GRP1 = 183, O_GRP0_OLD = 184, O_GRP1_OLD = 185,
+    O_ENAM0 = 186, O_ENAM1 = 187, O_ENABL = 188, O_ENABL_OLD = 189, O_HMP0 = 190, O_HMP1 = 191,
+    O_HMM0 = 192, O_HMM1 = 193, O_HMBL = 194, O_VDELP0 = 195, O_VDELP1 = 196, O_VDELBL = 197,
+    O_RESMP0 = 198, O_RESMP1 = 199, O_SCORE_PREV = 200
+};
+
+STM_FN uint32_t brev8(uint32_t v)
+{
+#ifdef __CUDA_ARCH__
+    return __brev(v) >> 24;
+#else
+    v = ((v & 0xF0) >> 4) | ((v & 0x0F) << 4);
+    v = ((v & 0xCC) >> 2) | ((v & 0x33) << 2);
+    v = ((v & 0xAA) >> 1) | ((v & 0x55) << 1);
+    return v;
+#endif
+}
+STM_FN uint32_t brev32(uint32_t v)
+{
+#ifdef __CUDA_ARCH__
+    return __brev(v);
+#else
+    v = ((v >> 1) & 0x55555555u) | ((v & 0x55555555u) << 1);
+    v = ((v >> 2) & 0x33333333u) | ((v & 0x33333333u) << 2);
+    v = ((v >> 4) & 0x0F0F0F0Fu) | ((v & 0x0F0F0F0Fu) << 4);
+    v = ((v >> 8) & 0x00FF00FFu) | ((v & 0x00FF00FFu) << 8);
+    return (v >> 16) | (v << 16);
+#endif
+}
+STM_FN uint32_t funnel_r(uint32_t lo, uint32_t hi, uint32_t sh)   // sh in {0,8,16,24}
+{
+#ifdef __CUDA_ARCH__
+    return __funnelshift_r(lo, hi, sh);
+#else
+    return sh ? (lo >> sh) | (hi << (32 - sh)) : lo;
+#endif
+}
+// each of the low 8 bits replicated 4x: bit i -> bits 4i..4i+3
+STM_FN uint32_t spread8x4(uint32_t b)
+{
+    b = (b | (b << 12)) & 0x000F000Fu;
+    b = (b | (b << 6))  & 0x03030303u;
+    b = (b | (b << 3))  & 0x11111111u;
+    return b * 0xFu;
+}
+// low 4 bits -> 4 byte masks 0x00 / 0xFF
+STM_FN uint32_t nib_to_bytes(uint32_t n)
+{
+    return (((n & 0xF) * 0x00204081u) & 0x01010101u) * 0xFFu;
+}
+STM_FN uint32_t sel_bytes(uint32_t under, uint32_t over, uint32_t m) { return (under & ~m) | (over & m); }
+
+// ---- the per-env machine ---------------------------------------------------------------------------
+// M must provide:
+//   uint32_t ld8(off) / void st8(off, v) / ld16 / st16 / ld32 / st32     blob access (off = byte offset)
+//   uint32_t rom8(idx), rom32(word_idx)                                    cartridge image
+//   uint32_t opinfo(op)                                                    decode table
+//   void px4(row, g, word)   store 4 pixels (colour indices) of native row `row`, group g (0..39)
+//   void px1(row, x, v)      store 1 pixel
+template <class M>
+struct Emu {
+    M &m;
+    const GameParams &gp;
+    // hot state in registers
+    uint32_t pc, a, x, y, sp, p, bank;
+    uint32_t hcyc, line, rx, flags;
+    int32_t  timer;
+    uint32_t tflag;
+    bool     render;        // pixels of this frame are wanted
+    uint32_t end_line_no;
+    bool     wsync;
+
+    STM_DEV Emu(M &mm, const GameParams &g) : m(mm), gp(g) {}
+
+    STM_DEV void load()
+    {
+        pc = m.ld16(O_PC); a = m.ld8(O_A); x = m.ld8(O_X); y = m.ld8(O_Y); sp = m.ld8(O_SP); p = m.ld8(O_P);
+        bank = m.ld8(O_BANK); line = m.ld16(O_LINE); hcyc = m.ld8(O_HCYC); rx = m.ld8(O_RX);
+        flags = m.ld8(O_FLAGS); timer = (int32_t)m.ld32(O_TIMER); tflag = m.ld8(O_TFLAG);
+        render = false; end_line_no = 0; wsync = false;
+    }
+    STM_DEV void store()
+    {
+        m.st16(O_PC, pc); m.st8(O_A, a); m.st8(O_X, x); m.st8(O_Y, y); m.st8(O_SP, sp); m.st8(O_P, p);
+        m.st8(O_BANK, bank); m.st16(O_LINE, line); m.st8(O_HCYC, hcyc); m.st8(O_RX, rx);
+        m.st8(O_FLAGS, flags); m.st32(O_TIMER, (uint32_t)timer); m.st8(O_TFLAG, tflag);
+    }
+
+    // ---------------- input ----------------
+    STM_DEV bool fire_pressed() { uint32_t act = m.ld8(O_ACTION); return act == 1 || act >= 10; }
+    STM_DEV uint32_t dir_bits()    // bit0 up, bit1 down, bit2 left, bit3 right
+    {
+        uint32_t act = m.ld8(O_ACTION);
+        uint32_t b = act >= 10 ? act - 8 : act;           // FIRE variants repeat codes 2..9
+        if (act < 2 || act > 17) return 0;
+        switch (b) {
+        case 2: return 1; case 3: return 8; case 4: return 4; case 5: return 2;
+        case 6: return 9; case 7: return 5; case 8: return 10; default: return 6;
+        }
+    }
+    STM_DEV void update_latch()
+    {
+        if (!(m.ld8(O_VBLANK) & 0x40)) { m.st8(O_INPT_LATCH, 0); return; }
+        if (gp.controller == STM_CTRL_JOYSTICK && fire_pressed()) m.st8(O_INPT_LATCH, m.ld8(O_INPT_LATCH) | 1);
+    }
+    STM_DEV void set_action(uint32_t ale)
+    {
+        m.st8(O_ACTION, ale);
+        if (gp.controller == STM_CTRL_PADDLE) {
+            uint32_t d = dir_bits();
+            int pp = (int)m.ld8(O_PADDLE);
+            if (d & 8) pp -= STM_PADDLE_DELTA;
+            if (d & 4) pp += STM_PADDLE_DELTA;
+            pp = pp < STM_PADDLE_MIN ? STM_PADDLE_MIN : (pp > STM_PADDLE_MAX ? STM_PADDLE_MAX : pp);
+            m.st8(O_PADDLE, (uint32_t)pp);
+        }
+        update_latch();
+    }
+
+    // ---------------- TIA rendering: 32-pixel words from object masks ----------------
+    // bits of `pat` (width <= 32, bit 0 = leftmost pixel) placed at ring position `start` (0..159),
+    // returned as seen by word w (pixels 32w..32w+31); the 160-pixel line is a ring.
+    STM_DEV uint32_t place(uint32_t pat, int start, int w)
+    {
+        int r = start - 32 * w;
+        uint32_t out = 0;
+        if (r > -32 && r < 32) out = r >= 0 ? pat << r : pat >> (-r);
+        r -= 160;
+        if (r > -32 && r < 32) out |= r >= 0 ? pat << r : pat >> (-r);
+        return out;
+    }
+    STM_DEV uint32_t copies(uint32_t pat, uint32_t pos, uint32_t nusiz, int w)
+    {
+        uint32_t mode = nusiz & 7;
+        uint32_t out = place(pat, (int)pos, w);
+        // second / third copy offsets: 1:{16} 2:{32} 3:{16,32} 4:{64} 6:{32,64}
+        uint32_t o1 = (mode == 1 || mode == 3) ? 16u : ((mode == 2 || mode == 6) ? 32u : (mode == 4 ? 64u : 0u));
+        uint32_t o2 = mode == 3 ? 32u : (mode == 6 ? 64u : 0u);
+        if (o1) { uint32_t s = pos + o1; if (s >= 160) s -= 160; out |= place(pat, (int)s, w); }
+        if (o2) { uint32_t s = pos + o2; if (s >= 160) s -= 160; out |= place(pat, (int)s, w); }
+        return out;
+    }
+    STM_DEV uint32_t player_pat(uint32_t grp, uint32_t nusiz, uint32_t refp)
+    {
+        uint32_t mode = nusiz & 7;
+        uint32_t g = (refp & 8) ? grp : brev8(grp);          // bit 0 = leftmost pixel
+        if (mode == 5) {                                      // double width: each bit -> 2
+            g = (g | (g << 4)) & 0x0F0Fu; g = (g | (g << 2)) & 0x3333u; g = (g | (g << 1)) & 0x5555u;
+            return g * 3u;
+        }
+        if (mode == 7) return spread8x4(g);                   // quad width
+        return g;
+    }
+
+    STM_DEV void catchup(uint32_t xe)
+    {
+        if (xe > STM_VIS_W) xe = STM_VIS_W;
+        if (xe <= rx) return;
+        int row = (int)line - STM_YSTART;
+        bool draw = render && row >= 0 && row < STM_VIS_H;
+        uint32_t vblank = m.ld8(O_VBLANK);
+        bool vb = (vblank & 2) != 0;
+        uint32_t g0 = (m.ld8(O_VDELP0) & 1) ? m.ld8(O_GRP0_OLD) : m.ld8(O_GRP0);
+        uint32_t g1 = (m.ld8(O_VDELP1) & 1) ? m.ld8(O_GRP1_OLD) : m.ld8(O_GRP1);
+        uint32_t enbl = (m.ld8(O_VDELBL) & 1) ? m.ld8(O_ENABL_OLD) : m.ld8(O_ENABL);
+        bool m0on = (m.ld8(O_ENAM0) & 2) && !(m.ld8(O_RESMP0) & 2);
+        bool m1on = (m.ld8(O_ENAM1) & 2) && !(m.ld8(O_RESMP1) & 2);
+        bool blon = (enbl & 2) != 0;
+        bool movable = g0 || g1 || m0on || m1on || blon;
+        if (!draw && (vb || !movable)) { rx = xe; return; }
+
+        uint32_t ctrlpf = m.ld8(O_CTRLPF);
+        uint32_t nusiz0 = m.ld8(O_NUSIZ0), nusiz1 = m.ld8(O_NUSIZ1);
+        // playfield as 40 four-pixel columns: low word = columns 0..31, high = 32..39
+        uint32_t pf20 = (m.ld8(O_PF0) >> 4) | (brev8(m.ld8(O_PF1)) << 4) | (m.ld8(O_PF2) << 12);
+        uint32_t pfr = (ctrlpf & 1) ? (brev32(pf20) >> 12) : pf20;
+        uint32_t pf_lo = pf20 | (pfr << 20), pf_hi = pfr >> 12;
+        uint32_t pat0 = g0 ? player_pat(g0, nusiz0, m.ld8(O_REFP0)) : 0;
+        uint32_t pat1 = g1 ? player_pat(g1, nusiz1, m.ld8(O_REFP1)) : 0;
+        uint32_t mp0 = (1u << (1u << ((nusiz0 >> 4) & 3))) - 1u;
+        uint32_t mp1 = (1u << (1u << ((nusiz1 >> 4) & 3))) - 1u;
+        uint32_t bp  = (1u << (1u << ((ctrlpf >> 4) & 3))) - 1u;
+        uint32_t pos_p0 = m.ld8(O_POS + 0), pos_p1 = m.ld8(O_POS + 1), pos_m0 = m.ld8(O_POS + 2),
+                 pos_m1 = m.ld8(O_POS + 3), pos_bl = m.ld8(O_POS + 4);
+        uint32_t cx = 0;
+        uint32_t c_p0 = 0, c_p1 = 0, c_pf = 0, c_bk = 0;
+        bool comb = (flags & STM_F_HMOVE_BLANK) != 0;
+        if (draw) {
+            c_p0 = (m.ld8(O_COLUP0) >> 1) * 0x01010101u; c_p1 = (m.ld8(O_COLUP1) >> 1) * 0x01010101u;
+            c_pf = (m.ld8(O_COLUPF) >> 1) * 0x01010101u; c_bk = (m.ld8(O_COLUBK) >> 1) * 0x01010101u;
+        }
+        int w0 = (int)(rx >> 5), w1 = (int)((xe - 1) >> 5);
+        for (int w = w0; w <= w1; w++) {
+            int lo = (int)rx - 32 * w; if (lo < 0) lo = 0;
+            int hi = (int)xe - 32 * w; if (hi > 32) hi = 32;
+            uint32_t seg = (hi == 32 ? 0xFFFFFFFFu : ((1u << hi) - 1u)) & ~((1u << lo) - 1u);
+            uint32_t pfcols = w < 4 ? (pf_lo >> (8 * w)) & 0xFFu : pf_hi & 0xFFu;
+            uint32_t pfm = spread8x4(pfcols) & seg;
+            uint32_t p0m = pat0 ? copies(pat0, pos_p0, nusiz0, w) & seg : 0;
+            uint32_t p1m = pat1 ? copies(pat1, pos_p1, nusiz1, w) & seg : 0;
+            uint32_t m0m = m0on ? copies(mp0, pos_m0, nusiz0, w) & seg : 0;
+            uint32_t m1m = m1on ? copies(mp1, pos_m1, nusiz1, w) & seg : 0;
+            uint32_t blm = blon ? place(bp, (int)pos_bl, w) & seg : 0;
+            if (!vb && movable) {
+                if (m0m & p0m) cx |= 1u << 0;
+                if (m0m & p1m) cx |= 1u << 1;
+                if (m1m & p1m) cx |= 1u << 2;
+                if (m1m & p0m) cx |= 1u << 3;
+                if (p0m & blm) cx |= 1u << 4;
+                if (p0m & pfm) cx |= 1u << 5;
+                if (p1m & blm) cx |= 1u << 6;
+                if (p1m & pfm) cx |= 1u << 7;
+                if (m0m & blm) cx |= 1u << 8;
+                if (m0m & pfm) cx |= 1u << 9;
+                if (m1m & blm) cx |= 1u << 10;
+                if (m1m & pfm) cx |= 1u << 11;
+                if (blm & pfm) cx |= 1u << 13;
+                if (m0m & m1m) cx |= 1u << 14;
+                if (p0m & p1m) cx |= 1u << 15;
+            }
+            if (draw) {
+                uint32_t l0 = p0m | m0m, l1 = p1m | m1m;
+                bool pfp = (ctrlpf & 4) != 0, score = (ctrlpf & 2) != 0 && !pfp;
+                for (int n = lo >> 2; n <= (hi - 1) >> 2; n++) {
+                    uint32_t sh = 4u * (uint32_t)n;
+                    uint32_t word;
+                    if (vb) word = 0;
+                    else {
+                        uint32_t b0 = nib_to_bytes(l0 >> sh), b1 = nib_to_bytes(l1 >> sh);
+                        uint32_t bb = nib_to_bytes(blm >> sh), bf = nib_to_bytes(pfm >> sh);
+                        uint32_t pfcol = score ? ((32 * w + (int)sh) < 80 ? c_p0 : c_p1) : c_pf;
+                        word = c_bk;
+                        if (pfp) {
+                            word = sel_bytes(word, c_p1, b1); word = sel_bytes(word, c_p0, b0);
+                            word = sel_bytes(word, c_pf, bf | bb);
+                        } else {
+                            word = sel_bytes(word, pfcol, bf); word = sel_bytes(word, c_pf, bb);
+                            word = sel_bytes(word, c_p1, b1);  word = sel_bytes(word, c_p0, b0);
+                        }
+                        if (comb && w == 0 && n < 2) word = 0;
+                    }
+                    uint32_t nm = (seg >> sh) & 0xFu;
+                    uint32_t g = 8u * (uint32_t)w + (uint32_t)n;
+                    if (nm == 0xFu) m.px4((uint32_t)row, g, word);
+                    else {
+                        for (uint32_t k = 0; k < 4; k++)
+                            if (nm & (1u << k)) m.px1((uint32_t)row, 4u * g + k, (word >> (8u * k)) & 0xFFu);
+                    }
+                }
+            }
+        }
+        if (cx) m.st16(O_CX, m.ld16(O_CX) | cx);
+        rx = xe;
+    }
+
+    STM_DEV void end_line()
+    {
+        catchup(STM_VIS_W);
+        line++;
+        rx = 0;
+        flags &= ~(uint32_t)STM_F_HMOVE_BLANK;
+        if (!(m.ld8(O_VBLANK) & 0x80)) { uint32_t c = m.ld8(O_CHARGE); if (c < 255) m.st8(O_CHARGE, c + 1); }
+        if (line >= STM_MAX_LINES) { flags |= STM_F_FRAME_DONE; end_line_no = STM_MAX_LINES; line = 0; }
+    }
+    STM_DEV void advance(uint32_t cyc)
+    {
+        timer -= (int32_t)cyc;
+        if (timer < 0) { tflag |= 0x80; if (timer < -(1 << 30)) timer += (1 << 30); }
+        hcyc += cyc;
+        if (hcyc >= STM_CYC_PER_LINE) { end_line(); hcyc -= STM_CYC_PER_LINE; }
+    }
+    STM_DEV uint32_t cur_x() { int v = (int)hcyc * 3 - STM_HBLANK_CLK; return v < 0 ? 0u : (uint32_t)v; }
+
+    // ---------------- TIA registers ----------------
+    STM_DEV uint32_t tia_read(uint32_t reg)
+    {
+        reg &= 0x0F;
+        if (reg < 8) { catchup(cur_x()); return ((m.ld16(O_CX) >> (2 * reg)) & 3u) << 6; }
+        if (reg < 12) {
+            uint32_t i = reg - 8;
+            if (gp.controller != STM_CTRL_PADDLE || i > 1) return 0;
+            if (m.ld8(O_VBLANK) & 0x80) return 0;
+            return m.ld8(O_CHARGE) >= m.ld8(O_PADDLE + i) ? 0x80u : 0u;
+        }
+        if (reg == 12) {
+            if (gp.controller != STM_CTRL_JOYSTICK) return 0x80;
+            if (fire_pressed()) return 0;
+            if ((m.ld8(O_VBLANK) & 0x40) && (m.ld8(O_INPT_LATCH) & 1)) return 0;
+            return 0x80;
+        }
+        return reg == 13 ? 0x80u : 0u;
+    }
+    STM_DEV void set_pos(uint32_t obj, bool player)
+    {
+        uint32_t clk = hcyc * 3;
+        uint32_t v = clk < STM_HBLANK_CLK ? (player ? 3u : 2u) : (clk - STM_HBLANK_CLK + (player ? 5u : 4u)) % 160u;
+        m.st8(O_POS + obj, v);
+    }
+    STM_DEV void hmove_obj(uint32_t obj, uint32_t hm)
+    {
+        int mv = (int)(int8_t)(uint8_t)hm >> 4;
+        int v = (int)m.ld8(O_POS + obj) - mv + 160;
+        if (v >= 160) v -= 160;
+        if (v >= 160) v -= 160;
+        m.st8(O_POS + obj, (uint32_t)v);
+    }
+    STM_DEV void tia_write(uint32_t reg, uint32_t v)
+    {
+        reg &= 0x3F;
+        if (reg > 0x2C) return;
+        if (reg == 0x02) { wsync = true; return; }
+        if (reg == 0x03 || (reg >= 0x15 && reg <= 0x1A)) return;
+        catchup(cur_x());
+        if (reg >= 0x04 && reg <= 0x0F) { m.st8(O_NUSIZ0 + (reg - 4), v); return; }   // NUSIZ0..PF2 are laid out in register order
+        if (reg >= 0x1D && reg <= 0x1F) { m.st8(O_ENAM0 + (reg - 0x1D), v); return; }   // ENAM0, ENAM1, ENABL
+        if (reg >= 0x20 && reg <= 0x27) { m.st8(O_HMP0 + (reg - 0x20), v); return; }   // HMP0..VDELBL likewise
+        switch (reg) {
+        case 0x00:
+            if ((v & 2) && !(m.ld8(O_VSYNC) & 2)) { flags |= STM_F_FRAME_DONE; end_line_no = line; line = 0; }
+            m.st8(O_VSYNC, v); break;
+        case 0x01:
+            if (v & 0x80) m.st8(O_CHARGE, 0);
+            m.st8(O_VBLANK, v); update_latch(); break;
+        case 0x10: set_pos(STM_P0, true); break;
+        case 0x11: set_pos(STM_P1, true); break;
+        case 0x12: set_pos(STM_M0, false); break;
+        case 0x13: set_pos(STM_M1, false); break;
+        case 0x14: set_pos(STM_BL, false); break;
+        case 0x1B: m.st8(O_GRP0, v); m.st8(O_GRP1_OLD, m.ld8(O_GRP1)); break;
+        case 0x1C: m.st8(O_GRP1, v); m.st8(O_GRP0_OLD, m.ld8(O_GRP0)); m.st8(O_ENABL_OLD, m.ld8(O_ENABL)); break;
+        case 0x28:
+            if ((m.ld8(O_RESMP0) & 2) && !(v & 2)) m.st8(O_POS + STM_M0, (m.ld8(O_POS + STM_P0) + 4u) % 160u);
+            m.st8(O_RESMP0, v); break;
+        case 0x29:
+            if ((m.ld8(O_RESMP1) & 2) && !(v & 2)) m.st8(O_POS + STM_M1, (m.ld8(O_POS + STM_P1) + 4u) % 160u);
+            m.st8(O_RESMP1, v); break;
+        case 0x2A:
+            hmove_obj(STM_P0, m.ld8(O_HMP0)); hmove_obj(STM_P1, m.ld8(O_HMP1));
+            hmove_obj(STM_M0, m.ld8(O_HMM0)); hmove_obj(STM_M1, m.ld8(O_HMM1));
+            hmove_obj(STM_BL, m.ld8(O_HMBL));
+            if (hcyc * 3 < STM_HBLANK_CLK) flags |= STM_F_HMOVE_BLANK;
+            break;
+        case 0x2B:
+            m.st8(O_HMP0, 0); m.st8(O_HMP1, 0); m.st8(O_HMM0, 0); m.st8(O_HMM1, 0); m.st8(O_HMBL, 0); break;
+        case 0x2C: m.st16(O_CX, 0); break;
+        default: break;
+        }
+    }
+
+    // ---------------- RIOT ----------------
+    STM_DEV uint32_t swcha_in()
+    {
+        if (gp.controller == STM_CTRL_PADDLE) return fire_pressed() ? 0x7Fu : 0xFFu;
+        uint32_t d = dir_bits(), v = 0xFF;
+        if (d & 8) v &= ~0x80u;
+        if (d & 4) v &= ~0x40u;
+        if (d & 2) v &= ~0x20u;
+        if (d & 1) v &= ~0x10u;
+        return v;
+    }
+    STM_DEV uint32_t riot_read(uint32_t addr)
+    {
+        if (addr & 4) {
+            if (addr & 1) return tflag;
+            uint32_t v = timer >= 0 ? ((uint32_t)timer >> m.ld8(O_TSHIFT)) & 0xFFu : (uint32_t)timer & 0xFFu;
+            tflag &= 0x7F;
+            return v;
+        }
+        uint32_t sel = addr & 3;
+        if (sel == 0) { uint32_t d = m.ld8(O_SWACNT); return (m.ld8(O_SWCHA_OUT) & d) | (swcha_in() & ~d & 0xFFu); }
+        if (sel == 1) return m.ld8(O_SWACNT);
+        if (sel == 2) { uint32_t d = m.ld8(O_SWBCNT); return (m.ld8(O_SWCHB_OUT) & d) | (0x0Bu & ~d); }
+        return m.ld8(O_SWBCNT);
+    }
+    STM_DEV void riot_write(uint32_t addr, uint32_t v)
+    {
+        if (addr & 4) {
+            if (addr & 0x10) {
+                uint32_t sh = (0x0A060300u >> (8 * (addr & 3))) & 0xFFu;
+                m.st8(O_TSHIFT, sh);
+                timer = (int32_t)(v << sh) - 1;
+                tflag &= 0x7F;
+            }
+            return;
+        }
+        m.st8(O_SWCHA_OUT + (addr & 3), v);     // SWCHA_OUT, SWACNT, SWCHB_OUT, SWBCNT are consecutive
+    }
+
+    // ---------------- bus ----------------
+    STM_DEV uint32_t rom_at(uint32_t addr) { return m.rom8((bank << 12) | (addr & gp.rom_mask)); }
+    STM_DEV void hotspot(uint32_t addr)
+    {
+        if (gp.bank_scheme == STM_BANK_F8) {
+            if (addr == 0x1FF8) bank = 0; else if (addr == 0x1FF9) bank = 1;
+        }
+    }
+    STM_DEV uint32_t peek(uint32_t addr)
+    {
+        addr &= 0x1FFF;
+        if (addr & 0x1000) return rom_at(addr);
+        if ((addr & 0x280) == 0x80) return m.ld8(addr & 0x7F);
+        return 0;
+    }
+    STM_DEV uint32_t rd(uint32_t addr)
+    {
+        addr &= 0x1FFF;
+        if ((addr & 0x1280) == 0x80) return m.ld8(addr & 0x7F);          // RAM first: the common case
+        if (addr & 0x1000) { hotspot(addr); return rom_at(addr); }
+        if (!(addr & 0x80)) return tia_read(addr);
+        return riot_read(addr);
+    }
+    STM_DEV void wr(uint32_t addr, uint32_t v)
+    {
+        addr &= 0x1FFF; v &= 0xFF;
+        if ((addr & 0x1280) == 0x80) { m.st8(addr & 0x7F, v); return; }
+        if (addr & 0x1000) { hotspot(addr); return; }
+        if (!(addr & 0x80)) { tia_write(addr, v); return; }
+        riot_write(addr, v);
+    }
+    STM_DEV void push(uint32_t v) { wr(0x100 | sp, v); sp = (sp - 1) & 0xFF; }
+    STM_DEV uint32_t pull() { sp = (sp + 1) & 0xFF; return rd(0x100 | sp); }
+    STM_DEV uint32_t peek16zp(uint32_t z) { return peek(z & 0xFF) | (peek((z + 1) & 0xFF) << 8); }
+
+    // ---------------- ALU helpers ----------------
+    STM_DEV void setnz(uint32_t v) { p = (p & ~(FN | FZ)) | (v & 0x80) | ((v & 0xFF) ? 0u : (uint32_t)FZ); }
+    STM_DEV void adc(uint32_t v)
+    {
+        uint32_t cin = p & FC;
+        if (p & FD) {
+            uint32_t al = (a & 0x0F) + (v & 0x0F) + cin;
+            if (al > 9) al += 6;
+            uint32_t ah = (a >> 4) + (v >> 4) + (al > 0x0F ? 1u : 0u);
+            uint32_t bin = (a + v + cin) & 0xFF;
+            p &= ~(uint32_t)(FN | FZ | FV | FC);
+            if (!bin) p |= FZ;
+            if (ah & 8) p |= FN;
+            if (~(a ^ v) & (a ^ (ah << 4)) & 0x80) p |= FV;
+            if (ah > 9) ah += 6;
+            if (ah > 15) p |= FC;
+            a = ((ah << 4) | (al & 0x0F)) & 0xFF;
+        } else {
+            uint32_t s = a + v + cin;
+            p &= ~(uint32_t)(FV | FC);
+            if (s > 0xFF) p |= FC;
+            if (~(a ^ v) & (a ^ s) & 0x80) p |= FV;
+            a = s & 0xFF;
+            setnz(a);
+        }
+    }
+    STM_DEV void sbc(uint32_t v)
+    {
+        uint32_t bc = (p & FC) ? 0u : 1u;
+        uint32_t s = a - v - bc;
+        uint32_t res = s & 0xFF;
+        bool dec = (p & FD) != 0;
+        p &= ~(uint32_t)(FV | FC);
+        if (!(s & 0x100)) p |= FC;
+        if ((a ^ v) & (a ^ s) & 0x80) p |= FV;
+        setnz(res);
+        if (dec) {
+            int al = (int)(a & 0x0F) - (int)(v & 0x0F) - (int)bc;
+            int ah = (int)(a >> 4) - (int)(v >> 4);
+            if (al & 0x10) { al -= 6; ah--; }
+            if (ah & 0x10) ah -= 6;
+            res = (uint32_t)(((ah << 4) | (al & 0x0F)) & 0xFF);
+        }
+        a = res;
+    }
+    STM_DEV void cmp(uint32_t r, uint32_t v)
+    {
+        uint32_t d = r - v;
+        p &= ~(uint32_t)FC;
+        if (!(d & 0x100)) p |= FC;
+        setnz(d);
+    }
+    STM_DEV uint32_t asl(uint32_t v) { p = (p & ~(uint32_t)FC) | (v >> 7); v = (v << 1) & 0xFF; setnz(v); return v; }
+    STM_DEV uint32_t lsr(uint32_t v) { p = (p & ~(uint32_t)FC) | (v & 1); v >>= 1; setnz(v); return v; }
+    STM_DEV uint32_t rol(uint32_t v) { uint32_t c = p & FC; p = (p & ~(uint32_t)FC) | (v >> 7); v = ((v << 1) | c) & 0xFF; setnz(v); return v; }
+    STM_DEV uint32_t ror(uint32_t v) { uint32_t c = p & FC; p = (p & ~(uint32_t)FC) | (v & 1); v = (v >> 1) | (c << 7); setnz(v); return v; }
+
+    // ---------------- one instruction ----------------
+    STM_DEV void exec_one()
+    {
+        // fetch: opcode + two operand bytes
+        uint32_t op, b1, b2;
+        uint32_t a13 = pc & 0x1FFF;
+        if ((a13 & 0x1000) && (a13 & 0xFFF) <= 0xFFD) {
+            uint32_t off = (bank << 12) | (a13 & gp.rom_mask);
+            uint32_t wi = off >> 2;
+            uint32_t w_lo = m.rom32(wi);
+            uint32_t wrap = (gp.rom_mask >> 2);
+            uint32_t wi2 = ((wi + 1) & wrap) | (wi & ~wrap);
+            uint32_t w_hi = m.rom32(wi2);
+            uint32_t f = funnel_r(w_lo, w_hi, (off & 3) * 8);
+            op = f & 0xFF; b1 = (f >> 8) & 0xFF; b2 = (f >> 16) & 0xFF;
+        } else {
+            op = peek(pc); b1 = peek(pc + 1); b2 = peek(pc + 2);
+        }
+        uint32_t info = m.opinfo(op);
+        uint32_t mode = info & 15, kind = (info >> 4) & 3, cyc = (info >> 6) & 15, cls = info >> 10;
+
+        // effective address
+        uint32_t ea = 0, npc;
+        {
+            uint32_t idx = (mode == M_ZPX || mode == M_ABX) ? x : ((mode == M_ZPY || mode == M_ABY || mode == M_INY) ? y : 0u);
+            if (mode >= M_ZP && mode <= M_ZPY) { ea = (b1 + idx) & 0xFF; }
+            else if (mode >= M_ABS && mode <= M_ABY) {
+                uint32_t base = b1 | (b2 << 8);
+                ea = (base + idx) & 0xFFFF;
+                if (kind == K_R && ((ea ^ base) & 0xFF00)) cyc++;
+            } else if (mode == M_INX) { ea = peek16zp(b1 + x); }
+            else if (mode == M_INY) {
+                uint32_t base = peek16zp(b1);
+                ea = (base + idx) & 0xFFFF;
+                if (kind == K_R && ((ea ^ base) & 0xFF00)) cyc++;
+            } else if (mode == M_IND) {
+                uint32_t ptr = b1 | (b2 << 8);
+                ea = peek(ptr) | (peek((ptr & 0xFF00) | ((ptr + 1) & 0xFF)) << 8);
+            }
+            uint32_t len = (mode == M_IMP || mode == M_ACC) ? 1u : ((mode == M_ABS || mode == M_ABX || mode == M_ABY || mode == M_IND) ? 3u : 2u);
+            npc = (pc + len) & 0xFFFF;
+        }
+        if (cls == C_BRA) {
+            // condition flag by opcode bits 7..6: N V C Z ; bit 5 = required value
+            uint32_t fsel = op >> 6;
+            uint32_t fbit = fsel == 0 ? FN : (fsel == 1 ? FV : (fsel == 2 ? FC : FZ));
+            bool want = (op & 0x20) != 0;
+            if (((p & fbit) != 0) == want) {
+                uint32_t t = (npc + (uint32_t)(int32_t)(int8_t)(uint8_t)b1) & 0xFFFF;
+                cyc += 1 + (((t ^ npc) & 0xFF00) ? 1u : 0u);
+                npc = t;
+            }
+        }
+
+        wsync = false;
+        advance(cyc - 1);
+
+        uint32_t v = 0;
+        if (mode == M_IMM) v = b1;
+        else if (kind == K_R || kind == K_M) v = rd(ea);
+        else if (mode == M_ACC) v = a;
+
+        bool wb = false;            // write v back to ea (or A for M_ACC)
+        switch (cls) {
+        case C_LDA: a = v; setnz(v); break;
+        case C_LDX: x = v; setnz(v); break;
+        case C_LDY: y = v; setnz(v); break;
+        case C_LAX: a = x = v; setnz(v); break;
+        case C_STA: wr(ea, a); break;
+        case C_STX: wr(ea, x); break;
+        case C_STY: wr(ea, y); break;
+        case C_SAX: wr(ea, a & x); break;
+        case C_TAX: x = a; setnz(x); break;
+        case C_TAY: y = a; setnz(y); break;
+        case C_TXA: a = x; setnz(a); break;
+        case C_TYA: a = y; setnz(a); break;
+        case C_TSX: x = sp; setnz(x); break;
+        case C_TXS: sp = x; break;
+        case C_PHA: push(a); break;
+        case C_PHP: push(p | FB | FU); break;
+        case C_PLA: a = pull(); setnz(a); break;
+        case C_PLP: p = (pull() & ~(uint32_t)FB) | FU; break;
+        case C_AND: a &= v; setnz(a); break;
+        case C_ORA: a |= v; setnz(a); break;
+        case C_EOR: a ^= v; setnz(a); break;
+        case C_ADC: adc(v); break;
+        case C_SBC: sbc(v); break;
+        case C_CMP: cmp(a, v); break;
+        case C_CPX: cmp(x, v); break;
+        case C_CPY: cmp(y, v); break;
+        case C_BIT: p = (p & ~(uint32_t)(FN | FV | FZ)) | (v & 0xC0) | ((v & a) ? 0u : (uint32_t)FZ); break;
+        case C_ASL: v = asl(v); wb = true; break;
+        case C_LSR: v = lsr(v); wb = true; break;
+        case C_ROL: v = rol(v); wb = true; break;
+        case C_ROR: v = ror(v); wb = true; break;
+        case C_INC: v = (v + 1) & 0xFF; setnz(v); wb = true; break;
+        case C_DEC: v = (v - 1) & 0xFF; setnz(v); wb = true; break;
+        case C_INX: x = (x + 1) & 0xFF; setnz(x); break;
+        case C_INY: y = (y + 1) & 0xFF; setnz(y); break;
+        case C_DEX: x = (x - 1) & 0xFF; setnz(x); break;
+        case C_DEY: y = (y - 1) & 0xFF; setnz(y); break;
+        case C_CLC: p &= ~(uint32_t)FC; break;
+        case C_SEC: p |= FC; break;
+        case C_CLI: p &= ~(uint32_t)FI; break;
+        case C_SEI: p |= FI; break;
+        case C_CLV: p &= ~(uint32_t)FV; break;
+        case C_CLD: p &= ~(uint32_t)FD; break;
+        case C_SED: p |= FD; break;
+        case C_JMP: npc = ea; break;
+        case C_JSR: { uint32_t ret = (pc + 2) & 0xFFFF; push(ret >> 8); push(ret & 0xFF); npc = ea; break; }
+        case C_RTS: { uint32_t lo = pull(); uint32_t hi = pull(); npc = (((hi << 8) | lo) + 1) & 0xFFFF; break; }
+        case C_RTI: { p = (pull() & ~(uint32_t)FB) | FU; uint32_t lo = pull(); uint32_t hi = pull(); npc = (hi << 8) | lo; break; }
+        case C_BRK: {
+            uint32_t ret = (pc + 2) & 0xFFFF;
+            push(ret >> 8); push(ret & 0xFF); push(p | FB | FU);
+            p |= FI;
+            npc = peek(0xFFFE) | (peek(0xFFFF) << 8);
+            break; }
+        case C_DCP: v = (v - 1) & 0xFF; wr(ea, v); cmp(a, v); break;
+        case C_ISC: v = (v + 1) & 0xFF; wr(ea, v); sbc(v); break;
+        case C_SLO: v = asl(v); wr(ea, v); a |= v; setnz(a); break;
+        case C_RLA: v = rol(v); wr(ea, v); a &= v; setnz(a); break;
+        case C_SRE: v = lsr(v); wr(ea, v); a ^= v; setnz(a); break;
+        case C_RRA: v = ror(v); wr(ea, v); adc(v); break;
+        case C_ANC: a &= v; setnz(a); p = (p & ~(uint32_t)FC) | (a >> 7); break;
+        case C_ALR: a &= v; a = lsr(a); break;
+        case C_SBX: { uint32_t t = (a & x) - v; p &= ~(uint32_t)FC; if (!(t & 0x100)) p |= FC; x = t & 0xFF; setnz(x); break; }
+        default: break;     // C_NOP, C_BRA (resolved above)
+        }
+        if (wb) { if (mode == M_ACC) a = v; else wr(ea, v); }
+
+        pc = npc;
+        advance(1);
+        if (wsync && hcyc != 0) advance(STM_CYC_PER_LINE - hcyc);
+    }
+
+    // ---------------- one emulated frame ----------------
+    // Rows the frame never reached are zero-filled, as the oracle does.
+    STM_DEV void run_frame(uint32_t ale_action, bool want_pixels)
+    {
+        render = want_pixels;
+        set_action(ale_action);
+        flags &= ~(uint32_t)STM_F_FRAME_DONE;
+        while (!(flags & STM_F_FRAME_DONE)) exec_one();
+        if (want_pixels) {
+            int r0 = (int)end_line_no - STM_YSTART; if (r0 < 0) r0 = 0;
+            for (int r = r0; r < STM_VIS_H; r++)
+                for (uint32_t g = 0; g < 40; g++) m.px4((uint32_t)r, g, 0);
+        }
+        m.st32(O_FRAME, m.ld32(O_FRAME) + 1);
+    }
+
+    // ---------------- get_data (cule_bfs.py:157-158) ----------------
+    STM_DEV int bcd_score(const uint8_t *addr)
+    {
+        int s = 0;
+        for (int i = 0; i < 3; i++) {
+            if (addr[i] == 0xFF) continue;
+            uint32_t b = m.ld8(addr[i] & 0x7F);
+            s = s * 100 + (int)(b >> 4) * 10 + (int)(b & 15);
+        }
+        return s;
+    }
+    STM_DEV int game_lives()
+    {
+        if (gp.lives_addr == 0xFF) return 0;
+        return (int)((m.ld8(gp.lives_addr & 0x7F) >> gp.lives_shift) & gp.lives_mask);
+    }
+    // returns the frame reward; updates done / lives
+    STM_DEV int get_data(bool episodic_life, uint32_t &done, int &lives)
+    {
+        int score = bcd_score(gp.score_addr) - bcd_score(gp.score2_addr);
+        int r = score - (int)m.ld32(O_SCORE_PREV);
+        m.st32(O_SCORE_PREV, (uint32_t)score);
+        int lv = game_lives();
+        bool term = false;
+        if (gp.term_addr != 0xFF) term = (m.ld8(gp.term_addr & 0x7F) & gp.term_mask) == gp.term_value;
+        if (term || (episodic_life && lv < lives)) done = 1;
+        lives = lv;
+        return r;
+    }
+};
+
+} // namespace stm

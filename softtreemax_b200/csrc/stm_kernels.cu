@@ -1,0 +1,685 @@
+// stm_kernels.cu — sm_100a kernels K1 (clone), K2 (batched Atari 2600 agent step), K3 (frames)
+// and the C ABI of include/stm_b200.h around them.
+//
+// Reference call sites replaced (policies/cule_bfs.py): expand :143 / new_expand :81-96 (K1),
+// step + get_data :152-158 (K2), generate_frames + max + replicate_state + cat :162-172 (K3),
+// the per-depth driver loop :129-173 and epilogue :204-209 (stm_bfs).
+//
+// Data layout in HBM
+//   env pool      : n x 256 B state blobs (include/stm_state.h), rewards f32, done u8, lives i32
+//   obs stacks    : n x 4 x 84 x 84 u8
+//   native scratch: per tile of 32 envs, [frame 0..1][row 0..209][group 0..39][lane 0..31] u32,
+//                   one u32 = 4 horizontally adjacent pixels (7-bit colour indices) of one env.
+//                   Lane-minor, so that a warp whose lanes draw the same 4-pixel group of the same
+//                   row (the common case: siblings run the same display kernel in near lock-step)
+//                   issues ONE coalesced 128-byte store, and K3 reads it back coalesced.
+#include <cuda_runtime.h>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <cmath>
+#include <new>
+#include "../../include/stm_b200.h"
+#include "../../include/stm_palette.h"
+#include "emu_core.cuh"
+
+namespace {
+
+using namespace stm;
+
+static_assert(sizeof(stm_env_state) == STM_STATE_BYTES, "state blob must be 256 bytes");
+static_assert(offsetof(stm_env_state, pc) == O_PC && offsetof(stm_env_state, timer) == O_TIMER &&
+              offsetof(stm_env_state, cx) == O_CX && offsetof(stm_env_state, pos) == O_POS &&
+              offsetof(stm_env_state, vsync) == O_VSYNC && offsetof(stm_env_state, nusiz0) == O_NUSIZ0 &&
+              offsetof(stm_env_state, pf2) == O_PF2 && offsetof(stm_env_state, enam0) == O_ENAM0 &&
+              offsetof(stm_env_state, hmp0) == O_HMP0 && offsetof(stm_env_state, vdelbl) == O_VDELBL &&
+              offsetof(stm_env_state, resmp1) == O_RESMP1 && offsetof(stm_env_state, score_prev) == O_SCORE_PREV &&
+              offsetof(stm_env_state, swcha_out) == O_SWCHA_OUT && offsetof(stm_env_state, paddle) == O_PADDLE,
+              "emu_core.cuh offsets out of sync with stm_state.h");
+
+constexpr int kTileEnvs = 32;                                   // envs per native-scratch tile (= warp)
+constexpr size_t kTileWords = 2ull * STM_VIS_H * 40 * kTileEnvs; // u32 per tile (2 frames)
+constexpr int kStepThreads = 128;
+
+thread_local char g_create_error[256] = "";
+
+} // namespace
+
+struct stm_ctx {
+    int device = 0;
+    stm_game_desc desc{};
+    GameParams gp{};
+    uint32_t rom_words = 0;
+    uint32_t *d_rom = nullptr;       // cartridge image, as words
+    uint32_t *d_lut = nullptr;       // 256-entry decode table
+    uint32_t *d_scratch = nullptr;   // native frames
+    uint8_t  *d_stepped = nullptr;   // per scratch env: 1 if the env was emulated by the last stm_step
+    int scratch_envs = 0;
+    int last_render_frames = 0;      // how many native frames the last stm_step(render) produced (1 or 2)
+    // intermediate-level pools for stm_bfs (ping-pong)
+    uint8_t *pool_state[2] = {nullptr, nullptr};
+    float   *pool_reward[2] = {nullptr, nullptr};
+    uint8_t *pool_done[2] = {nullptr, nullptr};
+    int32_t *pool_lives[2] = {nullptr, nullptr};
+    uint8_t *pool_stack[2] = {nullptr, nullptr};
+    size_t pool_envs[2] = {0, 0};
+    size_t pool_stack_envs[2] = {0, 0};
+    // device staging for stm_bfs_host
+    uint8_t *h_in_state = nullptr, *h_in_stack = nullptr, *h_out_stack = nullptr;
+    float *h_out_reward = nullptr; uint8_t *h_out_done = nullptr; int32_t *h_out_lives = nullptr;
+    size_t h_roots = 0, h_leaves = 0;
+    uint32_t reset_pc = 0;
+    long long launches = 0;
+    char err[256] = "";
+};
+
+namespace {
+
+int fail(stm_ctx *ctx, int code, const char *fmt, ...)
+{
+    char *dst = ctx ? ctx->err : g_create_error;
+    va_list ap; va_start(ap, fmt); vsnprintf(dst, 256, fmt, ap); va_end(ap);
+    return code;
+}
+#define CUDA_TRY(ctx, expr) do { cudaError_t e_ = (expr); if (e_ != cudaSuccess) \
+    return fail(ctx, e_ == cudaErrorMemoryAllocation ? STM_ERR_NOMEM : STM_ERR_CUDA, "%s: %s", #expr, cudaGetErrorString(e_)); } while (0)
+
+// ---------------------------------------------------------------------------------------------
+// K1 — clone.  Persistent CTAs; a tile of kCloneParents parent rows (8 KB) is brought into shared
+// memory with one 1-D bulk async copy (TMA, completes on an mbarrier), double buffered, and fanned
+// out with 128-bit stores.  HBM traffic = n_src*S read + n_src*fanout*S written (the algorithmic
+// minimum); the small per-env arrays ride along.
+// ---------------------------------------------------------------------------------------------
+constexpr int kCloneParents = 32;
+constexpr int kCloneThreads = 256;
+
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t count)
+{ asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" :: "r"(smem_u32(bar)), "r"(count)); }
+__device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, uint32_t bytes)
+{ asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(smem_u32(bar)), "r"(bytes) : "memory"); }
+__device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity)
+{
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "WAIT_%=:\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+        "@p bra DONE_%=;\n\t"
+        "bra WAIT_%=;\n\t"
+        "DONE_%=:\n\t}"
+        :: "r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(void *dst_smem, const void *src_gmem, uint32_t bytes, uint64_t *bar)
+{
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 :: "r"(smem_u32(dst_smem)), "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+
+__global__ void __launch_bounds__(kCloneThreads)
+stm_clone_kernel(const uint4 *__restrict__ src, uint4 *__restrict__ dst,
+                 const float *__restrict__ src_r, float *__restrict__ dst_r,
+                 const uint8_t *__restrict__ src_d, uint8_t *__restrict__ dst_d,
+                 const int32_t *__restrict__ src_l, int32_t *__restrict__ dst_l,
+                 int n_src, int fanout)
+{
+    __shared__ __align__(128) uint4 tile[2][kCloneParents * 16];
+    __shared__ __align__(8) uint64_t bar[2];
+    const int ntiles = (n_src + kCloneParents - 1) / kCloneParents;
+    if (threadIdx.x == 0) {
+        mbar_init(&bar[0], 1); mbar_init(&bar[1], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+    auto issue = [&](int t, int stage) {
+        int p0 = t * kCloneParents;
+        int np = min(kCloneParents, n_src - p0);
+        uint32_t bytes = (uint32_t)np * STM_STATE_BYTES;
+        mbar_expect_tx(&bar[stage], bytes);
+        bulk_g2s(tile[stage], src + (size_t)p0 * 16, bytes, &bar[stage]);
+    };
+    int t = blockIdx.x, it = 0;
+    if (t < ntiles && threadIdx.x == 0) issue(t, 0);
+    for (; t < ntiles; t += gridDim.x, it++) {
+        int stage = it & 1;
+        int tn = t + gridDim.x;
+        if (tn < ntiles && threadIdx.x == 0) issue(tn, stage ^ 1);
+        mbar_wait(&bar[stage], (it >> 1) & 1);
+        int p0 = t * kCloneParents;
+        int np = min(kCloneParents, n_src - p0);
+        int nchunks = np * fanout * 16;
+        uint4 *out = dst + (size_t)p0 * fanout * 16;
+        for (int i = threadIdx.x; i < nchunks; i += kCloneThreads) {
+            int child = i >> 4, piece = i & 15;
+            int parent = child / fanout;
+            out[i] = tile[stage][parent * 16 + piece];
+        }
+        if (src_r) {
+            for (int c = threadIdx.x; c < np * fanout; c += kCloneThreads) {
+                int parent = p0 + c / fanout;
+                size_t o = (size_t)p0 * fanout + c;
+                dst_r[o] = src_r[parent]; dst_d[o] = src_d[parent]; dst_l[o] = src_l[parent];
+            }
+        }
+        __syncthreads();      // everyone is done reading tile[stage] before it is refilled
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// K2 — batched agent step.  One env per thread, 128 envs per CTA.
+// Shared memory: the CTA's 128 state blobs, word-interleaved (word k of env t at [k*128 + t], so
+// lane t always hits bank t%32: conflict-free for every access pattern, RAM bytes included), the
+// cartridge image (4 or 8 KB) and the decode table.
+// ---------------------------------------------------------------------------------------------
+struct DevMem {
+    uint8_t *blob;             // &sblob[tid] as bytes
+    const uint32_t *rom;       // shared
+    const uint32_t *lut;       // shared
+    uint32_t *scr;             // native scratch of this env's tile, + lane
+    uint32_t fsel;             // which of the two native frames is being drawn
+
+    __device__ __forceinline__ uint32_t boff(uint32_t o) const { return (o >> 2) * (kStepThreads * 4) + (o & 3); }
+    __device__ __forceinline__ uint32_t ld8(uint32_t o) const { return blob[boff(o)]; }
+    __device__ __forceinline__ void st8(uint32_t o, uint32_t v) { blob[boff(o)] = (uint8_t)v; }
+    __device__ __forceinline__ uint32_t ld16(uint32_t o) const { return *(const uint16_t *)(blob + boff(o)); }
+    __device__ __forceinline__ void st16(uint32_t o, uint32_t v) { *(uint16_t *)(blob + boff(o)) = (uint16_t)v; }
+    __device__ __forceinline__ uint32_t ld32(uint32_t o) const { return *(const uint32_t *)(blob + boff(o)); }
+    __device__ __forceinline__ void st32(uint32_t o, uint32_t v) { *(uint32_t *)(blob + boff(o)) = v; }
+    __device__ __forceinline__ uint32_t rom8(uint32_t i) const { return (rom[i >> 2] >> ((i & 3) * 8)) & 0xFFu; }
+    __device__ __forceinline__ uint32_t rom32(uint32_t wi) const { return rom[wi]; }
+    __device__ __forceinline__ uint32_t opinfo(uint32_t op) const { return lut[op]; }
+    __device__ __forceinline__ void px4(uint32_t row, uint32_t g, uint32_t w)
+    { scr[((fsel * STM_VIS_H + row) * 40 + g) * kTileEnvs] = w; }
+    __device__ __forceinline__ void px1(uint32_t row, uint32_t x, uint32_t v)
+    { ((uint8_t *)&scr[((fsel * STM_VIS_H + row) * 40 + (x >> 2)) * kTileEnvs])[x & 3] = (uint8_t)v; }
+};
+
+struct StepArgs {
+    uint8_t *states; const uint8_t *actions; float *rewards; uint8_t *done; int32_t *lives;
+    const uint32_t *rom; const uint32_t *lut; uint32_t *scratch; uint8_t *stepped;
+    int n, frameskip, episodic_life, render; uint32_t rom_words; float weight;
+    GameParams gp;
+};
+
+__global__ void __launch_bounds__(kStepThreads, 4)
+stm_step_kernel(const StepArgs a)
+{
+    extern __shared__ __align__(16) uint32_t smem[];
+    uint32_t *sblob = smem;                              // 64 words x 128 threads
+    uint32_t *srom = sblob + 64 * kStepThreads;
+    uint32_t *slut = srom + a.rom_words;
+    const int tid = threadIdx.x;
+    for (uint32_t i = tid; i < a.rom_words; i += kStepThreads) srom[i] = a.rom[i];
+    for (uint32_t i = tid; i < 256; i += kStepThreads) slut[i] = a.lut[i];
+    const int env = blockIdx.x * kStepThreads + tid;
+    const bool valid = env < a.n;
+    if (valid) {
+        const uint4 *g = reinterpret_cast<const uint4 *>(a.states + (size_t)env * STM_STATE_BYTES);
+        #pragma unroll
+        for (int k = 0; k < 16; k++) {
+            uint4 v = g[k];
+            sblob[(4 * k + 0) * kStepThreads + tid] = v.x; sblob[(4 * k + 1) * kStepThreads + tid] = v.y;
+            sblob[(4 * k + 2) * kStepThreads + tid] = v.z; sblob[(4 * k + 3) * kStepThreads + tid] = v.w;
+        }
+    }
+    __syncthreads();
+    if (!valid) return;
+    uint32_t done = a.done[env];
+    if (a.stepped) a.stepped[env] = done ? 0 : 1;
+    if (done) return;                                    // frozen env: nothing changes
+
+    DevMem m;
+    m.blob = reinterpret_cast<uint8_t *>(sblob + tid);
+    m.rom = srom; m.lut = slut;
+    m.scr = a.scratch ? a.scratch + (size_t)(env / kTileEnvs) * kTileWords + (env % kTileEnvs) : nullptr;
+    m.fsel = 0;
+    Emu<DevMem> e(m, a.gp);
+    e.load();
+    int lives = a.lives[env];
+    float rew = a.rewards[env];
+    uint32_t act = a.actions ? a.actions[env] : (uint32_t)(env % (int)a.gp.n_actions);
+    uint32_t ale = a.gp.actions[act];
+    for (int f = 0; f < a.frameskip; f++) {
+        bool want = a.render && f >= a.frameskip - 2;
+        // the newest frame always goes to slot 1, the one before it to slot 0
+        m.fsel = (f == a.frameskip - 1) ? 1u : 0u;
+        e.run_frame(ale, want);
+        int r = e.get_data(a.episodic_life != 0, done, lives);
+        rew = __fadd_rn(rew, __fmul_rn(a.weight, (float)r));
+    }
+    e.store();
+    uint4 *g = reinterpret_cast<uint4 *>(a.states + (size_t)env * STM_STATE_BYTES);
+    #pragma unroll
+    for (int k = 0; k < 16; k++) {
+        uint4 v;
+        v.x = sblob[(4 * k + 0) * kStepThreads + tid]; v.y = sblob[(4 * k + 1) * kStepThreads + tid];
+        v.z = sblob[(4 * k + 2) * kStepThreads + tid]; v.w = sblob[(4 * k + 3) * kStepThreads + tid];
+        g[k] = v;
+    }
+    a.rewards[env] = rew; a.done[env] = (uint8_t)done; a.lives[env] = lives;
+}
+
+// ---------------------------------------------------------------------------------------------
+// K3 — observation kernel.  One CTA per (tile of 32 envs, output row oy).  The four native rows
+// the output row needs (2 source rows x 2 frames) are read coalesced (lane-minor) and transposed
+// into shared memory env-major with an odd pitch; then 21 threads per env each produce one packed
+// word (4 output pixels): grey LUT, 2x2 bilinear with integer weights, max over the two frames.
+// The same CTA moves row oy of the three older stack frames from the parent's stack.
+// HBM per leaf: reads 2*168*160 B of native frames (rows 2 mod 5 are never sampled) + 21 168 B of
+// parent stack, writes 28 224 B.
+// ---------------------------------------------------------------------------------------------
+constexpr int kFrameThreads = 256;
+constexpr int kPitch = 41;      // words per (source row, env) in shared memory; odd => conflict-free transpose
+
+__constant__ uint8_t c_gray[128] = STM_GRAY_LUT_INIT;
+
+__global__ void __launch_bounds__(kFrameThreads)
+stm_frames_kernel(const uint32_t *__restrict__ scratch, const uint8_t *__restrict__ stepped,
+                  const uint8_t *__restrict__ parent, uint8_t *__restrict__ child,
+                  int n, int fanout, int nframes)
+{
+    __shared__ uint32_t srows[4][kTileEnvs * kPitch];      // [frame*2 + {y0,y1}]
+    __shared__ uint8_t sgray[128];
+    const int tile = blockIdx.x, oy = blockIdx.y, tid = threadIdx.x;
+    const int env0 = tile * kTileEnvs;
+    const int nenv = min(kTileEnvs, n - env0);
+    if (tid < 128) sgray[tid] = c_gray[tid];
+    const int ny = 10 * oy + 3, y0 = ny >> 2, fy = ny & 3;
+    const int y1 = min(y0 + 1, STM_VIS_H - 1);
+    const uint32_t *tbase = scratch + (size_t)tile * kTileWords;
+    for (int i = tid; i < 4 * 40 * kTileEnvs; i += kFrameThreads) {
+        int lane = i & 31, g = (i >> 5) % 40, rs = i / (40 * 32);
+        int frame = rs >> 1, row = (rs & 1) ? y1 : y0;
+        uint32_t v = 0;
+        if (frame >= 2 - nframes)        // with a single rendered frame only slot 1 holds data
+            v = tbase[((size_t)(frame * STM_VIS_H + row) * 40 + g) * kTileEnvs + lane];
+        srows[rs][lane * kPitch + g] = v;
+    }
+    __syncthreads();
+    // new frame -> child[env][3][oy][:]
+    for (int i = tid; i < nenv * 21; i += kFrameThreads) {
+        int e = i / 21, wq = i % 21;
+        uint32_t packed = 0;
+        if (stepped[env0 + e]) {
+            const uint8_t *r00 = reinterpret_cast<const uint8_t *>(&srows[0][e * kPitch]);
+            const uint8_t *r01 = reinterpret_cast<const uint8_t *>(&srows[1][e * kPitch]);
+            const uint8_t *r10 = reinterpret_cast<const uint8_t *>(&srows[2][e * kPitch]);
+            const uint8_t *r11 = reinterpret_cast<const uint8_t *>(&srows[3][e * kPitch]);
+            #pragma unroll
+            for (int k = 0; k < 4; k++) {
+                int ox = 4 * wq + k;
+                int nx = 80 * ox + 19, x0 = nx / 42, fx = nx - 42 * x0;
+                int x1 = min(x0 + 1, STM_VIS_W - 1);
+                int a00 = sgray[r00[x0] & 127], a01 = sgray[r00[x1] & 127];
+                int a10 = sgray[r01[x0] & 127], a11 = sgray[r01[x1] & 127];
+                int va = ((4 - fy) * ((42 - fx) * a00 + fx * a01) + fy * ((42 - fx) * a10 + fx * a11) + 84) / 168;
+                int b00 = sgray[r10[x0] & 127], b01 = sgray[r10[x1] & 127];
+                int b10 = sgray[r11[x0] & 127], b11 = sgray[r11[x1] & 127];
+                int vb = ((4 - fy) * ((42 - fx) * b00 + fx * b01) + fy * ((42 - fx) * b10 + fx * b11) + 84) / 168;
+                packed |= (uint32_t)max(va, vb) << (8 * k);
+            }
+        }
+        uint32_t *dst = reinterpret_cast<uint32_t *>(child + ((size_t)(env0 + e) * STM_STACK + 3) * STM_OBS_BYTES + oy * STM_OBS_W);
+        dst[wq] = packed;
+    }
+    // stack shift: child[env][0..2][oy] = parent[env / fanout][1..3][oy]
+    for (int i = tid; i < nenv * 63; i += kFrameThreads) {
+        int e = i / 63, r = i % 63, f = r / 21, wq = r % 21;
+        size_t pe = (size_t)(env0 + e) / fanout;
+        const uint32_t *s = reinterpret_cast<const uint32_t *>(parent + (pe * STM_STACK + f + 1) * STM_OBS_BYTES + oy * STM_OBS_W);
+        uint32_t *d = reinterpret_cast<uint32_t *>(child + ((size_t)(env0 + e) * STM_STACK + f) * STM_OBS_BYTES + oy * STM_OBS_W);
+        d[wq] = s[wq];
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// small kernels
+// ---------------------------------------------------------------------------------------------
+__global__ void stm_reset_kernel(uint8_t *states, float *rewards, uint8_t *done, int32_t *lives, int n,
+                                 uint32_t reset_pc, int lives0)
+{
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    uint4 *g = reinterpret_cast<uint4 *>(states + (size_t)i * STM_STATE_BYTES);
+    for (int k = 0; k < 16; k++) g[k] = make_uint4(0, 0, 0, 0);
+    stm_env_state *e = reinterpret_cast<stm_env_state *>(states + (size_t)i * STM_STATE_BYTES);
+    e->pc = (uint16_t)reset_pc; e->sp = 0xFD; e->p = 0x24; e->tshift = 10;
+    e->paddle[0] = e->paddle[1] = STM_PADDLE_INIT;
+    if (rewards) rewards[i] = 0.f;
+    if (done) done[i] = 0;
+    if (lives) lives[i] = lives0;
+}
+
+// root injection for stm_bfs: rewards/done zeroed (cule_bfs.py:115-118), lives decoded from RAM
+__global__ void stm_root_init_kernel(const uint8_t *states, float *rewards, uint8_t *done, int32_t *lives,
+                                     int n, GameParams gp)
+{
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    rewards[i] = 0.f; done[i] = 0;
+    int lv = 0;
+    if (gp.lives_addr != 0xFF) lv = (states[(size_t)i * STM_STATE_BYTES + (gp.lives_addr & 0x7F)] >> gp.lives_shift) & gp.lives_mask;
+    lives[i] = lv;
+}
+
+__global__ void stm_finalize_kernel(const float *rewards, float *out_rewards, int n, int clip)
+{
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    float r = rewards[i];
+    if (clip) r = (float)((r > 0.f) - (r < 0.f));
+    out_rewards[i] = r;
+}
+
+int ensure_scratch(stm_ctx *ctx, int n_envs)
+{
+    if (n_envs <= ctx->scratch_envs) return STM_OK;
+    int tiles = (n_envs + kTileEnvs - 1) / kTileEnvs;
+    if (ctx->d_scratch) { cudaFree(ctx->d_scratch); ctx->d_scratch = nullptr; }
+    if (ctx->d_stepped) { cudaFree(ctx->d_stepped); ctx->d_stepped = nullptr; }
+    ctx->scratch_envs = 0;
+    CUDA_TRY(ctx, cudaMalloc(&ctx->d_scratch, (size_t)tiles * kTileWords * sizeof(uint32_t)));
+    CUDA_TRY(ctx, cudaMalloc(&ctx->d_stepped, (size_t)tiles * kTileEnvs));
+    ctx->scratch_envs = tiles * kTileEnvs;
+    return STM_OK;
+}
+
+int launch_step(stm_ctx *ctx, uint8_t *states, const uint8_t *actions, int n, int frameskip,
+                int episodic_life, float weight, float *rewards, uint8_t *done, int32_t *lives,
+                int render, cudaStream_t st)
+{
+    StepArgs a;
+    a.states = states; a.actions = actions; a.rewards = rewards; a.done = done; a.lives = lives;
+    a.rom = ctx->d_rom; a.lut = ctx->d_lut;
+    a.scratch = render ? ctx->d_scratch : nullptr;
+    a.stepped = render ? ctx->d_stepped : nullptr;
+    a.n = n; a.frameskip = frameskip; a.episodic_life = episodic_life; a.render = render;
+    a.rom_words = ctx->rom_words; a.weight = weight; a.gp = ctx->gp;
+    size_t smem = (size_t)(64 * kStepThreads + ctx->rom_words + 256) * sizeof(uint32_t);
+    int blocks = (n + kStepThreads - 1) / kStepThreads;
+    stm_step_kernel<<<blocks, kStepThreads, smem, st>>>(a);
+    ctx->launches++;
+    if (render) ctx->last_render_frames = frameskip >= 2 ? 2 : 1;
+    CUDA_TRY(ctx, cudaGetLastError());
+    return STM_OK;
+}
+
+int launch_frames(stm_ctx *ctx, const uint8_t *parent, uint8_t *child, int n, int fanout, cudaStream_t st)
+{
+    dim3 grid((n + kTileEnvs - 1) / kTileEnvs, STM_OBS_H);
+    stm_frames_kernel<<<grid, kFrameThreads, 0, st>>>(ctx->d_scratch, ctx->d_stepped, parent, child, n, fanout,
+                                                     ctx->last_render_frames);
+    ctx->launches++;
+    CUDA_TRY(ctx, cudaGetLastError());
+    return STM_OK;
+}
+
+int launch_clone(stm_ctx *ctx, const uint8_t *ss, const float *sr, const uint8_t *sd, const int32_t *sl,
+                 uint8_t *ds, float *dr, uint8_t *dd, int32_t *dl, int n_src, int fanout, cudaStream_t st)
+{
+    int ntiles = (n_src + kCloneParents - 1) / kCloneParents;
+    int grid = ntiles < 148 * 4 ? ntiles : 148 * 4;       // persistent: up to 4 CTAs on each of the 148 SMs
+    stm_clone_kernel<<<grid, kCloneThreads, 0, st>>>(reinterpret_cast<const uint4 *>(ss), reinterpret_cast<uint4 *>(ds),
+                                                    sr, dr, sd, dd, sl, dl, n_src, fanout);
+    ctx->launches++;
+    CUDA_TRY(ctx, cudaGetLastError());
+    return STM_OK;
+}
+
+template <class T> int grow(stm_ctx *ctx, T *&p, size_t count)
+{
+    if (p) { cudaFree(p); p = nullptr; }
+    CUDA_TRY(ctx, cudaMalloc(&p, count * sizeof(T)));
+    return STM_OK;
+}
+
+int ensure_pool(stm_ctx *ctx, int which, size_t envs, size_t stack_envs)
+{
+    int rc;
+    if (envs > ctx->pool_envs[which]) {
+        ctx->pool_envs[which] = 0;
+        if ((rc = grow(ctx, ctx->pool_state[which], envs * STM_STATE_BYTES))) return rc;
+        if ((rc = grow(ctx, ctx->pool_reward[which], envs))) return rc;
+        if ((rc = grow(ctx, ctx->pool_done[which], envs))) return rc;
+        if ((rc = grow(ctx, ctx->pool_lives[which], envs))) return rc;
+        ctx->pool_envs[which] = envs;
+    }
+    if (stack_envs > ctx->pool_stack_envs[which]) {
+        ctx->pool_stack_envs[which] = 0;
+        if ((rc = grow(ctx, ctx->pool_stack[which], stack_envs * STM_STACK * STM_OBS_BYTES))) return rc;
+        ctx->pool_stack_envs[which] = stack_envs;
+    }
+    return STM_OK;
+}
+
+} // namespace
+
+// =============================================================================================
+// C ABI
+// =============================================================================================
+extern "C" {
+
+const char *stm_last_error(const stm_ctx *ctx) { return ctx ? ctx->err : g_create_error; }
+size_t stm_state_bytes(const stm_ctx *) { return STM_STATE_BYTES; }
+int stm_num_actions(const stm_ctx *ctx) { return ctx ? ctx->desc.n_actions : 0; }
+long long stm_launch_count(const stm_ctx *ctx) { return ctx ? ctx->launches : 0; }
+int stm_max_step_envs(const stm_ctx *ctx) { return ctx ? ctx->scratch_envs : 0; }
+
+int stm_ctx_create(stm_ctx **out, const stm_game_desc *desc, const uint8_t *rom, int device)
+{
+    if (!out || !desc || !rom) return fail(nullptr, STM_ERR_ARG, "stm_ctx_create: null argument");
+    *out = nullptr;
+    bool ok_size = (desc->bank_scheme == STM_BANK_NONE && (desc->rom_size == 2048 || desc->rom_size == 4096)) ||
+                   (desc->bank_scheme == STM_BANK_F8 && desc->rom_size == 8192);
+    if (!ok_size) return fail(nullptr, STM_ERR_ARG, "stm_ctx_create: unsupported rom_size %u / bank_scheme %u", desc->rom_size, desc->bank_scheme);
+    if (desc->n_actions < 1 || desc->n_actions > 18) return fail(nullptr, STM_ERR_ARG, "stm_ctx_create: n_actions %u out of range", desc->n_actions);
+    if (desc->controller > STM_CTRL_PADDLE) return fail(nullptr, STM_ERR_ARG, "stm_ctx_create: unknown controller");
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0)
+        return fail(nullptr, STM_ERR_CUDA, "stm_ctx_create: no CUDA device (%s); this library has no CPU fallback", cudaGetErrorString(e));
+    if (device < 0 || device >= ndev) return fail(nullptr, STM_ERR_ARG, "stm_ctx_create: device %d out of range", device);
+    stm_ctx *ctx = new (std::nothrow) stm_ctx();
+    if (!ctx) return fail(nullptr, STM_ERR_NOMEM, "stm_ctx_create: out of host memory");
+    ctx->device = device; ctx->desc = *desc;
+    GameParams &gp = ctx->gp;
+    memset(&gp, 0, sizeof(gp));
+    gp.rom_mask = desc->bank_scheme == STM_BANK_F8 ? 0xFFF : desc->rom_size - 1;
+    gp.bank_scheme = desc->bank_scheme; gp.controller = desc->controller; gp.n_actions = desc->n_actions;
+    memcpy(gp.actions, desc->actions, 18);
+    memcpy(gp.score_addr, desc->score_addr, 3); memcpy(gp.score2_addr, desc->score2_addr, 3);
+    gp.lives_addr = desc->lives_addr; gp.lives_shift = desc->lives_shift; gp.lives_mask = desc->lives_mask;
+    gp.term_addr = desc->term_addr; gp.term_mask = desc->term_mask; gp.term_value = desc->term_value;
+    ctx->rom_words = desc->rom_size / 4;
+    ctx->reset_pc = rom[0xFFC & gp.rom_mask] | (rom[0xFFD & gp.rom_mask] << 8);   // power-on bank is 0
+    uint32_t lut[256];
+    build_decode_table(lut);
+    int rc = STM_OK;
+    auto body = [&]() -> int {
+        CUDA_TRY(ctx, cudaSetDevice(device));
+        CUDA_TRY(ctx, cudaMalloc(&ctx->d_rom, desc->rom_size));
+        CUDA_TRY(ctx, cudaMalloc(&ctx->d_lut, sizeof(lut)));
+        CUDA_TRY(ctx, cudaMemcpy(ctx->d_rom, rom, desc->rom_size, cudaMemcpyHostToDevice));
+        CUDA_TRY(ctx, cudaMemcpy(ctx->d_lut, lut, sizeof(lut), cudaMemcpyHostToDevice));
+        size_t smem = (size_t)(64 * kStepThreads + ctx->rom_words + 256) * sizeof(uint32_t);
+        CUDA_TRY(ctx, cudaFuncSetAttribute(stm_step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        return ensure_scratch(ctx, 4096);
+    };
+    rc = body();
+    if (rc != STM_OK) { snprintf(g_create_error, sizeof g_create_error, "%s", ctx->err); stm_ctx_destroy(ctx); return rc; }
+    *out = ctx;
+    return STM_OK;
+}
+
+int stm_ctx_destroy(stm_ctx *ctx)
+{
+    if (!ctx) return STM_OK;
+    cudaSetDevice(ctx->device);
+    cudaFree(ctx->d_rom); cudaFree(ctx->d_lut); cudaFree(ctx->d_scratch); cudaFree(ctx->d_stepped);
+    for (int i = 0; i < 2; i++) {
+        cudaFree(ctx->pool_state[i]); cudaFree(ctx->pool_reward[i]); cudaFree(ctx->pool_done[i]);
+        cudaFree(ctx->pool_lives[i]); cudaFree(ctx->pool_stack[i]);
+    }
+    cudaFree(ctx->h_in_state); cudaFree(ctx->h_in_stack); cudaFree(ctx->h_out_stack);
+    cudaFree(ctx->h_out_reward); cudaFree(ctx->h_out_done); cudaFree(ctx->h_out_lives);
+    delete ctx;
+    return STM_OK;
+}
+
+int stm_set_scratch_envs(stm_ctx *ctx, int n_envs)
+{
+    if (!ctx || n_envs < 1) return fail(ctx, STM_ERR_ARG, "stm_set_scratch_envs: bad argument");
+    CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    return ensure_scratch(ctx, n_envs);
+}
+
+int stm_reset_states(stm_ctx *ctx, uint8_t *states, float *rewards, uint8_t *done, int32_t *lives, int n, void *stream)
+{
+    if (!ctx || !states || n < 0) return fail(ctx, STM_ERR_ARG, "stm_reset_states: bad argument");
+    if (n == 0) return STM_OK;
+    stm_reset_kernel<<<(n + 127) / 128, 128, 0, (cudaStream_t)stream>>>(states, rewards, done, lives, n, ctx->reset_pc, 0);
+    ctx->launches++;
+    CUDA_TRY(ctx, cudaGetLastError());
+    return STM_OK;
+}
+
+int stm_expand(stm_ctx *ctx, const uint8_t *src_states, const float *src_rewards, const uint8_t *src_done,
+               const int32_t *src_lives, uint8_t *dst_states, float *dst_rewards, uint8_t *dst_done,
+               int32_t *dst_lives, int n_src, int fanout, void *stream)
+{
+    if (!ctx || !src_states || !dst_states || n_src < 0 || fanout < 1) return fail(ctx, STM_ERR_ARG, "stm_expand: bad argument");
+    bool all = src_rewards && src_done && src_lives && dst_rewards && dst_done && dst_lives;
+    bool none = !src_rewards && !src_done && !src_lives && !dst_rewards && !dst_done && !dst_lives;
+    if (!all && !none) return fail(ctx, STM_ERR_ARG, "stm_expand: rewards/done/lives must be all given or all NULL");
+    if (((uintptr_t)src_states | (uintptr_t)dst_states) & 15) return fail(ctx, STM_ERR_ARG, "stm_expand: state pointers must be 16-byte aligned");
+    if (n_src == 0) return STM_OK;
+    return launch_clone(ctx, src_states, src_rewards, src_done, src_lives, dst_states, dst_rewards, dst_done, dst_lives,
+                        n_src, fanout, (cudaStream_t)stream);
+}
+
+int stm_step(stm_ctx *ctx, uint8_t *states, const uint8_t *actions, int n, int frameskip, int episodic_life,
+             float weight, float *rewards, uint8_t *done, int32_t *lives, int render, void *stream)
+{
+    if (!ctx || !states || !rewards || !done || !lives || n < 0 || frameskip < 1)
+        return fail(ctx, STM_ERR_ARG, "stm_step: bad argument");
+    if ((uintptr_t)states & 15) return fail(ctx, STM_ERR_ARG, "stm_step: states must be 16-byte aligned");
+    if (render && n > ctx->scratch_envs)
+        return fail(ctx, STM_ERR_ARG, "stm_step: n=%d exceeds the native-frame scratch (%d envs); call stm_set_scratch_envs", n, ctx->scratch_envs);
+    if (n == 0) return STM_OK;
+    return launch_step(ctx, states, actions, n, frameskip, episodic_life, weight, rewards, done, lives, render, (cudaStream_t)stream);
+}
+
+int stm_frames(stm_ctx *ctx, const uint8_t *parent_stacks, uint8_t *child_stacks, int n, int fanout, void *stream)
+{
+    if (!ctx || !parent_stacks || !child_stacks || n < 0 || fanout < 1) return fail(ctx, STM_ERR_ARG, "stm_frames: bad argument");
+    if (n > ctx->scratch_envs) return fail(ctx, STM_ERR_ARG, "stm_frames: n exceeds the native-frame scratch");
+    if (ctx->last_render_frames == 0) return fail(ctx, STM_ERR_ARG, "stm_frames: no rendered stm_step precedes this call");
+    if (((uintptr_t)parent_stacks | (uintptr_t)child_stacks) & 3) return fail(ctx, STM_ERR_ARG, "stm_frames: stacks must be 4-byte aligned");
+    if (n == 0) return STM_OK;
+    return launch_frames(ctx, parent_stacks, child_stacks, n, fanout, (cudaStream_t)stream);
+}
+
+int stm_bfs(stm_ctx *ctx, const uint8_t *root_states, const uint8_t *root_stacks, int n_roots, int depth,
+            float gamma, int frameskip, int episodic_life, int clip_reward, uint8_t *leaf_stacks,
+            float *leaf_rewards, uint8_t *leaf_done, int32_t *leaf_lives, uint8_t *leaf_states, void *stream)
+{
+    if (!ctx || !root_states || !root_stacks || !leaf_stacks || !leaf_rewards || n_roots < 1 || depth < 1 || frameskip < 1)
+        return fail(ctx, STM_ERR_ARG, "stm_bfs: bad argument");
+    cudaStream_t st = (cudaStream_t)stream;
+    const int A = ctx->desc.n_actions;
+    // level sizes
+    size_t n_level[16];
+    if (depth > 15) return fail(ctx, STM_ERR_ARG, "stm_bfs: depth %d too large", depth);
+    n_level[0] = (size_t)n_roots;
+    for (int k = 1; k <= depth; k++) {
+        n_level[k] = n_level[k - 1] * (size_t)A;
+        if (n_level[k] > 0x7FFFFFFFull) return fail(ctx, STM_ERR_ARG, "stm_bfs: %d roots x %d^%d leaves overflow int32", n_roots, A, depth);
+    }
+    CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    // pools: level k lives in pool k&1.  States/rewards/done/lives of EVERY level (the last one too:
+    // leaf_states/done/lives are optional outputs) go through the pools; stacks of the last level are
+    // written straight into leaf_stacks.
+    size_t need[2] = {0, 0}, need_stack[2] = {0, 0};
+    for (int k = 0; k <= depth; k++) {
+        if (n_level[k] > need[k & 1]) need[k & 1] = n_level[k];
+        if (k >= 1 && k < depth && n_level[k] > need_stack[k & 1]) need_stack[k & 1] = n_level[k];
+    }
+    int rc;
+    for (int w = 0; w < 2; w++) if ((rc = ensure_pool(ctx, w, need[w], need_stack[w]))) return rc;
+    int chunk = ctx->scratch_envs;
+
+    // level 0 = the roots
+    CUDA_TRY(ctx, cudaMemcpyAsync(ctx->pool_state[0], root_states, n_level[0] * STM_STATE_BYTES, cudaMemcpyDeviceToDevice, st));
+    stm_root_init_kernel<<<(n_roots + 127) / 128, 128, 0, st>>>(ctx->pool_state[0], ctx->pool_reward[0], ctx->pool_done[0],
+                                                               ctx->pool_lives[0], n_roots, ctx->gp);
+    ctx->launches++;
+    for (int k = 0; k < depth; k++) {
+        int cur = k & 1, nxt = cur ^ 1;
+        size_t n_src = n_level[k], n_dst = n_level[k + 1];
+        if ((rc = launch_clone(ctx, ctx->pool_state[cur], ctx->pool_reward[cur], ctx->pool_done[cur], ctx->pool_lives[cur],
+                               ctx->pool_state[nxt], ctx->pool_reward[nxt], ctx->pool_done[nxt], ctx->pool_lives[nxt],
+                               (int)n_src, A, st))) return rc;
+        float weight = (float)pow((double)gamma, (double)k);
+        const uint8_t *pstack = k == 0 ? root_stacks : ctx->pool_stack[cur];
+        uint8_t *cstack = k == depth - 1 ? leaf_stacks : ctx->pool_stack[nxt];
+        // chunks are multiples of the tile size and of A, so "action = env % A" holds inside a chunk
+        size_t step = (size_t)chunk - (size_t)chunk % (size_t)(kTileEnvs * A);
+        if (step == 0) return fail(ctx, STM_ERR_ARG, "stm_bfs: scratch too small for %d actions", A);
+        for (size_t off = 0; off < n_dst; off += step) {
+            int cn = (int)((n_dst - off) < step ? (n_dst - off) : step);
+            if ((rc = launch_step(ctx, ctx->pool_state[nxt] + off * STM_STATE_BYTES, nullptr, cn, frameskip, episodic_life, weight,
+                                  ctx->pool_reward[nxt] + off, ctx->pool_done[nxt] + off, ctx->pool_lives[nxt] + off, 1, st))) return rc;
+            // parent of env (off+i) is (off+i)/A = off/A + i/A because off % A == 0
+            if ((rc = launch_frames(ctx, pstack + (off / A) * STM_STACK * STM_OBS_BYTES, cstack + off * STM_STACK * STM_OBS_BYTES, cn, A, st))) return rc;
+        }
+    }
+    int fin = depth & 1;
+    size_t L = n_level[depth];
+    stm_finalize_kernel<<<(unsigned)((L + 255) / 256), 256, 0, st>>>(ctx->pool_reward[fin], leaf_rewards, (int)L, clip_reward);
+    ctx->launches++;
+    if (leaf_done) CUDA_TRY(ctx, cudaMemcpyAsync(leaf_done, ctx->pool_done[fin], L, cudaMemcpyDeviceToDevice, st));
+    if (leaf_lives) CUDA_TRY(ctx, cudaMemcpyAsync(leaf_lives, ctx->pool_lives[fin], L * sizeof(int32_t), cudaMemcpyDeviceToDevice, st));
+    if (leaf_states) CUDA_TRY(ctx, cudaMemcpyAsync(leaf_states, ctx->pool_state[fin], L * STM_STATE_BYTES, cudaMemcpyDeviceToDevice, st));
+    CUDA_TRY(ctx, cudaGetLastError());
+    return STM_OK;
+}
+
+int stm_bfs_host(stm_ctx *ctx, const uint8_t *root_states, const uint8_t *root_stacks, int n_roots, int depth,
+                 float gamma, int frameskip, int episodic_life, int clip_reward, uint8_t *leaf_stacks,
+                 float *leaf_rewards, uint8_t *leaf_done, int32_t *leaf_lives, void *stream)
+{
+    if (!ctx || !root_states || !root_stacks || !leaf_stacks || !leaf_rewards || n_roots < 1 || depth < 1)
+        return fail(ctx, STM_ERR_ARG, "stm_bfs_host: bad argument");
+    cudaStream_t st = (cudaStream_t)stream;
+    CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    size_t L = (size_t)n_roots;
+    for (int k = 0; k < depth; k++) L *= (size_t)ctx->desc.n_actions;
+    const size_t SB = (size_t)STM_STACK * STM_OBS_BYTES;
+    if ((size_t)n_roots > ctx->h_roots) {
+        cudaFree(ctx->h_in_state); cudaFree(ctx->h_in_stack); ctx->h_in_state = ctx->h_in_stack = nullptr; ctx->h_roots = 0;
+        CUDA_TRY(ctx, cudaMalloc(&ctx->h_in_state, (size_t)n_roots * STM_STATE_BYTES));
+        CUDA_TRY(ctx, cudaMalloc(&ctx->h_in_stack, (size_t)n_roots * SB));
+        ctx->h_roots = (size_t)n_roots;
+    }
+    if (L > ctx->h_leaves) {
+        cudaFree(ctx->h_out_stack); cudaFree(ctx->h_out_reward); cudaFree(ctx->h_out_done); cudaFree(ctx->h_out_lives);
+        ctx->h_out_stack = nullptr; ctx->h_out_reward = nullptr; ctx->h_out_done = nullptr; ctx->h_out_lives = nullptr; ctx->h_leaves = 0;
+        CUDA_TRY(ctx, cudaMalloc(&ctx->h_out_stack, L * SB));
+        CUDA_TRY(ctx, cudaMalloc(&ctx->h_out_reward, L * sizeof(float)));
+        CUDA_TRY(ctx, cudaMalloc(&ctx->h_out_done, L));
+        CUDA_TRY(ctx, cudaMalloc(&ctx->h_out_lives, L * sizeof(int32_t)));
+        ctx->h_leaves = L;
+    }
+    CUDA_TRY(ctx, cudaMemcpyAsync(ctx->h_in_state, root_states, (size_t)n_roots * STM_STATE_BYTES, cudaMemcpyHostToDevice, st));
+    CUDA_TRY(ctx, cudaMemcpyAsync(ctx->h_in_stack, root_stacks, (size_t)n_roots * SB, cudaMemcpyHostToDevice, st));
+    int rc = stm_bfs(ctx, ctx->h_in_state, ctx->h_in_stack, n_roots, depth, gamma, frameskip, episodic_life, clip_reward,
+                     ctx->h_out_stack, ctx->h_out_reward, ctx->h_out_done, ctx->h_out_lives, nullptr, stream);
+    if (rc) return rc;
+    CUDA_TRY(ctx, cudaMemcpyAsync(leaf_stacks, ctx->h_out_stack, L * SB, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(ctx, cudaMemcpyAsync(leaf_rewards, ctx->h_out_reward, L * sizeof(float), cudaMemcpyDeviceToHost, st));
+    if (leaf_done) CUDA_TRY(ctx, cudaMemcpyAsync(leaf_done, ctx->h_out_done, L, cudaMemcpyDeviceToHost, st));
+    if (leaf_lives) CUDA_TRY(ctx, cudaMemcpyAsync(leaf_lives, ctx->h_out_lives, L * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(ctx, cudaStreamSynchronize(st));
+    return STM_OK;
+}
+
+} // extern "C"

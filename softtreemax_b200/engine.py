@@ -1,0 +1,128 @@
+"""Engine: the Python face of one stm_ctx (one per GPU).  PyTorch is used for device memory and
+streams only; every computation below is a call into libstm_b200.so (include/stm_b200.h).
+
+Tensor conventions (all on cuda:<device>, contiguous):
+    states  (n, 256) uint8      rewards (n,) float32     done (n,) uint8     lives (n,) int32
+    stacks  (n, 4, 84, 84) uint8
+"""
+import ctypes as C
+
+import numpy as np
+import torch
+
+from . import games
+from ._lib import STATE_BYTES, StmError, check, lib
+
+
+def _ptr(t):
+    if t is None:
+        return None
+    if isinstance(t, np.ndarray):
+        assert t.flags["C_CONTIGUOUS"]
+        return t.ctypes.data_as(C.c_void_p)
+    assert t.is_contiguous(), "stm: tensors must be contiguous"
+    return C.c_void_p(t.data_ptr())
+
+
+class Engine:
+    def __init__(self, game, device=0, scratch_envs=None):
+        if not torch.cuda.is_available():
+            raise StmError("softtreemax_b200 needs a CUDA device (sm_100a); there is no CPU fallback")
+        self.desc, self.rom, self.info = games.load(game)
+        self.device = torch.device("cuda", device)
+        self._h = C.c_void_p()
+        romb = (C.c_uint8 * len(self.rom)).from_buffer_copy(self.rom)
+        check(lib().stm_ctx_create(C.byref(self._h), C.byref(self.desc), romb, device))
+        self.n_actions = lib().stm_num_actions(self._h)
+        self.action_codes = list(self.desc.actions[:self.n_actions])
+        if scratch_envs:
+            self.set_scratch_envs(scratch_envs)
+
+    def close(self):
+        if getattr(self, "_h", None):
+            lib().stm_ctx_destroy(self._h)
+            self._h = None
+
+    __del__ = close
+
+    # ------------------------------------------------------------------------------------
+    def _stream(self):
+        return C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
+
+    @property
+    def launch_count(self):
+        return lib().stm_launch_count(self._h)
+
+    @property
+    def max_step_envs(self):
+        return lib().stm_max_step_envs(self._h)
+
+    def set_scratch_envs(self, n):
+        check(lib().stm_set_scratch_envs(self._h, int(n)), self._h)
+
+    def alloc(self, n):
+        d = self.device
+        return (torch.empty((n, STATE_BYTES), dtype=torch.uint8, device=d),
+                torch.empty((n,), dtype=torch.float32, device=d),
+                torch.empty((n,), dtype=torch.uint8, device=d),
+                torch.empty((n,), dtype=torch.int32, device=d))
+
+    def reset_states(self, n):
+        states, rewards, done, lives = self.alloc(n)
+        check(lib().stm_reset_states(self._h, _ptr(states), _ptr(rewards), _ptr(done), _ptr(lives), n,
+                                     self._stream()), self._h)
+        return states, rewards, done, lives
+
+    def expand(self, states, rewards, done, lives, fanout):
+        n = states.shape[0]
+        out = self.alloc(n * fanout)
+        check(lib().stm_expand(self._h, _ptr(states), _ptr(rewards), _ptr(done), _ptr(lives),
+                               _ptr(out[0]), _ptr(out[1]), _ptr(out[2]), _ptr(out[3]), n, fanout,
+                               self._stream()), self._h)
+        return out
+
+    def step(self, states, rewards, done, lives, actions=None, frameskip=4, episodic_life=True,
+             weight=1.0, render=True):
+        n = states.shape[0]
+        if actions is not None:
+            actions = actions.to(torch.uint8).contiguous()
+        check(lib().stm_step(self._h, _ptr(states), _ptr(actions), n, frameskip, int(episodic_life),
+                             float(weight), _ptr(rewards), _ptr(done), _ptr(lives), int(render),
+                             self._stream()), self._h)
+
+    def frames(self, parent_stacks, n, fanout=1, out=None):
+        if out is None:
+            out = torch.empty((n, 4, 84, 84), dtype=torch.uint8, device=self.device)
+        check(lib().stm_frames(self._h, _ptr(parent_stacks), _ptr(out), n, fanout, self._stream()), self._h)
+        return out
+
+    def bfs(self, root_states, root_stacks, depth, gamma=0.99, frameskip=4, episodic_life=True,
+            clip_reward=True, want_states=False, out=None):
+        R = root_states.shape[0]
+        L = R * self.n_actions ** depth
+        d = self.device
+        if out is None:
+            out = dict(stacks=torch.empty((L, 4, 84, 84), dtype=torch.uint8, device=d),
+                       rewards=torch.empty((L,), dtype=torch.float32, device=d),
+                       done=torch.empty((L,), dtype=torch.uint8, device=d),
+                       lives=torch.empty((L,), dtype=torch.int32, device=d),
+                       states=torch.empty((L, STATE_BYTES), dtype=torch.uint8, device=d) if want_states else None)
+        check(lib().stm_bfs(self._h, _ptr(root_states), _ptr(root_stacks), R, depth, float(gamma), frameskip,
+                            int(episodic_life), int(clip_reward), _ptr(out["stacks"]), _ptr(out["rewards"]),
+                            _ptr(out["done"]), _ptr(out["lives"]), _ptr(out.get("states")), self._stream()),
+              self._h)
+        return out
+
+    def bfs_host(self, root_states, root_stacks, depth, gamma=0.99, frameskip=4, episodic_life=True,
+                 clip_reward=True, out=None):
+        """Host-buffer entry point (numpy arrays or pinned CPU tensors in, same out)."""
+        R = root_states.shape[0]
+        L = R * self.n_actions ** depth
+        if out is None:
+            out = dict(stacks=np.empty((L, 4, 84, 84), np.uint8), rewards=np.empty((L,), np.float32),
+                       done=np.empty((L,), np.uint8), lives=np.empty((L,), np.int32))
+        check(lib().stm_bfs_host(self._h, _ptr(root_states), _ptr(root_stacks), R, depth, float(gamma),
+                                 frameskip, int(episodic_life), int(clip_reward), _ptr(out["stacks"]),
+                                 _ptr(out["rewards"]), _ptr(out["done"]), _ptr(out["lives"]), self._stream()),
+              self._h)
+        return out

@@ -1,0 +1,257 @@
+"""GPU parity tests proper: the CUDA path, called through the C ABI (softtreemax_b200.engine is a
+thin ctypes wrapper over include/stm_b200.h), against the CPU oracle on identical seeded inputs.
+Bar: BIT-EXACT (integer / byte / index work; the only float is the reward accumulator, whose
+multiply and add are separately rounded on both sides, so it is compared exactly too)."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+from conftest import random_rom_game
+
+pytestmark = pytest.mark.gpu
+
+torch = pytest.importorskip("torch")
+
+
+@pytest.fixture(scope="module")
+def engines():
+    from softtreemax_b200.engine import Engine
+    cache = {}
+
+    def get(name):
+        if name not in cache:
+            cache[name] = Engine(name)
+        return cache[name]
+    yield get
+    for e in cache.values():
+        e.close()
+
+
+def dev(a, eng):
+    return torch.from_numpy(np.ascontiguousarray(a)).to(eng.device)
+
+
+def oracle_level(orc, g, states, rewards, done, lives, stacks, A, weight, frameskip=4, episodic_life=True):
+    """One tree level on the CPU: clone xA, agent step with action i % A, new stacks."""
+    n = states.shape[0] * A
+    st = np.repeat(states, A, axis=0).copy()
+    rw = np.repeat(rewards, A).copy()
+    dn = np.repeat(done, A).copy()
+    lv = np.repeat(lives, A).copy()
+    ob = np.zeros((n, 4, 84, 84), np.uint8)
+    for i in range(n):
+        d1, r1, l1 = dn[i:i + 1], rw[i:i + 1], lv[i:i + 1]
+        obs, *_ = g.agent_step(st[i], i % A, frameskip=frameskip, episodic_life=episodic_life, weight=weight,
+                               done=d1, reward=r1, lives=l1)
+        ob[i, :3] = stacks[i // A, 1:]
+        ob[i, 3] = obs
+    return st, rw, dn, lv, ob
+
+
+@pytest.mark.parametrize("n,fanout", [(1, 4), (33, 3), (257, 4), (1000, 6), (64, 1)])
+def test_k1_clone_bitexact(engines, n, fanout):
+    eng = engines("synth_breakout")
+    rng = np.random.default_rng(n)
+    st = rng.integers(0, 256, (n, 256), dtype=np.uint8)
+    rw = rng.standard_normal(n).astype(np.float32)
+    dn = rng.integers(0, 2, n).astype(np.uint8)
+    lv = rng.integers(0, 9, n).astype(np.int32)
+    out = eng.expand(dev(st, eng), dev(rw, eng), dev(dn, eng), dev(lv, eng), fanout)
+    torch.cuda.synchronize()
+    idx = np.arange(n * fanout) // fanout                      # child i <- parent i // fanout (cule_bfs.py:90)
+    assert np.array_equal(out[0].cpu().numpy(), st[idx])
+    assert np.array_equal(out[1].cpu().numpy(), rw[idx])
+    assert np.array_equal(out[2].cpu().numpy(), dn[idx])
+    assert np.array_equal(out[3].cpu().numpy(), lv[idx])
+
+
+@pytest.mark.parametrize("name", ["synth_breakout", "synth_pong", "synth_torture"])
+@pytest.mark.parametrize("frameskip", [4, 1, 2])
+def test_k2_k3_one_level_bitexact(orc, engines, name, frameskip):
+    g = orc.Game(name)
+    eng = engines(name)
+    A = g.n_actions
+    R = 37 if A <= 6 else 9                                     # ragged on purpose (not a multiple of 32)
+    roots, stacks = orc.make_roots(g, R, seed=5, base_steps=30, spread=23)
+    rew0 = np.zeros(R, np.float32)
+    done0 = np.zeros(R, np.uint8)
+    done0[3] = 1                                                # a frozen env (and its A children)
+    lives0 = np.array([g.lives(r) for r in roots], np.int32)
+    w = np.float32(0.99) ** 2
+    st, rw, dn, lv, ob = oracle_level(orc, g, roots, rew0, done0, lives0, stacks, A, float(w), frameskip)
+    d = eng.expand(dev(roots, eng), dev(rew0, eng), dev(done0, eng), dev(lives0, eng), A)
+    eng.step(*d, frameskip=frameskip, weight=float(w), render=True)
+    obs = eng.frames(dev(stacks, eng), R * A, fanout=A)
+    torch.cuda.synchronize()
+    assert np.array_equal(d[0].cpu().numpy(), st), "state blobs (RAM + registers)"
+    assert np.array_equal(d[1].cpu().numpy(), rw), "rewards"
+    assert np.array_equal(d[2].cpu().numpy(), dn), "done"
+    assert np.array_equal(d[3].cpu().numpy(), lv), "lives"
+    assert np.array_equal(obs.cpu().numpy(), ob), "observation stacks"
+    assert ob[3 * A:4 * A, 3].max() == 0                        # frozen envs produce an all-zero new frame
+
+
+@pytest.mark.parametrize("seed", range(9))
+def test_random_rom_step_bitexact(orc, seed):
+    """Cartridges of random bytes: every opcode incl. undocumented ones, wild TIA/RIOT traffic,
+    frames that end on the scanline cap, F8 bank switching."""
+    from softtreemax_b200.engine import Engine
+    from softtreemax_b200 import games as pg
+    d, rom = random_rom_game(orc, seed)
+    g = orc.Game(desc=orc.make_desc(d, len(rom)), rom=rom)
+    eng = Engine.__new__(Engine)
+    # build an Engine around an ad-hoc descriptor (no games.json entry)
+    from softtreemax_b200._lib import lib, check
+    eng.desc, eng.rom, eng.info = pg.make_desc(d, len(rom)), rom, d
+    eng.device = torch.device("cuda", 0)
+    eng._h = C.c_void_p()
+    romb = (C.c_uint8 * len(rom)).from_buffer_copy(rom)
+    check(lib().stm_ctx_create(C.byref(eng._h), C.byref(eng.desc), romb, 0))
+    eng.n_actions = lib().stm_num_actions(eng._h)
+    try:
+        A = g.n_actions
+        n = 70
+        s0 = g.reset()
+        states = np.repeat(s0[None], n, axis=0)
+        rng = np.random.default_rng(seed)
+        states[:, 0:128] = rng.integers(0, 256, (n, 128))       # random RAM so that envs diverge
+        rw = np.zeros(n, np.float32)
+        dn = np.zeros(n, np.uint8)
+        lv = np.array([g.lives(s) for s in states], np.int32)
+        acts = rng.integers(0, A, n).astype(np.uint8)
+        ds, dr, dd, dl = dev(states, eng), dev(rw, eng), dev(dn, eng), dev(lv, eng)
+        stacks = np.zeros((n, 4, 84, 84), np.uint8)
+        for step in range(3):
+            eng.step(ds, dr, dd, dl, actions=dev(acts, eng), frameskip=2, weight=0.5, render=True)
+            obs = eng.frames(dev(stacks, eng), n, fanout=1)
+            new = np.zeros_like(stacks)
+            for i in range(n):
+                o, *_ = g.agent_step(states[i], int(acts[i]), frameskip=2, weight=0.5, done=dn[i:i + 1],
+                                     reward=rw[i:i + 1], lives=lv[i:i + 1])
+                new[i, :3] = stacks[i, 1:]
+                new[i, 3] = o
+            stacks = new
+            torch.cuda.synchronize()
+            assert np.array_equal(ds.cpu().numpy(), states), f"state, step {step}"
+            assert np.array_equal(obs.cpu().numpy(), stacks), f"obs, step {step}"
+            assert np.array_equal(dr.cpu().numpy(), rw) and np.array_equal(dd.cpu().numpy(), dn)
+            assert np.array_equal(dl.cpu().numpy(), lv)
+    finally:
+        eng.close()
+
+
+@pytest.mark.parametrize("name,R,depth", [("synth_breakout", 5, 1), ("synth_breakout", 3, 2), ("synth_breakout", 2, 3),
+                                          ("synth_pong", 2, 2), ("synth_torture", 1, 1), ("synth_torture", 3, 2)])
+def test_bfs_matches_oracle(orc, engines, name, R, depth):
+    g = orc.Game(name)
+    eng = engines(name)
+    roots, stacks = orc.make_roots(g, R, seed=9, base_steps=40, spread=31)
+    want = g.bfs(roots, stacks, depth, gamma=0.99, clip_reward=True)
+    got = eng.bfs(dev(roots, eng), dev(stacks, eng), depth, gamma=0.99, clip_reward=True, want_states=True)
+    torch.cuda.synchronize()
+    L = R * g.n_actions ** depth
+    assert np.array_equal(got["stacks"].cpu().numpy(), want[0].reshape(L, 4, 84, 84))
+    assert np.array_equal(got["rewards"].cpu().numpy(), want[1].reshape(L))
+    assert np.array_equal(got["done"].cpu().numpy(), want[2].reshape(L))
+    assert np.array_equal(got["lives"].cpu().numpy(), want[3].reshape(L))
+    assert np.array_equal(got["states"].cpu().numpy(), want[4].reshape(L, 256))
+
+
+def test_bfs_unclipped_rewards_and_chunking(orc, engines):
+    """clip_reward=False returns the raw discounted sums; a scratch smaller than a level forces the
+    level to be processed in several K2/K3 chunks — results must not change."""
+    from softtreemax_b200.engine import Engine
+    g = orc.Game("synth_torture")
+    roots, stacks = orc.make_roots(g, 2, seed=2, base_steps=25, spread=3)
+    want = g.bfs(roots, stacks, 2, gamma=0.9, clip_reward=False)
+    eng = Engine("synth_torture")                           # default scratch: 4096 envs
+    try:
+        got = eng.bfs(dev(roots, eng), dev(stacks, eng), 2, gamma=0.9, clip_reward=False)
+        torch.cuda.synchronize()
+        assert np.array_equal(got["rewards"].cpu().numpy(), want[1].reshape(-1))
+        assert np.abs(want[1]).max() > 1.0                  # the case really has non-trivial rewards
+        assert np.array_equal(got["stacks"].cpu().numpy(), want[0].reshape(-1, 4, 84, 84))
+    finally:
+        eng.close()
+    g = orc.Game("synth_breakout")
+    roots, stacks = orc.make_roots(g, 300, seed=4)
+    eng = engines("synth_breakout")
+    a = eng.bfs(dev(roots, eng), dev(stacks, eng), 2)       # 4800 leaves > 4096-env scratch => 2 chunks
+    eng.set_scratch_envs(8192)
+    b = eng.bfs(dev(roots, eng), dev(stacks, eng), 2)
+    torch.cuda.synchronize()
+    for k in ("stacks", "rewards", "done", "lives"):
+        assert torch.equal(a[k], b[k]), k
+    want = g.bfs(roots[:40], stacks[:40], 2)
+    assert np.array_equal(a["stacks"][:640].cpu().numpy(), want[0].reshape(-1, 4, 84, 84))
+
+
+def test_bfs_host_entry_point(orc, engines):
+    g = orc.Game("synth_breakout")
+    eng = engines("synth_breakout")
+    roots, stacks = orc.make_roots(g, 4, seed=1)
+    want = g.bfs(roots, stacks, 2)
+    got = eng.bfs_host(roots, stacks, 2)
+    assert np.array_equal(got["stacks"], want[0].reshape(-1, 4, 84, 84))
+    assert np.array_equal(got["rewards"], want[1].reshape(-1))
+    assert np.array_equal(got["done"], want[2].reshape(-1))
+    assert np.array_equal(got["lives"], want[3].reshape(-1))
+
+
+def test_full_size_properties(orc, engines):
+    """BASELINE size (Breakout depth 3, 1024 roots = 65 536 leaves): too big for the oracle in a test,
+    so check size-independent properties: determinism, root-permutation equivariance, the stack-shift
+    identity (leaf frames 0..2 are ancestors' frames), and oracle agreement on a sampled sub-tree."""
+    g = orc.Game("synth_breakout")
+    eng = engines("synth_breakout")
+    R, depth, A = 1024, 3, 4
+    eng.set_scratch_envs(65536)
+    roots, stacks = orc.make_roots(g, R, seed=1234)
+    dr, ds = dev(roots, eng), dev(stacks, eng)
+    a = eng.bfs(dr, ds, depth, want_states=True)
+    b = eng.bfs(dr, ds, depth, want_states=True)
+    torch.cuda.synchronize()
+    for k in a:
+        assert torch.equal(a[k], b[k]), f"non-deterministic {k}"
+    perm = torch.randperm(R, generator=torch.Generator().manual_seed(0)).to(eng.device)
+    c = eng.bfs(dr[perm].contiguous(), ds[perm].contiguous(), depth, want_states=True)
+    L = A ** depth
+    for k in a:
+        x = a[k].view(R, L, *a[k].shape[1:])[perm]
+        assert torch.equal(x.reshape(c[k].shape), c[k]), f"not equivariant under root permutation: {k}"
+    # stack-shift identity: frame 0 of every leaf = frame 3 of the root stack (depth 3 shifts three times)
+    leaf = a["stacks"].view(R, L, 4, 84, 84)
+    assert torch.equal(leaf[:, :, 0], ds[:, 3].unsqueeze(1).expand(R, L, 84, 84))
+    # siblings share frames 0..2
+    sib = leaf.view(R, L // A, A, 4, 84, 84)
+    assert torch.equal(sib[:, :, 0, :3], sib[:, :, 3, :3])
+    # oracle on a sample of roots
+    pick = [0, 517, 1023]
+    want = g.bfs(roots[pick], stacks[pick], depth)
+    for j, r in enumerate(pick):
+        assert np.array_equal(leaf[r].cpu().numpy(), want[0][j])
+        assert np.array_equal(a["rewards"].view(R, L)[r].cpu().numpy(), want[1][j])
+        assert np.array_equal(a["states"].view(R, L, 256)[r].cpu().numpy(), want[4][j])
+
+
+def test_argument_errors(engines):
+    from softtreemax_b200._lib import StmError
+    eng = engines("synth_breakout")
+    st, rw, dn, lv = eng.reset_states(8)
+    with pytest.raises(StmError):
+        eng.step(st, rw, dn, lv, frameskip=0)
+    with pytest.raises(StmError):
+        eng.set_scratch_envs(0)
+    big = eng.reset_states(eng.max_step_envs + 32)
+    with pytest.raises(StmError, match="scratch"):
+        eng.step(*big, render=True)
+
+
+def test_reset_states_match_oracle(orc, engines):
+    for name in ("synth_breakout", "synth_pong"):
+        eng = engines(name)
+        st, *_ = eng.reset_states(3)
+        torch.cuda.synchronize()
+        want = orc.Game(name).reset()
+        assert np.array_equal(st.cpu().numpy(), np.repeat(want[None], 3, 0))

@@ -1,0 +1,111 @@
+"""CPU-side cross-check of the CUDA emulator core against the oracle.
+
+softtreemax_b200/csrc/emu_core.cuh is written to compile for the host as well (plain-array memory
+policy, tests/tools/host_core.cpp).  Its structure differs from the oracle's on purpose (table
+decode by mode/class, 32-pixel mask words vs. one switch per opcode, per-pixel TIA), so agreement
+here is a real check — and it runs in the GPU-less container, before any GPU time is spent.
+The GPU run of the same core is checked in test_gpu_parity.py.
+"""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+from conftest import random_rom_game
+
+
+def _p(a):
+    return a.ctypes.data_as(C.c_void_p) if a is not None else None
+
+
+def _bind(H, orc):
+    H.hc_frame.argtypes = [C.POINTER(orc.GameDesc), C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_int,
+                           C.c_float, C.c_void_p, C.c_void_p, C.c_void_p]
+    H.hc_exec_one.argtypes = [C.POINTER(orc.GameDesc), C.c_void_p, C.c_void_p]
+    return H
+
+
+def run_pair(orc, H, game, nframes, seed, render_every=1):
+    rng = np.random.default_rng(seed)
+    so = game.reset()
+    sh = so.copy()
+    rom = np.frombuffer(game.rom, np.uint8).copy()
+    fbo, fbh = np.zeros(33600, np.uint8), np.zeros(33600, np.uint8)
+    do, dh = np.zeros(1, np.uint8), np.zeros(1, np.uint8)
+    ro, rh = np.zeros(1, np.float32), np.zeros(1, np.float32)
+    lo, lh = np.zeros(1, np.int32), np.zeros(1, np.int32)
+    for f in range(nframes):
+        a = int(game.desc.actions[rng.integers(0, game.n_actions)])
+        rend = (f % render_every) == 0
+        game.frame(so, a, fbo if rend else None)
+        orc.lib().orc_get_data(game.h, _p(so), 1, C.c_float(0.97), _p(do), _p(ro), _p(lo))
+        H.hc_frame(C.byref(game.desc), _p(rom), _p(sh), a, _p(fbh) if rend else None, 1, C.c_float(0.97),
+                   _p(dh), _p(rh), _p(lh))
+        assert np.array_equal(so, sh), f"state differs at frame {f}: offsets {np.nonzero(so != sh)[0][:16]}"
+        if rend:
+            assert np.array_equal(fbo, fbh), f"native frame differs at frame {f}"
+        assert (do[0], ro[0], lo[0]) == (dh[0], rh[0], lh[0])
+
+
+@pytest.mark.parametrize("name", ["synth_breakout", "synth_pong", "synth_torture"])
+def test_games_match_oracle(orc, host_core, name):
+    run_pair(orc, _bind(host_core, orc), orc.Game(name), 240, seed=3)
+
+
+@pytest.mark.parametrize("seed", range(12))
+def test_random_roms_match_oracle(orc, host_core, seed):
+    d, rom = random_rom_game(orc, seed)
+    g = orc.Game(desc=orc.make_desc(d, len(rom)), rom=rom)
+    run_pair(orc, _bind(host_core, orc), g, 30, seed=seed, render_every=2)
+
+
+def test_every_opcode_single_step(orc, host_core):
+    """All 256 opcodes x random register/RAM/TIA state x random operands, one instruction each."""
+    H = _bind(host_core, orc)
+    rng = np.random.default_rng(5)
+    d = dict(bank_scheme=0, controller=0, actions=[0, 1, 11], score_addr=[255, 255, 0], score2_addr=[255] * 3,
+             lives_addr=255, lives_shift=0, lives_mask=255, term_addr=255, term_mask=0, term_value=0)
+    for op in range(256):
+        for trial in range(24):
+            rom = rng.integers(0, 256, size=4096, dtype=np.uint8)
+            org = int(rng.integers(0, 4090))
+            rom[org] = op
+            if trial % 3 == 0:                      # bias operands towards TIA / RIOT / RAM addresses
+                rom[org + 1] = rng.choice([0x02, 0x10, 0x1B, 0x2A, 0x80, 0x84, 0x96, 0x00, 0x06])
+                rom[org + 2] = rng.choice([0x00, 0x02, 0x01])
+            desc = orc.make_desc(d, 4096)
+            g = orc.Game(desc=desc, rom=rom.tobytes())
+            s = g.reset()
+            s[0:128] = rng.integers(0, 256, 128)
+            s[128], s[129] = (0xF000 + org) & 0xFF, (0xF000 + org) >> 8
+            s[130:135] = rng.integers(0, 256, 5)                      # A X Y SP P
+            s[134] |= 0x20
+            s[136] = rng.integers(0, 250)
+            s[138] = rng.integers(0, 76)
+            s[139] = 0
+            s[144:148] = np.frombuffer(np.int32(rng.integers(-300, 70000)).tobytes(), np.uint8)
+            s[148] = rng.choice([0, 3, 6, 10])
+            s[154] = rng.integers(0, 18)
+            s[162:167] = rng.integers(0, 160, 5)
+            s[168:200] = rng.integers(0, 256, 32)
+            s[168] &= 0xFD                                            # VSYNC off so a strobe can end the frame
+            s2 = s.copy()
+            g.exec_one(s)
+            H.hc_exec_one(C.byref(desc), _p(np.frombuffer(g.rom, np.uint8).copy()), _p(s2))
+            assert np.array_equal(s, s2), f"opcode {op:02X} trial {trial}: offsets {np.nonzero(s != s2)[0]}"
+
+
+def test_decode_table_matches_documented_matrix(host_core):
+    """Spot-check the generated decode table against textbook entries (mode, kind, cycles)."""
+    t = (C.c_uint32 * 256)()
+    host_core.hc_decode_table(t)
+    unpack = lambda v: (v & 15, (v >> 4) & 3, (v >> 6) & 15)
+    IMP, IMM, ZP, ZPX, ZPY, ABS, ABX, ABY, INX, INY, REL, IND, ACC = range(13)
+    N, R, W, M = range(4)
+    want = {0xA9: (IMM, R, 2), 0xAD: (ABS, R, 4), 0xBD: (ABX, R, 4), 0xB1: (INY, R, 5), 0x91: (INY, W, 6),
+            0x9D: (ABX, W, 5), 0xFE: (ABX, M, 7), 0xE6: (ZP, M, 5), 0x20: (ABS, N, 6), 0x60: (IMP, N, 6),
+            0x6C: (IND, N, 5), 0x4C: (ABS, N, 3), 0x00: (IMP, N, 7), 0x0A: (ACC, N, 2), 0x96: (ZPY, W, 4),
+            0xB6: (ZPY, R, 4), 0xBE: (ABY, R, 4), 0xD0: (REL, N, 2), 0x48: (IMP, N, 3), 0x68: (IMP, N, 4),
+            0xA7: (ZP, R, 3), 0xC3: (INX, M, 8), 0xEA: (IMP, N, 2), 0x24: (ZP, R, 3)}
+    for op, w in want.items():
+        assert unpack(t[op]) == w, hex(op)

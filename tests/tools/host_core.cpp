@@ -1,0 +1,69 @@
+// host_core.cpp — TEST AID.  Compiles softtreemax_b200/csrc/emu_core.cuh for the host with a
+// plain-array memory policy so that the CUDA emulator core can be diffed against the oracle in
+// this GPU-less container (tests/test_host_core.py).  Never loaded by the product package.
+#include <cstring>
+#include <cstdint>
+#include "../../softtreemax_b200/csrc/emu_core.cuh"
+
+namespace {
+struct HostMem {
+    uint8_t *blob; const uint8_t *rom; const uint32_t *lut; uint8_t *fb;
+    uint32_t ld8(uint32_t o) const { return blob[o]; }
+    void st8(uint32_t o, uint32_t v) { blob[o] = (uint8_t)v; }
+    uint32_t ld16(uint32_t o) const { return blob[o] | (blob[o + 1] << 8); }
+    void st16(uint32_t o, uint32_t v) { blob[o] = (uint8_t)v; blob[o + 1] = (uint8_t)(v >> 8); }
+    uint32_t ld32(uint32_t o) const { uint32_t v; memcpy(&v, blob + o, 4); return v; }
+    void st32(uint32_t o, uint32_t v) { memcpy(blob + o, &v, 4); }
+    uint32_t rom8(uint32_t i) const { return rom[i]; }
+    uint32_t rom32(uint32_t wi) const { uint32_t v; memcpy(&v, rom + 4 * wi, 4); return v; }
+    uint32_t opinfo(uint32_t op) const { return lut[op]; }
+    void px4(uint32_t row, uint32_t g, uint32_t w) { if (fb) memcpy(fb + row * 160 + 4 * g, &w, 4); }
+    void px1(uint32_t row, uint32_t x, uint32_t v) { if (fb) fb[row * 160 + x] = (uint8_t)v; }
+};
+uint32_t g_lut[256];
+bool g_lut_ok = false;
+}
+
+extern "C" {
+
+void hc_fill_params(stm::GameParams *gp, const stm_game_desc *d)
+{
+    memset(gp, 0, sizeof(*gp));
+    gp->rom_mask = d->bank_scheme == STM_BANK_F8 ? 0xFFF : d->rom_size - 1;
+    gp->bank_scheme = d->bank_scheme; gp->controller = d->controller; gp->n_actions = d->n_actions;
+    memcpy(gp->actions, d->actions, 18);
+    memcpy(gp->score_addr, d->score_addr, 3); memcpy(gp->score2_addr, d->score2_addr, 3);
+    gp->lives_addr = d->lives_addr; gp->lives_shift = d->lives_shift; gp->lives_mask = d->lives_mask;
+    gp->term_addr = d->term_addr; gp->term_mask = d->term_mask; gp->term_value = d->term_value;
+}
+
+void hc_decode_table(uint32_t *out) { stm::build_decode_table(out); }
+
+// one emulated frame + get_data, like the oracle's orc_frame + orc_get_data
+void hc_frame(const stm_game_desc *d, const uint8_t *rom, uint8_t *blob, int ale_action, uint8_t *fb,
+              int episodic_life, float weight, uint8_t *done, float *reward, int32_t *lives)
+{
+    if (!g_lut_ok) { stm::build_decode_table(g_lut); g_lut_ok = true; }
+    stm::GameParams gp; hc_fill_params(&gp, d);
+    HostMem m{blob, rom, g_lut, fb};
+    stm::Emu<HostMem> e(m, gp);
+    e.load();
+    e.run_frame((uint32_t)ale_action, fb != nullptr);
+    uint32_t dn = *done; int lv = *lives;
+    int r = e.get_data(episodic_life != 0, dn, lv);
+    volatile float wr = weight * (float)r;
+    *reward = *reward + wr;
+    *done = (uint8_t)dn; *lives = lv;
+    e.store();
+}
+
+void hc_exec_one(const stm_game_desc *d, const uint8_t *rom, uint8_t *blob)
+{
+    if (!g_lut_ok) { stm::build_decode_table(g_lut); g_lut_ok = true; }
+    stm::GameParams gp; hc_fill_params(&gp, d);
+    HostMem m{blob, rom, g_lut, nullptr};
+    stm::Emu<HostMem> e(m, gp);
+    e.load(); e.exec_one(); e.store();
+}
+
+}
