@@ -94,13 +94,23 @@ int stm_bfs(stm_ctx *ctx, const uint8_t *root_states, const uint8_t *root_stacks
             uint8_t *leaf_stacks, float *leaf_rewards, uint8_t *leaf_done, int32_t *leaf_lives,
             uint8_t *leaf_states, void *stream);
 
-/* Same, with HOST buffers (pinned or pageable): copies roots host->device, runs stm_bfs, copies
- * the leaves device->host and synchronises `stream` before returning.  This is the call a
- * non-CUDA host program (the reference's Python loop, a cgo/JNI binding) makes. */
+/* Same, with HOST buffers (pinned or pageable) for the roots and for rewards/done/lives: copies
+ * the roots host->device, runs stm_bfs, copies the results device->host and synchronises
+ * `stream` before returning.  This is the call a non-CUDA host program makes, and it mirrors the
+ * reference boundary: `bfs(state, depth)` takes the root observation from host memory
+ * (environments/cule_env.py:93 hands SB3 numpy) and returns the leaves ON THE GPU
+ * (cule_bfs.py:170,204,209).  leaf_stacks is a DEVICE pointer when leaf_stacks_on_device != 0
+ * (the reference behaviour), else a HOST pointer that receives a full copy of the leaf stacks. */
 int stm_bfs_host(stm_ctx *ctx, const uint8_t *root_states, const uint8_t *root_stacks, int n_roots,
                  int depth, float gamma, int frameskip, int episodic_life, int clip_reward,
-                 uint8_t *leaf_stacks, float *leaf_rewards, uint8_t *leaf_done, int32_t *leaf_lives,
-                 void *stream);
+                 uint8_t *leaf_stacks, int leaf_stacks_on_device, float *leaf_rewards,
+                 uint8_t *leaf_done, int32_t *leaf_lives, void *stream);
+
+/* Per-kernel device timing for bench.py's roofline: when enabled, a CUDA event pair is recorded on
+ * the launch stream around every K1/K2/K3 launch.  stm_timing_read waits for them and returns the
+ * summed milliseconds and launch counts by kind {0: clone, 1: step, 2: frames}, then clears. */
+int stm_timing_enable(stm_ctx *ctx, int on);
+int stm_timing_read(stm_ctx *ctx, float *ms_by_kind, int *launches_by_kind);
 
 /* number of kernels this ctx has launched since creation (bench.py's gpu_launches) */
 long long stm_launch_count(const stm_ctx *ctx);

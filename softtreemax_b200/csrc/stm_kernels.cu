@@ -70,6 +70,12 @@ struct stm_ctx {
     size_t h_roots = 0, h_leaves = 0;
     uint32_t reset_pc = 0;
     long long launches = 0;
+    // optional per-kernel timing (stm_timing_*): CUDA events recorded around every launch
+    bool timing = false;
+    static constexpr int kMaxTimed = 4096;
+    cudaEvent_t *ev = nullptr;          // 2 * kMaxTimed events
+    int ev_kind[kMaxTimed];
+    int n_timed = 0;
     char err[256] = "";
 };
 
@@ -370,6 +376,20 @@ __global__ void stm_finalize_kernel(const float *rewards, float *out_rewards, in
     out_rewards[i] = r;
 }
 
+enum { T_CLONE = 0, T_STEP = 1, T_FRAMES = 2, T_KINDS = 3 };
+struct Timed {
+    stm_ctx *ctx; cudaStream_t st; int slot;
+    Timed(stm_ctx *c, cudaStream_t s, int kind) : ctx(c), st(s), slot(-1)
+    {
+        if (c->timing && c->n_timed < stm_ctx::kMaxTimed) {
+            slot = c->n_timed++;
+            c->ev_kind[slot] = kind;
+            cudaEventRecord(c->ev[2 * slot], s);
+        }
+    }
+    ~Timed() { if (slot >= 0) cudaEventRecord(ctx->ev[2 * slot + 1], st); }
+};
+
 int ensure_scratch(stm_ctx *ctx, int n_envs)
 {
     if (n_envs <= ctx->scratch_envs) return STM_OK;
@@ -396,7 +416,7 @@ int launch_step(stm_ctx *ctx, uint8_t *states, const uint8_t *actions, int n, in
     a.rom_words = ctx->rom_words; a.weight = weight; a.gp = ctx->gp;
     size_t smem = (size_t)(64 * kStepThreads + ctx->rom_words + 256) * sizeof(uint32_t);
     int blocks = (n + kStepThreads - 1) / kStepThreads;
-    stm_step_kernel<<<blocks, kStepThreads, smem, st>>>(a);
+    { Timed t(ctx, st, T_STEP); stm_step_kernel<<<blocks, kStepThreads, smem, st>>>(a); }
     ctx->launches++;
     if (render) ctx->last_render_frames = frameskip >= 2 ? 2 : 1;
     CUDA_TRY(ctx, cudaGetLastError());
@@ -406,8 +426,9 @@ int launch_step(stm_ctx *ctx, uint8_t *states, const uint8_t *actions, int n, in
 int launch_frames(stm_ctx *ctx, const uint8_t *parent, uint8_t *child, int n, int fanout, cudaStream_t st)
 {
     dim3 grid((n + kTileEnvs - 1) / kTileEnvs, STM_OBS_H);
-    stm_frames_kernel<<<grid, kFrameThreads, 0, st>>>(ctx->d_scratch, ctx->d_stepped, parent, child, n, fanout,
-                                                     ctx->last_render_frames);
+    { Timed t(ctx, st, T_FRAMES);
+      stm_frames_kernel<<<grid, kFrameThreads, 0, st>>>(ctx->d_scratch, ctx->d_stepped, parent, child, n, fanout,
+                                                       ctx->last_render_frames); }
     ctx->launches++;
     CUDA_TRY(ctx, cudaGetLastError());
     return STM_OK;
@@ -418,8 +439,9 @@ int launch_clone(stm_ctx *ctx, const uint8_t *ss, const float *sr, const uint8_t
 {
     int ntiles = (n_src + kCloneParents - 1) / kCloneParents;
     int grid = ntiles < 148 * 4 ? ntiles : 148 * 4;       // persistent: up to 4 CTAs on each of the 148 SMs
-    stm_clone_kernel<<<grid, kCloneThreads, 0, st>>>(reinterpret_cast<const uint4 *>(ss), reinterpret_cast<uint4 *>(ds),
-                                                    sr, dr, sd, dd, sl, dl, n_src, fanout);
+    { Timed t(ctx, st, T_CLONE);
+      stm_clone_kernel<<<grid, kCloneThreads, 0, st>>>(reinterpret_cast<const uint4 *>(ss), reinterpret_cast<uint4 *>(ds),
+                                                      sr, dr, sd, dd, sl, dl, n_src, fanout); }
     ctx->launches++;
     CUDA_TRY(ctx, cudaGetLastError());
     return STM_OK;
@@ -521,7 +543,36 @@ int stm_ctx_destroy(stm_ctx *ctx)
     }
     cudaFree(ctx->h_in_state); cudaFree(ctx->h_in_stack); cudaFree(ctx->h_out_stack);
     cudaFree(ctx->h_out_reward); cudaFree(ctx->h_out_done); cudaFree(ctx->h_out_lives);
+    if (ctx->ev) { for (int i = 0; i < 2 * stm_ctx::kMaxTimed; i++) cudaEventDestroy(ctx->ev[i]); delete[] ctx->ev; }
     delete ctx;
+    return STM_OK;
+}
+
+int stm_timing_enable(stm_ctx *ctx, int on)
+{
+    if (!ctx) return fail(ctx, STM_ERR_ARG, "stm_timing_enable: null ctx");
+    CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    if (on && !ctx->ev) {
+        ctx->ev = new (std::nothrow) cudaEvent_t[2 * stm_ctx::kMaxTimed];
+        if (!ctx->ev) return fail(ctx, STM_ERR_NOMEM, "stm_timing_enable: out of host memory");
+        for (int i = 0; i < 2 * stm_ctx::kMaxTimed; i++) CUDA_TRY(ctx, cudaEventCreate(&ctx->ev[i]));
+    }
+    ctx->timing = on != 0;
+    ctx->n_timed = 0;
+    return STM_OK;
+}
+
+int stm_timing_read(stm_ctx *ctx, float *ms_by_kind, int *launches_by_kind)
+{
+    if (!ctx || !ms_by_kind || !launches_by_kind) return fail(ctx, STM_ERR_ARG, "stm_timing_read: bad argument");
+    for (int k = 0; k < T_KINDS; k++) { ms_by_kind[k] = 0.f; launches_by_kind[k] = 0; }
+    for (int i = 0; i < ctx->n_timed; i++) {
+        CUDA_TRY(ctx, cudaEventSynchronize(ctx->ev[2 * i + 1]));
+        float ms = 0.f;
+        CUDA_TRY(ctx, cudaEventElapsedTime(&ms, ctx->ev[2 * i], ctx->ev[2 * i + 1]));
+        ms_by_kind[ctx->ev_kind[i]] += ms; launches_by_kind[ctx->ev_kind[i]]++;
+    }
+    ctx->n_timed = 0;
     return STM_OK;
 }
 
@@ -645,7 +696,7 @@ int stm_bfs(stm_ctx *ctx, const uint8_t *root_states, const uint8_t *root_stacks
 
 int stm_bfs_host(stm_ctx *ctx, const uint8_t *root_states, const uint8_t *root_stacks, int n_roots, int depth,
                  float gamma, int frameskip, int episodic_life, int clip_reward, uint8_t *leaf_stacks,
-                 float *leaf_rewards, uint8_t *leaf_done, int32_t *leaf_lives, void *stream)
+                 int leaf_stacks_on_device, float *leaf_rewards, uint8_t *leaf_done, int32_t *leaf_lives, void *stream)
 {
     if (!ctx || !root_states || !root_stacks || !leaf_stacks || !leaf_rewards || n_roots < 1 || depth < 1)
         return fail(ctx, STM_ERR_ARG, "stm_bfs_host: bad argument");
@@ -660,10 +711,10 @@ int stm_bfs_host(stm_ctx *ctx, const uint8_t *root_states, const uint8_t *root_s
         CUDA_TRY(ctx, cudaMalloc(&ctx->h_in_stack, (size_t)n_roots * SB));
         ctx->h_roots = (size_t)n_roots;
     }
-    if (L > ctx->h_leaves) {
+    if (L > ctx->h_leaves || (!leaf_stacks_on_device && !ctx->h_out_stack)) {
         cudaFree(ctx->h_out_stack); cudaFree(ctx->h_out_reward); cudaFree(ctx->h_out_done); cudaFree(ctx->h_out_lives);
         ctx->h_out_stack = nullptr; ctx->h_out_reward = nullptr; ctx->h_out_done = nullptr; ctx->h_out_lives = nullptr; ctx->h_leaves = 0;
-        CUDA_TRY(ctx, cudaMalloc(&ctx->h_out_stack, L * SB));
+        if (!leaf_stacks_on_device) CUDA_TRY(ctx, cudaMalloc(&ctx->h_out_stack, L * SB));
         CUDA_TRY(ctx, cudaMalloc(&ctx->h_out_reward, L * sizeof(float)));
         CUDA_TRY(ctx, cudaMalloc(&ctx->h_out_done, L));
         CUDA_TRY(ctx, cudaMalloc(&ctx->h_out_lives, L * sizeof(int32_t)));
@@ -672,9 +723,10 @@ int stm_bfs_host(stm_ctx *ctx, const uint8_t *root_states, const uint8_t *root_s
     CUDA_TRY(ctx, cudaMemcpyAsync(ctx->h_in_state, root_states, (size_t)n_roots * STM_STATE_BYTES, cudaMemcpyHostToDevice, st));
     CUDA_TRY(ctx, cudaMemcpyAsync(ctx->h_in_stack, root_stacks, (size_t)n_roots * SB, cudaMemcpyHostToDevice, st));
     int rc = stm_bfs(ctx, ctx->h_in_state, ctx->h_in_stack, n_roots, depth, gamma, frameskip, episodic_life, clip_reward,
-                     ctx->h_out_stack, ctx->h_out_reward, ctx->h_out_done, ctx->h_out_lives, nullptr, stream);
+                     leaf_stacks_on_device ? leaf_stacks : ctx->h_out_stack, ctx->h_out_reward, ctx->h_out_done,
+                     ctx->h_out_lives, nullptr, stream);
     if (rc) return rc;
-    CUDA_TRY(ctx, cudaMemcpyAsync(leaf_stacks, ctx->h_out_stack, L * SB, cudaMemcpyDeviceToHost, st));
+    if (!leaf_stacks_on_device) CUDA_TRY(ctx, cudaMemcpyAsync(leaf_stacks, ctx->h_out_stack, L * SB, cudaMemcpyDeviceToHost, st));
     CUDA_TRY(ctx, cudaMemcpyAsync(leaf_rewards, ctx->h_out_reward, L * sizeof(float), cudaMemcpyDeviceToHost, st));
     if (leaf_done) CUDA_TRY(ctx, cudaMemcpyAsync(leaf_done, ctx->h_out_done, L, cudaMemcpyDeviceToHost, st));
     if (leaf_lives) CUDA_TRY(ctx, cudaMemcpyAsync(leaf_lives, ctx->h_out_lives, L * sizeof(int32_t), cudaMemcpyDeviceToHost, st));

@@ -114,15 +114,29 @@ class Engine:
         return out
 
     def bfs_host(self, root_states, root_stacks, depth, gamma=0.99, frameskip=4, episodic_life=True,
-                 clip_reward=True, out=None):
-        """Host-buffer entry point (numpy arrays or pinned CPU tensors in, same out)."""
+                 clip_reward=True, out=None, stacks_on_device=False):
+        """Host-buffer entry point: roots come from host memory (numpy arrays or pinned CPU tensors),
+        rewards/done/lives go back to host memory; the leaf stacks stay on the GPU when
+        stacks_on_device (what the reference's bfs() returns) or are copied to the host too."""
         R = root_states.shape[0]
         L = R * self.n_actions ** depth
         if out is None:
-            out = dict(stacks=np.empty((L, 4, 84, 84), np.uint8), rewards=np.empty((L,), np.float32),
+            stacks = (torch.empty((L, 4, 84, 84), dtype=torch.uint8, device=self.device) if stacks_on_device
+                      else np.empty((L, 4, 84, 84), np.uint8))
+            out = dict(stacks=stacks, rewards=np.empty((L,), np.float32),
                        done=np.empty((L,), np.uint8), lives=np.empty((L,), np.int32))
+        on_dev = isinstance(out["stacks"], torch.Tensor) and out["stacks"].is_cuda
         check(lib().stm_bfs_host(self._h, _ptr(root_states), _ptr(root_stacks), R, depth, float(gamma),
-                                 frameskip, int(episodic_life), int(clip_reward), _ptr(out["stacks"]),
+                                 frameskip, int(episodic_life), int(clip_reward), _ptr(out["stacks"]), int(on_dev),
                                  _ptr(out["rewards"]), _ptr(out["done"]), _ptr(out["lives"]), self._stream()),
               self._h)
         return out
+
+    def timing(self, on=True):
+        check(lib().stm_timing_enable(self._h, int(on)), self._h)
+
+    def timing_read(self):
+        ms = (C.c_float * 3)()
+        cnt = (C.c_int * 3)()
+        check(lib().stm_timing_read(self._h, ms, cnt), self._h)
+        return {k: (float(ms[i]), int(cnt[i])) for i, k in enumerate(("clone", "step", "frames"))}
