@@ -137,6 +137,103 @@ static inline void build_decode_table(uint32_t *t)
     set(0xCA, C_DEX, M_IMP, K_N); set(0xEA, C_NOP, M_IMP, K_N);
 }
 
+
+// ---- hot decode word ---------------------------------------------------------------------------
+// The kernel does not switch on 60 operation classes: they are folded into ~25 execution groups
+// whose variants are selected by data bits (which register a load targets, which flag a CLC/SEC
+// touches, ...), so that lanes running LDA and LDX, or CLC and SED, stay converged.
+//   [2:0] am   0 none 1 imm 2 zp-family 3 abs-family 4 (zp,x) 5 (zp),y 6 (abs) 7 rel
+//   [4:3] idx  0 none 1 X 2 Y          [6:5] kind (bit0 reads memory, bit1 writes memory)
+//   [10:7] base cycles                 [12:11] length      [17:13] group      [31:18] data
+enum Grp : uint32_t {
+    G_NOP, G_LOAD, G_STORE, G_XFER, G_PUSH, G_PULL, G_LOGIC, G_ADC, G_SBC, G_CMP, G_BIT, G_SHIFT,
+    G_INCDEC_MEM, G_INCDEC_REG, G_FLAG, G_JMP, G_JSR, G_RTS, G_RTI, G_BRK, G_BRANCH, G_RMW_ALU,
+    G_ANC, G_ALR, G_SBX, G_COUNT
+};
+static inline uint32_t encode_hot(uint32_t e, uint32_t op)
+{
+    uint32_t mode = e & 15, kind = (e >> 4) & 3, cyc = (e >> 6) & 15, cls = e >> 10;
+    static const uint32_t AM[13] = { 0, 1, 2, 2, 2, 3, 3, 3, 4, 5, 7, 6, 0 };
+    static const uint32_t IX[13] = { 0, 0, 0, 1, 2, 0, 1, 2, 0, 2, 0, 0, 0 };
+    static const uint32_t LEN[13] = { 1, 2, 2, 2, 2, 3, 3, 3, 2, 2, 2, 3, 1 };
+    uint32_t grp = G_NOP, data = 0;
+    switch (cls) {
+    case C_LDA: grp = G_LOAD; data = 1; break;
+    case C_LDX: grp = G_LOAD; data = 2; break;
+    case C_LDY: grp = G_LOAD; data = 4; break;
+    case C_LAX: grp = G_LOAD; data = 3; break;
+    case C_STA: grp = G_STORE; data = 1; break;
+    case C_STX: grp = G_STORE; data = 2; break;
+    case C_STY: grp = G_STORE; data = 4; break;
+    case C_SAX: grp = G_STORE; data = 3; break;
+    // transfers: data = src (0 A, 1 X, 2 Y, 3 SP) | dst << 2 | setflags << 4
+    case C_TAX: grp = G_XFER; data = 0 | (1 << 2) | 16; break;
+    case C_TAY: grp = G_XFER; data = 0 | (2 << 2) | 16; break;
+    case C_TXA: grp = G_XFER; data = 1 | (0 << 2) | 16; break;
+    case C_TYA: grp = G_XFER; data = 2 | (0 << 2) | 16; break;
+    case C_TSX: grp = G_XFER; data = 3 | (1 << 2) | 16; break;
+    case C_TXS: grp = G_XFER; data = 1 | (3 << 2); break;
+    case C_PHA: grp = G_PUSH; data = 0; break;
+    case C_PHP: grp = G_PUSH; data = 1; break;
+    case C_PLA: grp = G_PULL; data = 0; break;
+    case C_PLP: grp = G_PULL; data = 1; break;
+    case C_AND: grp = G_LOGIC; data = 0; break;
+    case C_ORA: grp = G_LOGIC; data = 1; break;
+    case C_EOR: grp = G_LOGIC; data = 2; break;
+    case C_ADC: grp = G_ADC; break;
+    case C_SBC: grp = G_SBC; break;
+    case C_CMP: grp = G_CMP; data = 0; break;
+    case C_CPX: grp = G_CMP; data = 1; break;
+    case C_CPY: grp = G_CMP; data = 2; break;
+    case C_BIT: grp = G_BIT; break;
+    case C_ASL: grp = G_SHIFT; data = 0; break;
+    case C_LSR: grp = G_SHIFT; data = 1; break;
+    case C_ROL: grp = G_SHIFT; data = 2; break;
+    case C_ROR: grp = G_SHIFT; data = 3; break;
+    case C_INC: grp = G_INCDEC_MEM; data = 1; break;
+    case C_DEC: grp = G_INCDEC_MEM; data = 0xFF; break;
+    // data = reg (1 X, 2 Y) | delta << 2
+    case C_INX: grp = G_INCDEC_REG; data = 1 | (1 << 2); break;
+    case C_INY: grp = G_INCDEC_REG; data = 2 | (1 << 2); break;
+    case C_DEX: grp = G_INCDEC_REG; data = 1 | (0xFF << 2); break;
+    case C_DEY: grp = G_INCDEC_REG; data = 2 | (0xFF << 2); break;
+    // data = flag mask | set << 8
+    case C_CLC: grp = G_FLAG; data = 0x01; break;
+    case C_SEC: grp = G_FLAG; data = 0x01 | 256; break;
+    case C_CLI: grp = G_FLAG; data = 0x04; break;
+    case C_SEI: grp = G_FLAG; data = 0x04 | 256; break;
+    case C_CLV: grp = G_FLAG; data = 0x40; break;
+    case C_CLD: grp = G_FLAG; data = 0x08; break;
+    case C_SED: grp = G_FLAG; data = 0x08 | 256; break;
+    case C_JMP: grp = G_JMP; break;
+    case C_JSR: grp = G_JSR; break;
+    case C_RTS: grp = G_RTS; break;
+    case C_RTI: grp = G_RTI; break;
+    case C_BRK: grp = G_BRK; break;
+    // data = flag select (0 N, 1 V, 2 C, 3 Z) | wanted value << 2
+    case C_BRA: grp = G_BRANCH; data = (op >> 6) | (((op >> 5) & 1) << 2); break;
+    case C_SLO: grp = G_RMW_ALU; data = 0; break;
+    case C_RLA: grp = G_RMW_ALU; data = 1; break;
+    case C_SRE: grp = G_RMW_ALU; data = 2; break;
+    case C_RRA: grp = G_RMW_ALU; data = 3; break;
+    case C_DCP: grp = G_RMW_ALU; data = 4; break;
+    case C_ISC: grp = G_RMW_ALU; data = 5; break;
+    case C_ANC: grp = G_ANC; break;
+    case C_ALR: grp = G_ALR; break;
+    case C_SBX: grp = G_SBX; break;
+    default: grp = G_NOP; break;
+    }
+    if (mode == M_ACC) kind = K_N;
+    return AM[mode] | (IX[mode] << 3) | (kind << 5) | (cyc << 7) | (LEN[mode] << 11) | (grp << 13) | (data << 18);
+}
+// the table the kernel uses
+static inline void build_hot_table(uint32_t *t)
+{
+    uint32_t e[256];
+    build_decode_table(e);
+    for (uint32_t op = 0; op < 256; op++) t[op] = encode_hot(e[op], op);
+}
+
 // ---- game constants handed to the kernel ---------------------------------------------------------
 struct GameParams {
     uint32_t rom_mask;        // byte mask inside one bank window (0x7FF / 0xFFF)
@@ -212,36 +309,50 @@ STM_FN uint32_t sel_bytes(uint32_t under, uint32_t over, uint32_t m) { return (u
 // M must provide:
 //   uint32_t ld8(off) / void st8(off, v) / ld16 / st16 / ld32 / st32     blob access (off = byte offset)
 //   uint32_t rom8(idx), rom32(word_idx)                                    cartridge image
-//   uint32_t opinfo(op)                                                    decode table
+//   uint32_t opinfo(op)                                                    hot decode word (build_hot_table)
 //   void px4(row, g, word)   store 4 pixels (colour indices) of native row `row`, group g (0..39)
 //   void px1(row, x, v)      store 1 pixel
+//
+// One instruction = fetch -> decode -> address -> read phase -> execute (register-only switch over
+// ~25 groups) -> write phase -> retire.  Every memory access goes through ONE read site and ONE
+// write site, so the TIA/RIOT slow paths (and the big catch-up renderer behind them) exist once in
+// the kernel instead of once per opcode; stack pulls/pushes are sequenced through the same sites.
 template <class M>
 struct Emu {
     M &m;
     const GameParams &gp;
-    // hot state in registers
-    uint32_t pc, a, x, y, sp, p, bank;
-    uint32_t hcyc, line, rx, flags;
+    // hot state (registers)
+    uint32_t pc, a, x, y, sp;
+    uint32_t p;             // C, I, D, V only (mask 0x4D); N and Z live in zn
+    uint32_t zn;            // Z <=> (zn & 0xFF) == 0 ; N <=> (zn & 0x180) != 0
+    int32_t  hcyc;          // CPU cycle in the line; may be transiently negative inside an instruction
     int32_t  timer;
-    uint32_t tflag;
-    bool     render;        // pixels of this frame are wanted
-    uint32_t end_line_no;
-    bool     wsync;
+    uint32_t bank;
+    // warm state
+    uint32_t line, rx, flags, end_line_no;
+    bool     render, wsync;
 
     STM_DEV Emu(M &mm, const GameParams &g) : m(mm), gp(g) {}
 
+    STM_DEV uint32_t get_p() const
+    { return (p & 0x4Du) | FU | ((zn & 0x180u) ? (uint32_t)FN : 0u) | ((zn & 0xFFu) ? 0u : (uint32_t)FZ); }
+    STM_DEV void set_p(uint32_t v) { p = v & 0x4Du; zn = ((v & FN) << 1) | ((v & FZ) ? 0u : 1u); }
+
     STM_DEV void load()
     {
-        pc = m.ld16(O_PC); a = m.ld8(O_A); x = m.ld8(O_X); y = m.ld8(O_Y); sp = m.ld8(O_SP); p = m.ld8(O_P);
-        bank = m.ld8(O_BANK); line = m.ld16(O_LINE); hcyc = m.ld8(O_HCYC); rx = m.ld8(O_RX);
-        flags = m.ld8(O_FLAGS); timer = (int32_t)m.ld32(O_TIMER); tflag = m.ld8(O_TFLAG);
+        pc = m.ld16(O_PC); a = m.ld8(O_A); x = m.ld8(O_X); y = m.ld8(O_Y); sp = m.ld8(O_SP); set_p(m.ld8(O_P));
+        bank = m.ld8(O_BANK); line = m.ld16(O_LINE); hcyc = (int32_t)m.ld8(O_HCYC); rx = m.ld8(O_RX);
+        flags = m.ld8(O_FLAGS); timer = (int32_t)m.ld32(O_TIMER);
         render = false; end_line_no = 0; wsync = false;
     }
     STM_DEV void store()
     {
-        m.st16(O_PC, pc); m.st8(O_A, a); m.st8(O_X, x); m.st8(O_Y, y); m.st8(O_SP, sp); m.st8(O_P, p);
-        m.st8(O_BANK, bank); m.st16(O_LINE, line); m.st8(O_HCYC, hcyc); m.st8(O_RX, rx);
-        m.st8(O_FLAGS, flags); m.st32(O_TIMER, (uint32_t)timer); m.st8(O_TFLAG, tflag);
+        if (timer < -(1 << 30)) timer += (1 << 30);
+        m.st16(O_PC, pc); m.st8(O_A, a); m.st8(O_X, x); m.st8(O_Y, y); m.st8(O_SP, sp);
+        m.st8(O_P, get_p());
+        m.st8(O_BANK, bank); m.st16(O_LINE, line); m.st8(O_HCYC, (uint32_t)hcyc); m.st8(O_RX, rx);
+        m.st8(O_FLAGS, flags); m.st32(O_TIMER, (uint32_t)timer);
+        m.st8(O_TFLAG, timer < 0 ? 0x80u : 0u);      // the underflow latch always equals (timer < 0) between instructions
     }
 
     // ---------------- input ----------------
@@ -249,12 +360,10 @@ struct Emu {
     STM_DEV uint32_t dir_bits()    // bit0 up, bit1 down, bit2 left, bit3 right
     {
         uint32_t act = m.ld8(O_ACTION);
-        uint32_t b = act >= 10 ? act - 8 : act;           // FIRE variants repeat codes 2..9
         if (act < 2 || act > 17) return 0;
-        switch (b) {
-        case 2: return 1; case 3: return 8; case 4: return 4; case 5: return 2;
-        case 6: return 9; case 7: return 5; case 8: return 10; default: return 6;
-        }
+        uint32_t b = act >= 10 ? act - 8 : act;           // FIRE variants repeat codes 2..9
+        // nibble table for b = 2..9: 1 8 4 2 9 5 10 6
+        return (0x6A592481u >> (4 * (b - 2))) & 0xFu;
     }
     STM_DEV void update_latch()
     {
@@ -277,7 +386,7 @@ struct Emu {
 
     // ---------------- TIA rendering: 32-pixel words from object masks ----------------
     // bits of `pat` (width <= 32, bit 0 = leftmost pixel) placed at ring position `start` (0..159),
-    // returned as seen by word w (pixels 32w..32w+31); the 160-pixel line is a ring.
+    // as seen by word w (pixels 32w..32w+31); the 160-pixel line is a ring.
     STM_DEV uint32_t place(uint32_t pat, int start, int w)
     {
         int r = start - 32 * w;
@@ -292,10 +401,10 @@ struct Emu {
         uint32_t mode = nusiz & 7;
         uint32_t out = place(pat, (int)pos, w);
         // second / third copy offsets: 1:{16} 2:{32} 3:{16,32} 4:{64} 6:{32,64}
-        uint32_t o1 = (mode == 1 || mode == 3) ? 16u : ((mode == 2 || mode == 6) ? 32u : (mode == 4 ? 64u : 0u));
-        uint32_t o2 = mode == 3 ? 32u : (mode == 6 ? 64u : 0u);
-        if (o1) { uint32_t s = pos + o1; if (s >= 160) s -= 160; out |= place(pat, (int)s, w); }
-        if (o2) { uint32_t s = pos + o2; if (s >= 160) s -= 160; out |= place(pat, (int)s, w); }
+        uint32_t o1 = (0x02041210u >> (4 * mode)) & 0xFu;      // in units of 16 px: modes 1,3 -> 1; 2,6 -> 2; 4 -> 4
+        uint32_t o2 = mode == 3 ? 2u : (mode == 6 ? 4u : 0u);
+        if (o1) { uint32_t s = pos + 16 * o1; if (s >= 160) s -= 160; out |= place(pat, (int)s, w); }
+        if (o2) { uint32_t s = pos + 16 * o2; if (s >= 160) s -= 160; out |= place(pat, (int)s, w); }
         return out;
     }
     STM_DEV uint32_t player_pat(uint32_t grp, uint32_t nusiz, uint32_t refp)
@@ -310,12 +419,16 @@ struct Emu {
         return g;
     }
 
+    // Rows of the 210-row native frame that the 84x84 bilinear resize never samples (row % 5 == 2)
+    // are not drawn at all; nothing downstream reads them.
+    STM_DEV static bool row_sampled(int row) { return (uint32_t)row < (uint32_t)STM_VIS_H && (row % 5) != 2; }
+
     STM_DEV void catchup(uint32_t xe)
     {
         if (xe > STM_VIS_W) xe = STM_VIS_W;
         if (xe <= rx) return;
         int row = (int)line - STM_YSTART;
-        bool draw = render && row >= 0 && row < STM_VIS_H;
+        bool draw = render && row_sampled(row);
         uint32_t vblank = m.ld8(O_VBLANK);
         bool vb = (vblank & 2) != 0;
         uint32_t g0 = (m.ld8(O_VDELP0) & 1) ? m.ld8(O_GRP0_OLD) : m.ld8(O_GRP0);
@@ -326,6 +439,22 @@ struct Emu {
         bool blon = (enbl & 2) != 0;
         bool movable = g0 || g1 || m0on || m1on || blon;
         if (!draw && (vb || !movable)) { rx = xe; return; }
+
+        int w0 = (int)(rx >> 5), w1 = (int)((xe - 1) >> 5);
+        if (draw && vb) {                                    // blanked line: black pixels, no collisions
+            for (int w = w0; w <= w1; w++) {
+                int lo = (int)rx - 32 * w; if (lo < 0) lo = 0;
+                int hi = (int)xe - 32 * w; if (hi > 32) hi = 32;
+                for (int n = lo >> 2; n <= (hi - 1) >> 2; n++) {
+                    int l4 = lo - 4 * n, h4 = hi - 4 * n;
+                    uint32_t g = 8u * (uint32_t)w + (uint32_t)n;
+                    if (l4 <= 0 && h4 >= 4) m.px4((uint32_t)row, g, 0);
+                    else for (int k = l4 < 0 ? 0 : l4; k < (h4 > 4 ? 4 : h4); k++) m.px1((uint32_t)row, 4u * g + (uint32_t)k, 0);
+                }
+            }
+            rx = xe;
+            return;
+        }
 
         uint32_t ctrlpf = m.ld8(O_CTRLPF);
         uint32_t nusiz0 = m.ld8(O_NUSIZ0), nusiz1 = m.ld8(O_NUSIZ1);
@@ -343,50 +472,56 @@ struct Emu {
         uint32_t cx = 0;
         uint32_t c_p0 = 0, c_p1 = 0, c_pf = 0, c_bk = 0;
         bool comb = (flags & STM_F_HMOVE_BLANK) != 0;
+        bool pfp = (ctrlpf & 4) != 0, score = (ctrlpf & 2) != 0 && !pfp;
         if (draw) {
             c_p0 = (m.ld8(O_COLUP0) >> 1) * 0x01010101u; c_p1 = (m.ld8(O_COLUP1) >> 1) * 0x01010101u;
             c_pf = (m.ld8(O_COLUPF) >> 1) * 0x01010101u; c_bk = (m.ld8(O_COLUBK) >> 1) * 0x01010101u;
         }
-        int w0 = (int)(rx >> 5), w1 = (int)((xe - 1) >> 5);
         for (int w = w0; w <= w1; w++) {
             int lo = (int)rx - 32 * w; if (lo < 0) lo = 0;
             int hi = (int)xe - 32 * w; if (hi > 32) hi = 32;
             uint32_t seg = (hi == 32 ? 0xFFFFFFFFu : ((1u << hi) - 1u)) & ~((1u << lo) - 1u);
             uint32_t pfcols = w < 4 ? (pf_lo >> (8 * w)) & 0xFFu : pf_hi & 0xFFu;
             uint32_t pfm = spread8x4(pfcols) & seg;
-            uint32_t p0m = pat0 ? copies(pat0, pos_p0, nusiz0, w) & seg : 0;
-            uint32_t p1m = pat1 ? copies(pat1, pos_p1, nusiz1, w) & seg : 0;
-            uint32_t m0m = m0on ? copies(mp0, pos_m0, nusiz0, w) & seg : 0;
-            uint32_t m1m = m1on ? copies(mp1, pos_m1, nusiz1, w) & seg : 0;
-            uint32_t blm = blon ? place(bp, (int)pos_bl, w) & seg : 0;
-            if (!vb && movable) {
-                if (m0m & p0m) cx |= 1u << 0;
-                if (m0m & p1m) cx |= 1u << 1;
-                if (m1m & p1m) cx |= 1u << 2;
-                if (m1m & p0m) cx |= 1u << 3;
-                if (p0m & blm) cx |= 1u << 4;
-                if (p0m & pfm) cx |= 1u << 5;
-                if (p1m & blm) cx |= 1u << 6;
-                if (p1m & pfm) cx |= 1u << 7;
-                if (m0m & blm) cx |= 1u << 8;
-                if (m0m & pfm) cx |= 1u << 9;
-                if (m1m & blm) cx |= 1u << 10;
-                if (m1m & pfm) cx |= 1u << 11;
-                if (blm & pfm) cx |= 1u << 13;
-                if (m0m & m1m) cx |= 1u << 14;
-                if (p0m & p1m) cx |= 1u << 15;
+            uint32_t l0 = 0, l1 = 0, blm = 0;
+            if (movable) {
+                uint32_t p0m = pat0 ? copies(pat0, pos_p0, nusiz0, w) & seg : 0;
+                uint32_t p1m = pat1 ? copies(pat1, pos_p1, nusiz1, w) & seg : 0;
+                uint32_t m0m = m0on ? copies(mp0, pos_m0, nusiz0, w) & seg : 0;
+                uint32_t m1m = m1on ? copies(mp1, pos_m1, nusiz1, w) & seg : 0;
+                blm = blon ? place(bp, (int)pos_bl, w) & seg : 0;
+                l0 = p0m | m0m; l1 = p1m | m1m;
+                if (!vb && (l0 | l1 | blm)) {
+                    if (m0m & p0m) cx |= 1u << 0;
+                    if (m0m & p1m) cx |= 1u << 1;
+                    if (m1m & p1m) cx |= 1u << 2;
+                    if (m1m & p0m) cx |= 1u << 3;
+                    if (p0m & blm) cx |= 1u << 4;
+                    if (p0m & pfm) cx |= 1u << 5;
+                    if (p1m & blm) cx |= 1u << 6;
+                    if (p1m & pfm) cx |= 1u << 7;
+                    if (m0m & blm) cx |= 1u << 8;
+                    if (m0m & pfm) cx |= 1u << 9;
+                    if (m1m & blm) cx |= 1u << 10;
+                    if (m1m & pfm) cx |= 1u << 11;
+                    if (blm & pfm) cx |= 1u << 13;
+                    if (m0m & m1m) cx |= 1u << 14;
+                    if (p0m & p1m) cx |= 1u << 15;
+                }
             }
             if (draw) {
-                uint32_t l0 = p0m | m0m, l1 = p1m | m1m;
-                bool pfp = (ctrlpf & 4) != 0, score = (ctrlpf & 2) != 0 && !pfp;
+                bool plain = (l0 | l1 | blm) == 0;            // only playfield / background in this word
                 for (int n = lo >> 2; n <= (hi - 1) >> 2; n++) {
                     uint32_t sh = 4u * (uint32_t)n;
+                    uint32_t pfcol = score ? ((32 * w + (int)sh) < 80 ? c_p0 : c_p1) : c_pf;
                     uint32_t word;
-                    if (vb) word = 0;
-                    else {
+                    if (plain) {
+                        // playfield columns are 4 px wide and aligned: the nibble is all-or-nothing
+                        // inside the segment, so a byte mask from the (already seg-masked) nibble is exact
+                        word = sel_bytes(c_bk, pfcol, nib_to_bytes(pfm >> sh));
+                    } else {
                         uint32_t b0 = nib_to_bytes(l0 >> sh), b1 = nib_to_bytes(l1 >> sh);
                         uint32_t bb = nib_to_bytes(blm >> sh), bf = nib_to_bytes(pfm >> sh);
-                        uint32_t pfcol = score ? ((32 * w + (int)sh) < 80 ? c_p0 : c_p1) : c_pf;
                         word = c_bk;
                         if (pfp) {
                             word = sel_bytes(word, c_p1, b1); word = sel_bytes(word, c_p0, b0);
@@ -395,8 +530,8 @@ struct Emu {
                             word = sel_bytes(word, pfcol, bf); word = sel_bytes(word, c_pf, bb);
                             word = sel_bytes(word, c_p1, b1);  word = sel_bytes(word, c_p0, b0);
                         }
-                        if (comb && w == 0 && n < 2) word = 0;
                     }
+                    if (comb && w == 0 && n < 2) word = 0;
                     uint32_t nm = (seg >> sh) & 0xFu;
                     uint32_t g = 8u * (uint32_t)w + (uint32_t)n;
                     if (nm == 0xFu) m.px4((uint32_t)row, g, word);
@@ -419,21 +554,23 @@ struct Emu {
         flags &= ~(uint32_t)STM_F_HMOVE_BLANK;
         if (!(m.ld8(O_VBLANK) & 0x80)) { uint32_t c = m.ld8(O_CHARGE); if (c < 255) m.st8(O_CHARGE, c + 1); }
         if (line >= STM_MAX_LINES) { flags |= STM_F_FRAME_DONE; end_line_no = STM_MAX_LINES; line = 0; }
+        if (timer < -(1 << 30)) timer += (1 << 30);
     }
-    STM_DEV void advance(uint32_t cyc)
+    // cycle (within the line) at which the current instruction touches the bus; runs the line wrap
+    // first when that cycle lies beyond the end of the line
+    STM_DEV uint32_t access_cycle(uint32_t cyc)
     {
-        timer -= (int32_t)cyc;
-        if (timer < 0) { tflag |= 0x80; if (timer < -(1 << 30)) timer += (1 << 30); }
-        hcyc += cyc;
-        if (hcyc >= STM_CYC_PER_LINE) { end_line(); hcyc -= STM_CYC_PER_LINE; }
+        int32_t acc = hcyc + (int32_t)cyc - 1;
+        if (acc >= STM_CYC_PER_LINE) { end_line(); hcyc -= STM_CYC_PER_LINE; acc -= STM_CYC_PER_LINE; }
+        return (uint32_t)acc;
     }
-    STM_DEV uint32_t cur_x() { int v = (int)hcyc * 3 - STM_HBLANK_CLK; return v < 0 ? 0u : (uint32_t)v; }
+    STM_DEV uint32_t x_of(uint32_t acc) { int v = (int)acc * 3 - STM_HBLANK_CLK; return v < 0 ? 0u : (uint32_t)v; }
 
     // ---------------- TIA registers ----------------
-    STM_DEV uint32_t tia_read(uint32_t reg)
+    STM_DEV uint32_t tia_read(uint32_t reg, uint32_t acc)
     {
         reg &= 0x0F;
-        if (reg < 8) { catchup(cur_x()); return ((m.ld16(O_CX) >> (2 * reg)) & 3u) << 6; }
+        if (reg < 8) { catchup(x_of(acc)); return ((m.ld16(O_CX) >> (2 * reg)) & 3u) << 6; }
         if (reg < 12) {
             uint32_t i = reg - 8;
             if (gp.controller != STM_CTRL_PADDLE || i > 1) return 0;
@@ -448,9 +585,9 @@ struct Emu {
         }
         return reg == 13 ? 0x80u : 0u;
     }
-    STM_DEV void set_pos(uint32_t obj, bool player)
+    STM_DEV void set_pos(uint32_t obj, bool player, uint32_t acc)
     {
-        uint32_t clk = hcyc * 3;
+        uint32_t clk = acc * 3;
         uint32_t v = clk < STM_HBLANK_CLK ? (player ? 3u : 2u) : (clk - STM_HBLANK_CLK + (player ? 5u : 4u)) % 160u;
         m.st8(O_POS + obj, v);
     }
@@ -462,16 +599,17 @@ struct Emu {
         if (v >= 160) v -= 160;
         m.st8(O_POS + obj, (uint32_t)v);
     }
-    STM_DEV void tia_write(uint32_t reg, uint32_t v)
+    STM_DEV void tia_write(uint32_t reg, uint32_t v, uint32_t acc)
     {
         reg &= 0x3F;
         if (reg > 0x2C) return;
         if (reg == 0x02) { wsync = true; return; }
         if (reg == 0x03 || (reg >= 0x15 && reg <= 0x1A)) return;
-        catchup(cur_x());
-        if (reg >= 0x04 && reg <= 0x0F) { m.st8(O_NUSIZ0 + (reg - 4), v); return; }   // NUSIZ0..PF2 are laid out in register order
-        if (reg >= 0x1D && reg <= 0x1F) { m.st8(O_ENAM0 + (reg - 0x1D), v); return; }   // ENAM0, ENAM1, ENABL
+        catchup(x_of(acc));
+        if (reg >= 0x04 && reg <= 0x0F) { m.st8(O_NUSIZ0 + (reg - 4), v); return; }    // NUSIZ0..PF2 are laid out in register order
+        if (reg >= 0x1D && reg <= 0x1F) { m.st8(O_ENAM0 + (reg - 0x1D), v); return; }  // ENAM0, ENAM1, ENABL
         if (reg >= 0x20 && reg <= 0x27) { m.st8(O_HMP0 + (reg - 0x20), v); return; }   // HMP0..VDELBL likewise
+        if (reg >= 0x10 && reg <= 0x14) { set_pos(reg - 0x10, reg < 0x12, acc); return; }   // RESP0 RESP1 RESM0 RESM1 RESBL = pos[0..4]
         switch (reg) {
         case 0x00:
             if ((v & 2) && !(m.ld8(O_VSYNC) & 2)) { flags |= STM_F_FRAME_DONE; end_line_no = line; line = 0; }
@@ -479,11 +617,6 @@ struct Emu {
         case 0x01:
             if (v & 0x80) m.st8(O_CHARGE, 0);
             m.st8(O_VBLANK, v); update_latch(); break;
-        case 0x10: set_pos(STM_P0, true); break;
-        case 0x11: set_pos(STM_P1, true); break;
-        case 0x12: set_pos(STM_M0, false); break;
-        case 0x13: set_pos(STM_M1, false); break;
-        case 0x14: set_pos(STM_BL, false); break;
         case 0x1B: m.st8(O_GRP0, v); m.st8(O_GRP1_OLD, m.ld8(O_GRP1)); break;
         case 0x1C: m.st8(O_GRP1, v); m.st8(O_GRP0_OLD, m.ld8(O_GRP0)); m.st8(O_ENABL_OLD, m.ld8(O_ENABL)); break;
         case 0x28:
@@ -496,7 +629,7 @@ struct Emu {
             hmove_obj(STM_P0, m.ld8(O_HMP0)); hmove_obj(STM_P1, m.ld8(O_HMP1));
             hmove_obj(STM_M0, m.ld8(O_HMM0)); hmove_obj(STM_M1, m.ld8(O_HMM1));
             hmove_obj(STM_BL, m.ld8(O_HMBL));
-            if (hcyc * 3 < STM_HBLANK_CLK) flags |= STM_F_HMOVE_BLANK;
+            if (acc * 3 < STM_HBLANK_CLK) flags |= STM_F_HMOVE_BLANK;
             break;
         case 0x2B:
             m.st8(O_HMP0, 0); m.st8(O_HMP1, 0); m.st8(O_HMM0, 0); m.st8(O_HMM1, 0); m.st8(O_HMBL, 0); break;
@@ -509,20 +642,43 @@ struct Emu {
     STM_DEV uint32_t swcha_in()
     {
         if (gp.controller == STM_CTRL_PADDLE) return fire_pressed() ? 0x7Fu : 0xFFu;
-        uint32_t d = dir_bits(), v = 0xFF;
-        if (d & 8) v &= ~0x80u;
-        if (d & 4) v &= ~0x40u;
-        if (d & 2) v &= ~0x20u;
-        if (d & 1) v &= ~0x10u;
-        return v;
+        uint32_t d = dir_bits();
+        // bit7 right, bit6 left, bit5 down, bit4 up; 0 = pushed
+        return 0xFFu & ~(((d & 8) << 4) | ((d & 4) << 4) | ((d & 2) << 4) | ((d & 1) << 4));
     }
-    STM_DEV uint32_t riot_read(uint32_t addr)
+    // Spin-wait fast-forward.  `LDA INTIM ; BNE *-3` (AD 84 02 D0 FB) is how every 2600 program waits
+    // for the end of VBLANK/overscan; run literally it is ~30% of all emulated instructions.  When the
+    // read is about to return non-zero, whole iterations of the loop (which change nothing but time)
+    // are skipped: time moves forward line by line exactly as the iterations would have moved it,
+    // and the instruction then completes as the first iteration that could read zero.
+    STM_DEV void spin_skip(uint32_t cyc, uint32_t sh)
+    {
+        if (sh < 3) return;                                   // the zero window [0, 2^sh) must be >= one iteration
+        if (flags & STM_F_FRAME_DONE) return;                 // the frame ended inside this very instruction
+        if (peek(pc + 3) != 0xD0 || peek(pc + 4) != 0xFB) return;
+        uint32_t per = 7u + ((((pc + 5) ^ pc) & 0xFF00u) ? 1u : 0u);
+        int32_t t_acc = timer - (int32_t)(cyc - 1);
+        int32_t win = (1 << sh) - 1;
+        if (t_acc <= win) return;
+        int32_t j = (t_acc - win + (int32_t)per - 1) / (int32_t)per;
+        int32_t lines_left = (int32_t)STM_MAX_LINES - 2 - (int32_t)line;
+        if (lines_left <= 0) return;
+        int32_t jmax = (lines_left * STM_CYC_PER_LINE) / (int32_t)per;
+        if (j > jmax) j = jmax;
+        int32_t skip = j * (int32_t)per;
+        timer -= skip;
+        hcyc += skip;
+        while (hcyc + (int32_t)cyc - 1 >= STM_CYC_PER_LINE) { end_line(); hcyc -= STM_CYC_PER_LINE; }
+    }
+    STM_DEV uint32_t riot_read(uint32_t addr, uint32_t cyc, uint32_t opword)
     {
         if (addr & 4) {
-            if (addr & 1) return tflag;
-            uint32_t v = timer >= 0 ? ((uint32_t)timer >> m.ld8(O_TSHIFT)) & 0xFFu : (uint32_t)timer & 0xFFu;
-            tflag &= 0x7F;
-            return v;
+            if (addr & 1) return (timer - (int32_t)(cyc - 1)) < 0 ? 0x80u : 0u;     // INSTAT
+            uint32_t sh = m.ld8(O_TSHIFT);
+            // LDA abs (no index) only: group LOAD, am abs, idx none, 4 cycles
+            if ((opword & 0x3E01Fu) == ((G_LOAD << 13) | 3u) && cyc == 4) spin_skip(cyc, sh);
+            int32_t t = timer - (int32_t)(cyc - 1);
+            return t >= 0 ? ((uint32_t)t >> sh) & 0xFFu : (uint32_t)t & 0xFFu;
         }
         uint32_t sel = addr & 3;
         if (sel == 0) { uint32_t d = m.ld8(O_SWACNT); return (m.ld8(O_SWCHA_OUT) & d) | (swcha_in() & ~d & 0xFFu); }
@@ -530,14 +686,14 @@ struct Emu {
         if (sel == 2) { uint32_t d = m.ld8(O_SWBCNT); return (m.ld8(O_SWCHB_OUT) & d) | (0x0Bu & ~d); }
         return m.ld8(O_SWBCNT);
     }
-    STM_DEV void riot_write(uint32_t addr, uint32_t v)
+    STM_DEV void riot_write(uint32_t addr, uint32_t v, uint32_t cyc)
     {
         if (addr & 4) {
             if (addr & 0x10) {
                 uint32_t sh = (0x0A060300u >> (8 * (addr & 3))) & 0xFFu;
                 m.st8(O_TSHIFT, sh);
-                timer = (int32_t)(v << sh) - 1;
-                tflag &= 0x7F;
+                // the write happens at cycle cyc-1 of the instruction; retire subtracts all `cyc` cycles
+                timer = (int32_t)(v << sh) - 1 + (int32_t)(cyc - 1);
             }
             return;
         }
@@ -559,28 +715,28 @@ struct Emu {
         if ((addr & 0x280) == 0x80) return m.ld8(addr & 0x7F);
         return 0;
     }
-    STM_DEV uint32_t rd(uint32_t addr)
+    STM_DEV uint32_t peek16zp(uint32_t z) { return peek(z & 0xFF) | (peek((z + 1) & 0xFF) << 8); }
+    // the single read site / write site of the machine
+    STM_DEV uint32_t bus_read(uint32_t addr, uint32_t cyc, uint32_t opword)
     {
         addr &= 0x1FFF;
-        if ((addr & 0x1280) == 0x80) return m.ld8(addr & 0x7F);          // RAM first: the common case
+        if ((addr & 0x1280) == 0x80) return m.ld8(addr & 0x7F);          // RAM: the common case
         if (addr & 0x1000) { hotspot(addr); return rom_at(addr); }
-        if (!(addr & 0x80)) return tia_read(addr);
-        return riot_read(addr);
+        uint32_t acc = access_cycle(cyc);
+        if (!(addr & 0x80)) return tia_read(addr, acc);
+        return riot_read(addr, cyc, opword);
     }
-    STM_DEV void wr(uint32_t addr, uint32_t v)
+    STM_DEV void bus_write(uint32_t addr, uint32_t v, uint32_t cyc)
     {
-        addr &= 0x1FFF; v &= 0xFF;
+        addr &= 0x1FFF;
         if ((addr & 0x1280) == 0x80) { m.st8(addr & 0x7F, v); return; }
         if (addr & 0x1000) { hotspot(addr); return; }
-        if (!(addr & 0x80)) { tia_write(addr, v); return; }
-        riot_write(addr, v);
+        uint32_t acc = access_cycle(cyc);
+        if (!(addr & 0x80)) { tia_write(addr, v, acc); return; }
+        riot_write(addr, v, cyc);
     }
-    STM_DEV void push(uint32_t v) { wr(0x100 | sp, v); sp = (sp - 1) & 0xFF; }
-    STM_DEV uint32_t pull() { sp = (sp + 1) & 0xFF; return rd(0x100 | sp); }
-    STM_DEV uint32_t peek16zp(uint32_t z) { return peek(z & 0xFF) | (peek((z + 1) & 0xFF) << 8); }
 
-    // ---------------- ALU helpers ----------------
-    STM_DEV void setnz(uint32_t v) { p = (p & ~(FN | FZ)) | (v & 0x80) | ((v & 0xFF) ? 0u : (uint32_t)FZ); }
+    // ---------------- ALU helpers (register only) ----------------
     STM_DEV void adc(uint32_t v)
     {
         uint32_t cin = p & FC;
@@ -589,32 +745,27 @@ struct Emu {
             if (al > 9) al += 6;
             uint32_t ah = (a >> 4) + (v >> 4) + (al > 0x0F ? 1u : 0u);
             uint32_t bin = (a + v + cin) & 0xFF;
-            p &= ~(uint32_t)(FN | FZ | FV | FC);
-            if (!bin) p |= FZ;
-            if (ah & 8) p |= FN;
+            p &= ~(uint32_t)(FV | FC);
+            zn = (bin ? 1u : 0u) | ((ah & 8) << 5);           // Z from the binary sum, N from the high digit
             if (~(a ^ v) & (a ^ (ah << 4)) & 0x80) p |= FV;
             if (ah > 9) ah += 6;
             if (ah > 15) p |= FC;
             a = ((ah << 4) | (al & 0x0F)) & 0xFF;
         } else {
             uint32_t s = a + v + cin;
-            p &= ~(uint32_t)(FV | FC);
-            if (s > 0xFF) p |= FC;
-            if (~(a ^ v) & (a ^ s) & 0x80) p |= FV;
+            p = (p & ~(uint32_t)(FV | FC)) | (s >> 8) | (((~(a ^ v) & (a ^ s)) >> 1) & FV);
             a = s & 0xFF;
-            setnz(a);
+            zn = a;
         }
     }
     STM_DEV void sbc(uint32_t v)
     {
-        uint32_t bc = (p & FC) ? 0u : 1u;
+        uint32_t bc = (p & FC) ^ 1u;
         uint32_t s = a - v - bc;
         uint32_t res = s & 0xFF;
         bool dec = (p & FD) != 0;
-        p &= ~(uint32_t)(FV | FC);
-        if (!(s & 0x100)) p |= FC;
-        if ((a ^ v) & (a ^ s) & 0x80) p |= FV;
-        setnz(res);
+        p = (p & ~(uint32_t)(FV | FC)) | (((s >> 8) & 1u) ^ 1u) | ((((a ^ v) & (a ^ s)) >> 1) & FV);
+        zn = res;
         if (dec) {
             int al = (int)(a & 0x0F) - (int)(v & 0x0F) - (int)bc;
             int ah = (int)(a >> 4) - (int)(v >> 4);
@@ -627,14 +778,20 @@ struct Emu {
     STM_DEV void cmp(uint32_t r, uint32_t v)
     {
         uint32_t d = r - v;
-        p &= ~(uint32_t)FC;
-        if (!(d & 0x100)) p |= FC;
-        setnz(d);
+        p = (p & ~(uint32_t)FC) | (((d >> 8) & 1u) ^ 1u);
+        zn = d & 0xFF;
     }
-    STM_DEV uint32_t asl(uint32_t v) { p = (p & ~(uint32_t)FC) | (v >> 7); v = (v << 1) & 0xFF; setnz(v); return v; }
-    STM_DEV uint32_t lsr(uint32_t v) { p = (p & ~(uint32_t)FC) | (v & 1); v >>= 1; setnz(v); return v; }
-    STM_DEV uint32_t rol(uint32_t v) { uint32_t c = p & FC; p = (p & ~(uint32_t)FC) | (v >> 7); v = ((v << 1) | c) & 0xFF; setnz(v); return v; }
-    STM_DEV uint32_t ror(uint32_t v) { uint32_t c = p & FC; p = (p & ~(uint32_t)FC) | (v & 1); v = (v >> 1) | (c << 7); setnz(v); return v; }
+    // shift group: sub 0 ASL 1 LSR 2 ROL 3 ROR
+    STM_DEV uint32_t shift(uint32_t v, uint32_t sub)
+    {
+        uint32_t cin = (sub & 2) ? (p & FC) : 0u;
+        uint32_t cout, r;
+        if (sub & 1) { cout = v & 1; r = (v >> 1) | (cin << 7); }
+        else         { cout = v >> 7; r = ((v << 1) | cin) & 0xFF; }
+        p = (p & ~(uint32_t)FC) | cout;
+        zn = r;
+        return r;
+    }
 
     // ---------------- one instruction ----------------
     STM_DEV void exec_one()
@@ -654,122 +811,130 @@ struct Emu {
         } else {
             op = peek(pc); b1 = peek(pc + 1); b2 = peek(pc + 2);
         }
-        uint32_t info = m.opinfo(op);
-        uint32_t mode = info & 15, kind = (info >> 4) & 3, cyc = (info >> 6) & 15, cls = info >> 10;
+        const uint32_t w = m.opinfo(op);
+        const uint32_t am = w & 7, kind = (w >> 5) & 3, grp = (w >> 13) & 31, data = w >> 18;
+        uint32_t cyc = (w >> 7) & 15;
+        uint32_t npc = (pc + ((w >> 11) & 3)) & 0xFFFF;
 
         // effective address
-        uint32_t ea = 0, npc;
+        uint32_t ea;
         {
-            uint32_t idx = (mode == M_ZPX || mode == M_ABX) ? x : ((mode == M_ZPY || mode == M_ABY || mode == M_INY) ? y : 0u);
-            if (mode >= M_ZP && mode <= M_ZPY) { ea = (b1 + idx) & 0xFF; }
-            else if (mode >= M_ABS && mode <= M_ABY) {
-                uint32_t base = b1 | (b2 << 8);
-                ea = (base + idx) & 0xFFFF;
-                if (kind == K_R && ((ea ^ base) & 0xFF00)) cyc++;
-            } else if (mode == M_INX) { ea = peek16zp(b1 + x); }
-            else if (mode == M_INY) {
+            uint32_t idx = (w & 8) ? x : ((w & 16) ? y : 0u);
+            if (am <= 3) {                                     // none / imm / zp-family / abs-family: branch-free
+                uint32_t base = b1 | (am == 3 ? b2 << 8 : 0u);
+                uint32_t full = base + idx;
+                ea = full & (am == 3 ? 0xFFFFu : 0xFFu);
+                cyc += ((am == 3 && kind == K_R) ? 1u : 0u) & ((full ^ base) >> 8);
+            } else if (am == 4) { ea = peek16zp(b1 + x); }
+            else if (am == 5) {
                 uint32_t base = peek16zp(b1);
-                ea = (base + idx) & 0xFFFF;
+                ea = (base + y) & 0xFFFF;
                 if (kind == K_R && ((ea ^ base) & 0xFF00)) cyc++;
-            } else if (mode == M_IND) {
+            } else if (am == 6) {
                 uint32_t ptr = b1 | (b2 << 8);
                 ea = peek(ptr) | (peek((ptr & 0xFF00) | ((ptr + 1) & 0xFF)) << 8);
-            }
-            uint32_t len = (mode == M_IMP || mode == M_ACC) ? 1u : ((mode == M_ABS || mode == M_ABX || mode == M_ABY || mode == M_IND) ? 3u : 2u);
-            npc = (pc + len) & 0xFFFF;
+            } else ea = 0;
         }
-        if (cls == C_BRA) {
-            // condition flag by opcode bits 7..6: N V C Z ; bit 5 = required value
-            uint32_t fsel = op >> 6;
-            uint32_t fbit = fsel == 0 ? FN : (fsel == 1 ? FV : (fsel == 2 ? FC : FZ));
-            bool want = (op & 0x20) != 0;
-            if (((p & fbit) != 0) == want) {
+        if (grp == G_BRANCH) {
+            uint32_t fsel = data & 3;
+            bool fset = fsel == 0 ? (zn & 0x180u) != 0 : (fsel == 1 ? (p & FV) != 0 : (fsel == 2 ? (p & FC) != 0 : (zn & 0xFFu) == 0));
+            if (fset == ((data & 4) != 0)) {
                 uint32_t t = (npc + (uint32_t)(int32_t)(int8_t)(uint8_t)b1) & 0xFFFF;
                 cyc += 1 + (((t ^ npc) & 0xFF00) ? 1u : 0u);
                 npc = t;
             }
         }
-
         wsync = false;
-        advance(cyc - 1);
 
-        uint32_t v = 0;
-        if (mode == M_IMM) v = b1;
-        else if (kind == K_R || kind == K_M) v = rd(ea);
-        else if (mode == M_ACC) v = a;
+        // read phase: one memory operand, or 1..3 stack pulls
+        uint32_t r0 = b1, r1 = 0, r2 = 0;
+        {
+            uint32_t npull = grp == G_PULL ? 1u : (grp == G_RTS ? 2u : (grp == G_RTI ? 3u : 0u));
+            uint32_t nrd = npull ? npull : (((kind & 1) && am != 1) ? 1u : 0u);
+            for (uint32_t i = 0; i < nrd; i++) {
+                uint32_t addr = ea;
+                if (npull) { sp = (sp + 1) & 0xFF; addr = 0x100 | sp; }
+                r2 = r1; r1 = r0;
+                r0 = bus_read(addr, cyc, w);
+            }
+        }
+        uint32_t v = (am == 0 && grp == G_SHIFT) ? a : r0;
 
-        bool wb = false;            // write v back to ea (or A for M_ACC)
-        switch (cls) {
-        case C_LDA: a = v; setnz(v); break;
-        case C_LDX: x = v; setnz(v); break;
-        case C_LDY: y = v; setnz(v); break;
-        case C_LAX: a = x = v; setnz(v); break;
-        case C_STA: wr(ea, a); break;
-        case C_STX: wr(ea, x); break;
-        case C_STY: wr(ea, y); break;
-        case C_SAX: wr(ea, a & x); break;
-        case C_TAX: x = a; setnz(x); break;
-        case C_TAY: y = a; setnz(y); break;
-        case C_TXA: a = x; setnz(a); break;
-        case C_TYA: a = y; setnz(a); break;
-        case C_TSX: x = sp; setnz(x); break;
-        case C_TXS: sp = x; break;
-        case C_PHA: push(a); break;
-        case C_PHP: push(p | FB | FU); break;
-        case C_PLA: a = pull(); setnz(a); break;
-        case C_PLP: p = (pull() & ~(uint32_t)FB) | FU; break;
-        case C_AND: a &= v; setnz(a); break;
-        case C_ORA: a |= v; setnz(a); break;
-        case C_EOR: a ^= v; setnz(a); break;
-        case C_ADC: adc(v); break;
-        case C_SBC: sbc(v); break;
-        case C_CMP: cmp(a, v); break;
-        case C_CPX: cmp(x, v); break;
-        case C_CPY: cmp(y, v); break;
-        case C_BIT: p = (p & ~(uint32_t)(FN | FV | FZ)) | (v & 0xC0) | ((v & a) ? 0u : (uint32_t)FZ); break;
-        case C_ASL: v = asl(v); wb = true; break;
-        case C_LSR: v = lsr(v); wb = true; break;
-        case C_ROL: v = rol(v); wb = true; break;
-        case C_ROR: v = ror(v); wb = true; break;
-        case C_INC: v = (v + 1) & 0xFF; setnz(v); wb = true; break;
-        case C_DEC: v = (v - 1) & 0xFF; setnz(v); wb = true; break;
-        case C_INX: x = (x + 1) & 0xFF; setnz(x); break;
-        case C_INY: y = (y + 1) & 0xFF; setnz(y); break;
-        case C_DEX: x = (x - 1) & 0xFF; setnz(x); break;
-        case C_DEY: y = (y - 1) & 0xFF; setnz(y); break;
-        case C_CLC: p &= ~(uint32_t)FC; break;
-        case C_SEC: p |= FC; break;
-        case C_CLI: p &= ~(uint32_t)FI; break;
-        case C_SEI: p |= FI; break;
-        case C_CLV: p &= ~(uint32_t)FV; break;
-        case C_CLD: p &= ~(uint32_t)FD; break;
-        case C_SED: p |= FD; break;
-        case C_JMP: npc = ea; break;
-        case C_JSR: { uint32_t ret = (pc + 2) & 0xFFFF; push(ret >> 8); push(ret & 0xFF); npc = ea; break; }
-        case C_RTS: { uint32_t lo = pull(); uint32_t hi = pull(); npc = (((hi << 8) | lo) + 1) & 0xFFFF; break; }
-        case C_RTI: { p = (pull() & ~(uint32_t)FB) | FU; uint32_t lo = pull(); uint32_t hi = pull(); npc = (hi << 8) | lo; break; }
-        case C_BRK: {
+        // execute: registers only; memory results are queued in w0..w2
+        uint32_t nwr = 0, w0 = 0, w1 = 0, w2 = 0;
+        bool wpush = false;
+        switch (grp) {
+        case G_LOAD:
+            if (data & 1) a = v;
+            if (data & 2) x = v;
+            if (data & 4) y = v;
+            zn = v; break;
+        case G_STORE:
+            w0 = ((data & 1) ? a : 0xFFu) & ((data & 2) ? x : 0xFFu) & ((data & 4) ? y : 0xFFu);
+            nwr = 1; break;
+        case G_XFER: {
+            uint32_t s = data & 3, d = (data >> 2) & 3;
+            uint32_t val = s == 0 ? a : (s == 1 ? x : (s == 2 ? y : sp));
+            if (d == 0) a = val; else if (d == 1) x = val; else if (d == 2) y = val; else sp = val;
+            if (data & 16) zn = val;
+            break; }
+        case G_PUSH: w0 = data ? (get_p() | FB) : a; nwr = 1; wpush = true; break;
+        case G_PULL: if (data) set_p(r0); else { a = r0; zn = r0; } break;
+        case G_LOGIC: a = data == 0 ? (a & v) : (data == 1 ? (a | v) : (a ^ v)); zn = a; break;
+        case G_ADC: adc(v); break;
+        case G_SBC: sbc(v); break;
+        case G_CMP: cmp(data == 0 ? a : (data == 1 ? x : y), v); break;
+        case G_BIT: p = (p & ~(uint32_t)FV) | (v & FV); zn = (v & a) | ((v & 0x80) << 1); break;
+        case G_SHIFT: {
+            uint32_t r = shift(v, data);
+            if (am == 0) a = r; else { w0 = r; nwr = 1; }
+            break; }
+        case G_INCDEC_MEM: w0 = (v + data) & 0xFF; zn = w0; nwr = 1; break;
+        case G_INCDEC_REG: {
+            uint32_t d = data >> 2;
+            if (data & 1) { x = (x + d) & 0xFF; zn = x; } else { y = (y + d) & 0xFF; zn = y; }
+            break; }
+        case G_FLAG: p = (data & 256) ? (p | (data & 0xFF)) : (p & ~(data & 0xFF)); break;
+        case G_JMP: npc = ea; break;
+        case G_JSR: { uint32_t ret = (pc + 2) & 0xFFFF; w0 = ret >> 8; w1 = ret & 0xFF; nwr = 2; wpush = true; npc = ea; break; }
+        case G_RTS: npc = (((r0 << 8) | r1) + 1) & 0xFFFF; break;          // r1 = low byte (pulled first), r0 = high
+        case G_RTI: set_p(r2); npc = (r0 << 8) | r1; break;
+        case G_BRK: {
             uint32_t ret = (pc + 2) & 0xFFFF;
-            push(ret >> 8); push(ret & 0xFF); push(p | FB | FU);
+            w0 = ret >> 8; w1 = ret & 0xFF; w2 = get_p() | FB; nwr = 3; wpush = true;
             p |= FI;
             npc = peek(0xFFFE) | (peek(0xFFFF) << 8);
             break; }
-        case C_DCP: v = (v - 1) & 0xFF; wr(ea, v); cmp(a, v); break;
-        case C_ISC: v = (v + 1) & 0xFF; wr(ea, v); sbc(v); break;
-        case C_SLO: v = asl(v); wr(ea, v); a |= v; setnz(a); break;
-        case C_RLA: v = rol(v); wr(ea, v); a &= v; setnz(a); break;
-        case C_SRE: v = lsr(v); wr(ea, v); a ^= v; setnz(a); break;
-        case C_RRA: v = ror(v); wr(ea, v); adc(v); break;
-        case C_ANC: a &= v; setnz(a); p = (p & ~(uint32_t)FC) | (a >> 7); break;
-        case C_ALR: a &= v; a = lsr(a); break;
-        case C_SBX: { uint32_t t = (a & x) - v; p &= ~(uint32_t)FC; if (!(t & 0x100)) p |= FC; x = t & 0xFF; setnz(x); break; }
-        default: break;     // C_NOP, C_BRA (resolved above)
+        case G_RMW_ALU:
+            switch (data) {
+            case 0: w0 = shift(v, 0); a |= w0; zn = a; break;                               // SLO
+            case 1: w0 = shift(v, 2); a &= w0; zn = a; break;                               // RLA
+            case 2: w0 = shift(v, 1); a ^= w0; zn = a; break;                               // SRE
+            case 3: w0 = shift(v, 3); adc(w0); break;                                       // RRA
+            case 4: w0 = (v - 1) & 0xFF; cmp(a, w0); break;                                 // DCP
+            default: w0 = (v + 1) & 0xFF; sbc(w0); break;                                   // ISC
+            }
+            nwr = 1; break;
+        case G_ANC: a &= v; zn = a; p = (p & ~(uint32_t)FC) | (a >> 7); break;
+        case G_ALR: a = shift(a & v, 1); break;
+        case G_SBX: { uint32_t t = (a & x) - v; p = (p & ~(uint32_t)FC) | (((t >> 8) & 1u) ^ 1u); x = t & 0xFF; zn = x; break; }
+        default: break;     // G_NOP, G_BRANCH (resolved above)
         }
-        if (wb) { if (mode == M_ACC) a = v; else wr(ea, v); }
 
+        // write phase
+        for (uint32_t i = 0; i < nwr; i++) {
+            uint32_t addr = ea;
+            if (wpush) { addr = 0x100 | sp; sp = (sp - 1) & 0xFF; }
+            bus_write(addr, w0, cyc);
+            w0 = w1; w1 = w2;
+        }
+
+        // retire
         pc = npc;
-        advance(1);
-        if (wsync && hcyc != 0) advance(STM_CYC_PER_LINE - hcyc);
+        hcyc += (int32_t)cyc;
+        timer -= (int32_t)cyc;
+        if (hcyc >= STM_CYC_PER_LINE) { end_line(); hcyc -= STM_CYC_PER_LINE; }
+        if (wsync && hcyc != 0) { timer -= STM_CYC_PER_LINE - hcyc; end_line(); hcyc = 0; }
     }
 
     // ---------------- one emulated frame ----------------
@@ -783,7 +948,8 @@ struct Emu {
         if (want_pixels) {
             int r0 = (int)end_line_no - STM_YSTART; if (r0 < 0) r0 = 0;
             for (int r = r0; r < STM_VIS_H; r++)
-                for (uint32_t g = 0; g < 40; g++) m.px4((uint32_t)r, g, 0);
+                if (row_sampled(r))
+                    for (uint32_t g = 0; g < 40; g++) m.px4((uint32_t)r, g, 0);
         }
         m.st32(O_FRAME, m.ld32(O_FRAME) + 1);
     }

@@ -514,7 +514,7 @@ int stm_ctx_create(stm_ctx **out, const stm_game_desc *desc, const uint8_t *rom,
     ctx->rom_words = desc->rom_size / 4;
     ctx->reset_pc = rom[0xFFC & gp.rom_mask] | (rom[0xFFD & gp.rom_mask] << 8);   // power-on bank is 0
     uint32_t lut[256];
-    build_decode_table(lut);
+    build_hot_table(lut);
     int rc = STM_OK;
     auto body = [&]() -> int {
         CUDA_TRY(ctx, cudaSetDevice(device));

@@ -43,7 +43,7 @@ void hc_decode_table(uint32_t *out) { stm::build_decode_table(out); }
 void hc_frame(const stm_game_desc *d, const uint8_t *rom, uint8_t *blob, int ale_action, uint8_t *fb,
               int episodic_life, float weight, uint8_t *done, float *reward, int32_t *lives)
 {
-    if (!g_lut_ok) { stm::build_decode_table(g_lut); g_lut_ok = true; }
+    if (!g_lut_ok) { stm::build_hot_table(g_lut); g_lut_ok = true; }
     stm::GameParams gp; hc_fill_params(&gp, d);
     HostMem m{blob, rom, g_lut, fb};
     stm::Emu<HostMem> e(m, gp);
@@ -59,7 +59,7 @@ void hc_frame(const stm_game_desc *d, const uint8_t *rom, uint8_t *blob, int ale
 
 void hc_exec_one(const stm_game_desc *d, const uint8_t *rom, uint8_t *blob)
 {
-    if (!g_lut_ok) { stm::build_decode_table(g_lut); g_lut_ok = true; }
+    if (!g_lut_ok) { stm::build_hot_table(g_lut); g_lut_ok = true; }
     stm::GameParams gp; hc_fill_params(&gp, d);
     HostMem m{blob, rom, g_lut, nullptr};
     stm::Emu<HostMem> e(m, gp);
