@@ -23,9 +23,11 @@
 #ifdef __CUDACC__
 #define STM_DEV __device__ __forceinline__          /* member functions */
 #define STM_FN  __device__ __forceinline__          /* free functions   */
+#define STM_WARP_ALL(mask, pred) __all_sync((mask), (pred))
 #else
 #define STM_DEV inline
 #define STM_FN  static inline
+#define STM_WARP_ALL(mask, pred) (pred)
 #endif
 
 namespace stm {
@@ -310,8 +312,9 @@ STM_FN uint32_t sel_bytes(uint32_t under, uint32_t over, uint32_t m) { return (u
 //   uint32_t ld8(off) / void st8(off, v) / ld16 / st16 / ld32 / st32     blob access (off = byte offset)
 //   uint32_t rom8(idx), rom32(word_idx)                                    cartridge image
 //   uint32_t opinfo(op)                                                    hot decode word (build_hot_table)
-//   void px4(row, g, word)   store 4 pixels (colour indices) of native row `row`, group g (0..39)
-//   void px1(row, x, v)      store 1 pixel
+//   void px16(row, q, w0..w3) store 16 pixels of native row `row`, quad q (0..9): four packed words
+//   void px4(row, g, word)    store 4 pixels (colour indices), group g (0..39)
+//   void px1(row, x, v)       store 1 pixel
 //
 // One instruction = fetch -> decode -> address -> read phase -> execute (register-only switch over
 // ~25 groups) -> write phase -> retire.  Every memory access goes through ONE read site and ONE
@@ -423,6 +426,70 @@ struct Emu {
     // are not drawn at all; nothing downstream reads them.
     STM_DEV static bool row_sampled(int row) { return (uint32_t)row < (uint32_t)STM_VIS_H && (row % 5) != 2; }
 
+    // four pixels (one nibble of every layer mask) -> four packed colour bytes
+    STM_DEV uint32_t compose4(uint32_t l0, uint32_t l1, uint32_t blm, uint32_t pfm, uint32_t sh, uint32_t c_p0,
+                              uint32_t c_p1, uint32_t c_pf, uint32_t c_bk, uint32_t pfcol, bool pfp)
+    {
+        uint32_t b0 = nib_to_bytes(l0 >> sh), b1 = nib_to_bytes(l1 >> sh);
+        uint32_t bb = nib_to_bytes(blm >> sh), bf = nib_to_bytes(pfm >> sh);
+        uint32_t word = c_bk;
+        if (pfp) {
+            word = sel_bytes(word, c_p1, b1); word = sel_bytes(word, c_p0, b0);
+            word = sel_bytes(word, c_pf, bf | bb);
+        } else {
+            word = sel_bytes(word, pfcol, bf); word = sel_bytes(word, c_pf, bb);
+            word = sel_bytes(word, c_p1, b1);  word = sel_bytes(word, c_p0, b0);
+        }
+        return word;
+    }
+    // draw pixels [lo,hi) of word w (32 px).  A word holding only playfield/background (the usual
+    // case) costs one select per 4-pixel column and is stored 16 pixels at a time.
+    STM_DEV void emit_word(int row, int w, int lo, int hi, uint32_t seg, uint32_t l0, uint32_t l1, uint32_t blm,
+                           uint32_t pfm, uint32_t c_p0, uint32_t c_p1, uint32_t c_pf, uint32_t c_bk, bool pfp,
+                           bool score, bool comb)
+    {
+        const bool plain = (l0 | l1 | blm) == 0;
+        #pragma unroll 1
+        for (int q = 0; q < 2; q++) {                          // two 16-pixel quads per word
+            int qlo = 16 * q, qhi = qlo + 16;
+            if (hi <= qlo || lo >= qhi) continue;
+            uint32_t wd[4];
+            #pragma unroll
+            for (int j = 0; j < 4; j++) {
+                uint32_t sh = (uint32_t)(qlo + 4 * j);
+                uint32_t pfcol = score ? ((32 * w + (int)sh) < 80 ? c_p0 : c_p1) : c_pf;
+                uint32_t word = plain ? (((pfm >> sh) & 0xFu) ? pfcol : c_bk)
+                                      : compose4(l0, l1, blm, pfm, sh, c_p0, c_p1, c_pf, c_bk, pfcol, pfp);
+                if (comb && w == 0 && q == 0 && j < 2) word = 0;
+                wd[j] = word;
+            }
+            if (((seg >> qlo) & 0xFFFFu) == 0xFFFFu) m.px16((uint32_t)row, (uint32_t)(2 * w + q), wd[0], wd[1], wd[2], wd[3]);
+            else {
+                #pragma unroll 1
+                for (int j = 0; j < 4; j++) {
+                    uint32_t nm = (seg >> (qlo + 4 * j)) & 0xFu;
+                    uint32_t g = 8u * (uint32_t)w + 4u * (uint32_t)q + (uint32_t)j;
+                    if (nm == 0xFu) m.px4((uint32_t)row, g, wd[j]);
+                    else for (uint32_t k = 0; k < 4; k++)
+                        if (nm & (1u << k)) m.px1((uint32_t)row, 4u * g + k, (wd[j] >> (8u * k)) & 0xFFu);
+                }
+            }
+        }
+    }
+    // a span of pixels drawn in one colour pattern (used for blanked lines)
+    STM_DEV void emit_span(int row, uint32_t x0, uint32_t x1, uint32_t, uint32_t, uint32_t, uint32_t, uint32_t,
+                           uint32_t, uint32_t, uint32_t, bool, bool, bool, bool)
+    {
+        int w0 = (int)(x0 >> 5), w1 = (int)((x1 - 1) >> 5);
+        #pragma unroll 1
+        for (int w = w0; w <= w1; w++) {
+            int lo = (int)x0 - 32 * w; if (lo < 0) lo = 0;
+            int hi = (int)x1 - 32 * w; if (hi > 32) hi = 32;
+            uint32_t seg = (hi == 32 ? 0xFFFFFFFFu : ((1u << hi) - 1u)) & ~((1u << lo) - 1u);
+            emit_word(row, w, lo, hi, seg, 0, 0, 0, 0, 0, 0, 0, 0, false, false, false);
+        }
+    }
+
     STM_DEV void catchup(uint32_t xe)
     {
         if (xe > STM_VIS_W) xe = STM_VIS_W;
@@ -442,16 +509,7 @@ struct Emu {
 
         int w0 = (int)(rx >> 5), w1 = (int)((xe - 1) >> 5);
         if (draw && vb) {                                    // blanked line: black pixels, no collisions
-            for (int w = w0; w <= w1; w++) {
-                int lo = (int)rx - 32 * w; if (lo < 0) lo = 0;
-                int hi = (int)xe - 32 * w; if (hi > 32) hi = 32;
-                for (int n = lo >> 2; n <= (hi - 1) >> 2; n++) {
-                    int l4 = lo - 4 * n, h4 = hi - 4 * n;
-                    uint32_t g = 8u * (uint32_t)w + (uint32_t)n;
-                    if (l4 <= 0 && h4 >= 4) m.px4((uint32_t)row, g, 0);
-                    else for (int k = l4 < 0 ? 0 : l4; k < (h4 > 4 ? 4 : h4); k++) m.px1((uint32_t)row, 4u * g + (uint32_t)k, 0);
-                }
-            }
+            emit_span(row, rx, xe, 0, 0, 0, 0, 0, 0, 0, 0, false, false, false, true);
             rx = xe;
             return;
         }
@@ -477,6 +535,7 @@ struct Emu {
             c_p0 = (m.ld8(O_COLUP0) >> 1) * 0x01010101u; c_p1 = (m.ld8(O_COLUP1) >> 1) * 0x01010101u;
             c_pf = (m.ld8(O_COLUPF) >> 1) * 0x01010101u; c_bk = (m.ld8(O_COLUBK) >> 1) * 0x01010101u;
         }
+        #pragma unroll 1
         for (int w = w0; w <= w1; w++) {
             int lo = (int)rx - 32 * w; if (lo < 0) lo = 0;
             int hi = (int)xe - 32 * w; if (hi > 32) hi = 32;
@@ -509,38 +568,8 @@ struct Emu {
                     if (p0m & p1m) cx |= 1u << 15;
                 }
             }
-            if (draw) {
-                bool plain = (l0 | l1 | blm) == 0;            // only playfield / background in this word
-                for (int n = lo >> 2; n <= (hi - 1) >> 2; n++) {
-                    uint32_t sh = 4u * (uint32_t)n;
-                    uint32_t pfcol = score ? ((32 * w + (int)sh) < 80 ? c_p0 : c_p1) : c_pf;
-                    uint32_t word;
-                    if (plain) {
-                        // playfield columns are 4 px wide and aligned: the nibble is all-or-nothing
-                        // inside the segment, so a byte mask from the (already seg-masked) nibble is exact
-                        word = sel_bytes(c_bk, pfcol, nib_to_bytes(pfm >> sh));
-                    } else {
-                        uint32_t b0 = nib_to_bytes(l0 >> sh), b1 = nib_to_bytes(l1 >> sh);
-                        uint32_t bb = nib_to_bytes(blm >> sh), bf = nib_to_bytes(pfm >> sh);
-                        word = c_bk;
-                        if (pfp) {
-                            word = sel_bytes(word, c_p1, b1); word = sel_bytes(word, c_p0, b0);
-                            word = sel_bytes(word, c_pf, bf | bb);
-                        } else {
-                            word = sel_bytes(word, pfcol, bf); word = sel_bytes(word, c_pf, bb);
-                            word = sel_bytes(word, c_p1, b1);  word = sel_bytes(word, c_p0, b0);
-                        }
-                    }
-                    if (comb && w == 0 && n < 2) word = 0;
-                    uint32_t nm = (seg >> sh) & 0xFu;
-                    uint32_t g = 8u * (uint32_t)w + (uint32_t)n;
-                    if (nm == 0xFu) m.px4((uint32_t)row, g, word);
-                    else {
-                        for (uint32_t k = 0; k < 4; k++)
-                            if (nm & (1u << k)) m.px1((uint32_t)row, 4u * g + k, (word >> (8u * k)) & 0xFFu);
-                    }
-                }
-            }
+            if (draw)
+                emit_word(row, w, lo, hi, seg, l0, l1, blm, pfm, c_p0, c_p1, c_pf, c_bk, pfp, score, comb);
         }
         if (cx) m.st16(O_CX, m.ld16(O_CX) | cx);
         rx = xe;
@@ -794,7 +823,10 @@ struct Emu {
     }
 
     // ---------------- one instruction ----------------
-    STM_DEV void exec_one()
+    // Returns true when the instruction ran past the end of the scanline (or strobed WSYNC): the
+    // caller must then call finish_line().  Keeping the line wrap out of here lets the step kernel
+    // run all lanes of a warp to the end of their scanline and wrap — i.e. render — them together.
+    STM_DEV bool exec_core()
     {
         // fetch: opcode + two operand bytes
         uint32_t op, b1, b2;
@@ -933,23 +965,42 @@ struct Emu {
         pc = npc;
         hcyc += (int32_t)cyc;
         timer -= (int32_t)cyc;
+        return hcyc >= STM_CYC_PER_LINE || wsync;
+    }
+    STM_DEV void finish_line()
+    {
         if (hcyc >= STM_CYC_PER_LINE) { end_line(); hcyc -= STM_CYC_PER_LINE; }
         if (wsync && hcyc != 0) { timer -= STM_CYC_PER_LINE - hcyc; end_line(); hcyc = 0; }
+        wsync = false;
     }
+    STM_DEV void exec_one() { if (exec_core()) finish_line(); }
 
     // ---------------- one emulated frame ----------------
     // Rows the frame never reached are zero-filled, as the oracle does.
-    STM_DEV void run_frame(uint32_t ale_action, bool want_pixels)
+    // `lanes` = the warp lanes that run frames together (ballot of live envs); every one of them must
+    // call run_frame the same number of times.  Scanline lock-step: each lane runs instructions until
+    // its scanline ends, then the warp reconverges and wraps the line (the whole-line catch-up render)
+    // with all lanes active; lanes whose frame is over idle until the slowest lane's frame is over.
+    STM_DEV void run_frame(uint32_t ale_action, bool want_pixels, uint32_t lanes = 0xFFFFFFFFu)
     {
+        (void)lanes;
         render = want_pixels;
         set_action(ale_action);
         flags &= ~(uint32_t)STM_F_FRAME_DONE;
-        while (!(flags & STM_F_FRAME_DONE)) exec_one();
+        bool over = false;
+        do {
+            if (!over) {
+                bool ended = false;
+                while (!ended && !(flags & STM_F_FRAME_DONE)) ended = exec_core();
+                if (ended) finish_line();
+                over = (flags & STM_F_FRAME_DONE) != 0;
+            }
+        } while (!STM_WARP_ALL(lanes, over));
         if (want_pixels) {
             int r0 = (int)end_line_no - STM_YSTART; if (r0 < 0) r0 = 0;
             for (int r = r0; r < STM_VIS_H; r++)
                 if (row_sampled(r))
-                    for (uint32_t g = 0; g < 40; g++) m.px4((uint32_t)r, g, 0);
+                    for (uint32_t q = 0; q < 10; q++) m.px16((uint32_t)r, q, 0, 0, 0, 0);
         }
         m.st32(O_FRAME, m.ld32(O_FRAME) + 1);
     }

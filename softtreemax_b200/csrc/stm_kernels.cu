@@ -8,11 +8,11 @@
 // Data layout in HBM
 //   env pool      : n x 256 B state blobs (include/stm_state.h), rewards f32, done u8, lives i32
 //   obs stacks    : n x 4 x 84 x 84 u8
-//   native scratch: per tile of 32 envs, [frame 0..1][row 0..209][group 0..39][lane 0..31] u32,
-//                   one u32 = 4 horizontally adjacent pixels (7-bit colour indices) of one env.
-//                   Lane-minor, so that a warp whose lanes draw the same 4-pixel group of the same
-//                   row (the common case: siblings run the same display kernel in near lock-step)
-//                   issues ONE coalesced 128-byte store, and K3 reads it back coalesced.
+//   native scratch: per tile of 32 envs, [frame 0..1][row 0..209][quad 0..9][lane 0..31] uint4,
+//                   one uint4 = 16 horizontally adjacent pixels (7-bit colour indices) of one env.
+//                   Lane-minor, so that a warp whose lanes draw the same quad of the same row (the
+//                   usual case: K2 wraps scanlines in warp lock-step) issues ONE coalesced 512-byte
+//                   store, and K3 reads it back coalesced.
 #include <cuda_runtime.h>
 #include <cstdarg>
 #include <cstdio>
@@ -193,10 +193,14 @@ struct DevMem {
     __device__ __forceinline__ uint32_t rom8(uint32_t i) const { return (rom[i >> 2] >> ((i & 3) * 8)) & 0xFFu; }
     __device__ __forceinline__ uint32_t rom32(uint32_t wi) const { return rom[wi]; }
     __device__ __forceinline__ uint32_t opinfo(uint32_t op) const { return lut[op]; }
-    __device__ __forceinline__ void px4(uint32_t row, uint32_t g, uint32_t w)
-    { scr[((fsel * STM_VIS_H + row) * 40 + g) * kTileEnvs] = w; }
+    // scr points at this lane's uint4 slot of (frame 0, row 0, quad 0); quads are kTileEnvs uint4 apart
+    __device__ __forceinline__ uint32_t *quad(uint32_t row, uint32_t q) const
+    { return scr + (size_t)((fsel * STM_VIS_H + row) * 10 + q) * (kTileEnvs * 4); }
+    __device__ __forceinline__ void px16(uint32_t row, uint32_t q, uint32_t a, uint32_t b, uint32_t c, uint32_t d)
+    { *reinterpret_cast<uint4 *>(quad(row, q)) = make_uint4(a, b, c, d); }
+    __device__ __forceinline__ void px4(uint32_t row, uint32_t g, uint32_t w) { quad(row, g >> 2)[g & 3] = w; }
     __device__ __forceinline__ void px1(uint32_t row, uint32_t x, uint32_t v)
-    { ((uint8_t *)&scr[((fsel * STM_VIS_H + row) * 40 + (x >> 2)) * kTileEnvs])[x & 3] = (uint8_t)v; }
+    { reinterpret_cast<uint8_t *>(quad(row, x >> 4))[x & 15] = (uint8_t)v; }
 };
 
 struct StepArgs {
@@ -228,15 +232,17 @@ stm_step_kernel(const StepArgs a)
         }
     }
     __syncthreads();
+    uint32_t done = valid ? a.done[env] : 1u;
+    // lanes that emulate; they advance scanline by scanline in lock-step (Emu::run_frame)
+    const uint32_t lanes = __ballot_sync(0xFFFFFFFFu, valid && !done);
     if (!valid) return;
-    uint32_t done = a.done[env];
     if (a.stepped) a.stepped[env] = done ? 0 : 1;
     if (done) return;                                    // frozen env: nothing changes
 
     DevMem m;
     m.blob = reinterpret_cast<uint8_t *>(sblob + tid);
     m.rom = srom; m.lut = slut;
-    m.scr = a.scratch ? a.scratch + (size_t)(env / kTileEnvs) * kTileWords + (env % kTileEnvs) : nullptr;
+    m.scr = a.scratch ? a.scratch + (size_t)(env / kTileEnvs) * kTileWords + (env % kTileEnvs) * 4 : nullptr;
     m.fsel = 0;
     Emu<DevMem> e(m, a.gp);
     e.load();
@@ -248,7 +254,7 @@ stm_step_kernel(const StepArgs a)
         bool want = a.render && f >= a.frameskip - 2;
         // the newest frame always goes to slot 1, the one before it to slot 0
         m.fsel = (f == a.frameskip - 1) ? 1u : 0u;
-        e.run_frame(ale, want);
+        e.run_frame(ale, want, lanes);
         int r = e.get_data(a.episodic_life != 0, done, lives);
         rew = __fadd_rn(rew, __fmul_rn(a.weight, (float)r));
     }
@@ -291,14 +297,15 @@ stm_frames_kernel(const uint32_t *__restrict__ scratch, const uint8_t *__restric
     if (tid < 128) sgray[tid] = c_gray[tid];
     const int ny = 10 * oy + 3, y0 = ny >> 2, fy = ny & 3;
     const int y1 = min(y0 + 1, STM_VIS_H - 1);
-    const uint32_t *tbase = scratch + (size_t)tile * kTileWords;
-    for (int i = tid; i < 4 * 40 * kTileEnvs; i += kFrameThreads) {
-        int lane = i & 31, g = (i >> 5) % 40, rs = i / (40 * 32);
+    const uint4 *tbase = reinterpret_cast<const uint4 *>(scratch + (size_t)tile * kTileWords);
+    for (int i = tid; i < 4 * 10 * kTileEnvs; i += kFrameThreads) {
+        int lane = i & 31, q = (i >> 5) % 10, rs = i / (10 * 32);
         int frame = rs >> 1, row = (rs & 1) ? y1 : y0;
-        uint32_t v = 0;
+        uint4 v = make_uint4(0, 0, 0, 0);
         if (frame >= 2 - nframes)        // with a single rendered frame only slot 1 holds data
-            v = tbase[((size_t)(frame * STM_VIS_H + row) * 40 + g) * kTileEnvs + lane];
-        srows[rs][lane * kPitch + g] = v;
+            v = tbase[((size_t)(frame * STM_VIS_H + row) * 10 + q) * kTileEnvs + lane];
+        uint32_t *d = &srows[rs][lane * kPitch + 4 * q];
+        d[0] = v.x; d[1] = v.y; d[2] = v.z; d[3] = v.w;
     }
     __syncthreads();
     // new frame -> child[env][3][oy][:]

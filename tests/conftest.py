@@ -28,7 +28,7 @@ def host_core():
     so = os.path.join(d, "libhost_core.so")
     srcs = [os.path.join(d, "host_core.cpp"), os.path.join(ROOT, "softtreemax_b200", "csrc", "emu_core.cuh")]
     if not os.path.exists(so) or any(os.path.getmtime(s) > os.path.getmtime(so) for s in srcs):
-        subprocess.check_call(["/usr/bin/g++", "-O2", "-std=c++17", "-fPIC", "-shared", "-ffp-contract=off",
+        subprocess.check_call(["/usr/bin/g++", "-O2", "-std=c++17", "-fPIC", "-shared", "-ffp-contract=off", "-Wno-unknown-pragmas",
                                "-o", so, srcs[0]])
     return C.CDLL(so)
 

@@ -18,6 +18,8 @@ struct HostMem {
     uint32_t rom32(uint32_t wi) const { uint32_t v; memcpy(&v, rom + 4 * wi, 4); return v; }
     uint32_t opinfo(uint32_t op) const { return lut[op]; }
     void px4(uint32_t row, uint32_t g, uint32_t w) { if (fb) memcpy(fb + row * 160 + 4 * g, &w, 4); }
+    void px16(uint32_t row, uint32_t q, uint32_t a, uint32_t b, uint32_t c, uint32_t d)
+    { px4(row, 4 * q, a); px4(row, 4 * q + 1, b); px4(row, 4 * q + 2, c); px4(row, 4 * q + 3, d); }
     void px1(uint32_t row, uint32_t x, uint32_t v) { if (fb) fb[row * 160 + x] = (uint8_t)v; }
 };
 uint32_t g_lut[256];
