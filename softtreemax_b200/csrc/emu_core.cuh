@@ -23,11 +23,18 @@
 #ifdef __CUDACC__
 #define STM_DEV __device__ __forceinline__          /* member functions */
 #define STM_FN  __device__ __forceinline__          /* free functions   */
+#define STM_NOINLINE __device__ __noinline__
 #define STM_WARP_ALL(mask, pred) __all_sync((mask), (pred))
+#define STM_WARP_MIN(mask, v) __reduce_min_sync((mask), (v))
 #else
 #define STM_DEV inline
 #define STM_FN  static inline
+#define STM_NOINLINE static
 #define STM_WARP_ALL(mask, pred) (pred)
+#define STM_WARP_MIN(mask, v) (v)
+#endif
+#ifndef STM_MINPC
+#define STM_MINPC 0      /* 1: lowest-program-counter-first lane scheduling inside a scanline */
 #endif
 
 namespace stm {
@@ -236,6 +243,20 @@ static inline void build_hot_table(uint32_t *t)
     for (uint32_t op = 0; op < 256; op++) t[op] = encode_hot(e[op], op);
 }
 
+// predecoded cartridge: entry[off] = { hot word of rom[off], rom[off+1] | rom[off+2] << 8 } with the
+// operand offsets wrapped inside the bank window (window = mask + 1 bytes), as the bus would see them
+static inline void build_predecode(const uint8_t *rom, uint32_t rom_size, uint32_t mask, uint32_t *out /* 2 * rom_size */)
+{
+    uint32_t hot[256];
+    build_hot_table(hot);
+    for (uint32_t off = 0; off < rom_size; off++) {
+        uint32_t win = off & ~mask;
+        uint32_t o1 = win | ((off + 1) & mask), o2 = win | ((off + 2) & mask);
+        out[2 * off] = hot[rom[off]];
+        out[2 * off + 1] = rom[o1] | ((uint32_t)rom[o2] << 8);
+    }
+}
+
 // ---- game constants handed to the kernel ---------------------------------------------------------
 struct GameParams {
     uint32_t rom_mask;        // byte mask inside one bank window (0x7FF / 0xFFF)
@@ -307,86 +328,21 @@ STM_FN uint32_t nib_to_bytes(uint32_t n)
 }
 STM_FN uint32_t sel_bytes(uint32_t under, uint32_t over, uint32_t m) { return (under & ~m) | (over & m); }
 
-// ---- the per-env machine ---------------------------------------------------------------------------
-// M must provide:
-//   uint32_t ld8(off) / void st8(off, v) / ld16 / st16 / ld32 / st32     blob access (off = byte offset)
-//   uint32_t rom8(idx), rom32(word_idx)                                    cartridge image
-//   uint32_t opinfo(op)                                                    hot decode word (build_hot_table)
-//   void px16(row, q, w0..w3) store 16 pixels of native row `row`, quad q (0..9): four packed words
-//   void px4(row, g, word)    store 4 pixels (colour indices), group g (0..39)
-//   void px1(row, x, v)       store 1 pixel
-//
-// One instruction = fetch -> decode -> address -> read phase -> execute (register-only switch over
-// ~25 groups) -> write phase -> retire.  Every memory access goes through ONE read site and ONE
-// write site, so the TIA/RIOT slow paths (and the big catch-up renderer behind them) exist once in
-// the kernel instead of once per opcode; stack pulls/pushes are sequenced through the same sites.
+
+// Rows of the 210-row native frame that the 84x84 bilinear resize never samples (row % 5 == 2)
+// are not drawn at all; nothing downstream reads them.
+STM_FN bool row_sampled(int row) { return (uint32_t)row < (uint32_t)STM_VIS_H && (row % 5) != 2; }
+
+// ---- TIA line renderer --------------------------------------------------------------------------
+// Renders pixels [rx, xe) of the current scanline from the TIA registers in the state blob and
+// latches collisions.  It is the one large piece of code in the step kernel, so it is compiled
+// OUT OF LINE (a real call, arguments by value in registers): the instruction loop that calls it
+// then fits the instruction cache, and its five call sites share one copy.
 template <class M>
-struct Emu {
-    M &m;
-    const GameParams &gp;
-    // hot state (registers)
-    uint32_t pc, a, x, y, sp;
-    uint32_t p;             // C, I, D, V only (mask 0x4D); N and Z live in zn
-    uint32_t zn;            // Z <=> (zn & 0xFF) == 0 ; N <=> (zn & 0x180) != 0
-    int32_t  hcyc;          // CPU cycle in the line; may be transiently negative inside an instruction
-    int32_t  timer;
-    uint32_t bank;
-    // warm state
-    uint32_t line, rx, flags, end_line_no;
-    bool     render, wsync;
-
-    STM_DEV Emu(M &mm, const GameParams &g) : m(mm), gp(g) {}
-
-    STM_DEV uint32_t get_p() const
-    { return (p & 0x4Du) | FU | ((zn & 0x180u) ? (uint32_t)FN : 0u) | ((zn & 0xFFu) ? 0u : (uint32_t)FZ); }
-    STM_DEV void set_p(uint32_t v) { p = v & 0x4Du; zn = ((v & FN) << 1) | ((v & FZ) ? 0u : 1u); }
-
-    STM_DEV void load()
-    {
-        pc = m.ld16(O_PC); a = m.ld8(O_A); x = m.ld8(O_X); y = m.ld8(O_Y); sp = m.ld8(O_SP); set_p(m.ld8(O_P));
-        bank = m.ld8(O_BANK); line = m.ld16(O_LINE); hcyc = (int32_t)m.ld8(O_HCYC); rx = m.ld8(O_RX);
-        flags = m.ld8(O_FLAGS); timer = (int32_t)m.ld32(O_TIMER);
-        render = false; end_line_no = 0; wsync = false;
-    }
-    STM_DEV void store()
-    {
-        if (timer < -(1 << 30)) timer += (1 << 30);
-        m.st16(O_PC, pc); m.st8(O_A, a); m.st8(O_X, x); m.st8(O_Y, y); m.st8(O_SP, sp);
-        m.st8(O_P, get_p());
-        m.st8(O_BANK, bank); m.st16(O_LINE, line); m.st8(O_HCYC, (uint32_t)hcyc); m.st8(O_RX, rx);
-        m.st8(O_FLAGS, flags); m.st32(O_TIMER, (uint32_t)timer);
-        m.st8(O_TFLAG, timer < 0 ? 0x80u : 0u);      // the underflow latch always equals (timer < 0) between instructions
-    }
-
-    // ---------------- input ----------------
-    STM_DEV bool fire_pressed() { uint32_t act = m.ld8(O_ACTION); return act == 1 || act >= 10; }
-    STM_DEV uint32_t dir_bits()    // bit0 up, bit1 down, bit2 left, bit3 right
-    {
-        uint32_t act = m.ld8(O_ACTION);
-        if (act < 2 || act > 17) return 0;
-        uint32_t b = act >= 10 ? act - 8 : act;           // FIRE variants repeat codes 2..9
-        // nibble table for b = 2..9: 1 8 4 2 9 5 10 6
-        return (0x6A592481u >> (4 * (b - 2))) & 0xFu;
-    }
-    STM_DEV void update_latch()
-    {
-        if (!(m.ld8(O_VBLANK) & 0x40)) { m.st8(O_INPT_LATCH, 0); return; }
-        if (gp.controller == STM_CTRL_JOYSTICK && fire_pressed()) m.st8(O_INPT_LATCH, m.ld8(O_INPT_LATCH) | 1);
-    }
-    STM_DEV void set_action(uint32_t ale)
-    {
-        m.st8(O_ACTION, ale);
-        if (gp.controller == STM_CTRL_PADDLE) {
-            uint32_t d = dir_bits();
-            int pp = (int)m.ld8(O_PADDLE);
-            if (d & 8) pp -= STM_PADDLE_DELTA;
-            if (d & 4) pp += STM_PADDLE_DELTA;
-            pp = pp < STM_PADDLE_MIN ? STM_PADDLE_MIN : (pp > STM_PADDLE_MAX ? STM_PADDLE_MAX : pp);
-            m.st8(O_PADDLE, (uint32_t)pp);
-        }
-        update_latch();
-    }
-
+struct TiaLine {
+    M m;
+    uint32_t line, rx, flags;
+    bool render;
     // ---------------- TIA rendering: 32-pixel words from object masks ----------------
     // bits of `pat` (width <= 32, bit 0 = leftmost pixel) placed at ring position `start` (0..159),
     // as seen by word w (pixels 32w..32w+31); the 160-pixel line is a ring.
@@ -424,7 +380,6 @@ struct Emu {
 
     // Rows of the 210-row native frame that the 84x84 bilinear resize never samples (row % 5 == 2)
     // are not drawn at all; nothing downstream reads them.
-    STM_DEV static bool row_sampled(int row) { return (uint32_t)row < (uint32_t)STM_VIS_H && (row % 5) != 2; }
 
     // four pixels (one nibble of every layer mask) -> four packed colour bytes
     STM_DEV uint32_t compose4(uint32_t l0, uint32_t l1, uint32_t blm, uint32_t pfm, uint32_t sh, uint32_t c_p0,
@@ -492,8 +447,6 @@ struct Emu {
 
     STM_DEV void catchup(uint32_t xe)
     {
-        if (xe > STM_VIS_W) xe = STM_VIS_W;
-        if (xe <= rx) return;
         int row = (int)line - STM_YSTART;
         bool draw = render && row_sampled(row);
         uint32_t vblank = m.ld8(O_VBLANK);
@@ -573,6 +526,105 @@ struct Emu {
         }
         if (cx) m.st16(O_CX, m.ld16(O_CX) | cx);
         rx = xe;
+    }
+
+};
+
+template <class M>
+STM_NOINLINE uint32_t tia_catchup(M m, uint32_t line, uint32_t rx, uint32_t xe, uint32_t flags, bool render)
+{
+    TiaLine<M> t{m, line, rx, flags, render};
+    t.catchup(xe);
+    return t.rx;
+}
+
+// ---- the per-env machine ---------------------------------------------------------------------------
+// M must provide:
+//   uint32_t ld8(off) / void st8(off, v) / ld16 / st16 / ld32 / st32     blob access (off = byte offset)
+//   uint32_t rom8(idx)                                                     cartridge image
+//   void     fetch(off, &w, &ops)   predecoded instruction at image offset off: w = hot decode word of
+//                                   the opcode there, ops = operand bytes b1 | b2 << 8 (build_predecode)
+//   uint32_t opinfo(op)                                                    hot decode word (build_hot_table)
+//   void px16(row, q, w0..w3) store 16 pixels of native row `row`, quad q (0..9): four packed words
+//   void px4(row, g, word)    store 4 pixels (colour indices), group g (0..39)
+//   void px1(row, x, v)       store 1 pixel
+//
+// One instruction = fetch -> decode -> address -> read phase -> execute (register-only switch over
+// ~25 groups) -> write phase -> retire.  Every memory access goes through ONE read site and ONE
+// write site, so the TIA/RIOT slow paths (and the big catch-up renderer behind them) exist once in
+// the kernel instead of once per opcode; stack pulls/pushes are sequenced through the same sites.
+template <class M>
+struct Emu {
+    M &m;
+    const GameParams &gp;
+    // hot state (registers)
+    uint32_t pc, a, x, y, sp;
+    uint32_t p;             // C, I, D, V only (mask 0x4D); N and Z live in zn
+    uint32_t zn;            // Z <=> (zn & 0xFF) == 0 ; N <=> (zn & 0x180) != 0
+    int32_t  hcyc;          // CPU cycle in the line; may be transiently negative inside an instruction
+    int32_t  timer;
+    uint32_t bank;
+    // warm state
+    uint32_t line, rx, flags, end_line_no;
+    bool     render, wsync;
+
+    STM_DEV Emu(M &mm, const GameParams &g) : m(mm), gp(g) {}
+
+    STM_DEV uint32_t get_p() const
+    { return (p & 0x4Du) | FU | ((zn & 0x180u) ? (uint32_t)FN : 0u) | ((zn & 0xFFu) ? 0u : (uint32_t)FZ); }
+    STM_DEV void set_p(uint32_t v) { p = v & 0x4Du; zn = ((v & FN) << 1) | ((v & FZ) ? 0u : 1u); }
+
+    STM_DEV void load()
+    {
+        pc = m.ld16(O_PC); a = m.ld8(O_A); x = m.ld8(O_X); y = m.ld8(O_Y); sp = m.ld8(O_SP); set_p(m.ld8(O_P));
+        bank = m.ld8(O_BANK); line = m.ld16(O_LINE); hcyc = (int32_t)m.ld8(O_HCYC); rx = m.ld8(O_RX);
+        flags = m.ld8(O_FLAGS); timer = (int32_t)m.ld32(O_TIMER);
+        render = false; end_line_no = 0; wsync = false;
+    }
+    STM_DEV void store()
+    {
+        if (timer < -(1 << 30)) timer += (1 << 30);
+        m.st16(O_PC, pc); m.st8(O_A, a); m.st8(O_X, x); m.st8(O_Y, y); m.st8(O_SP, sp);
+        m.st8(O_P, get_p());
+        m.st8(O_BANK, bank); m.st16(O_LINE, line); m.st8(O_HCYC, (uint32_t)hcyc); m.st8(O_RX, rx);
+        m.st8(O_FLAGS, flags); m.st32(O_TIMER, (uint32_t)timer);
+        m.st8(O_TFLAG, timer < 0 ? 0x80u : 0u);      // the underflow latch always equals (timer < 0) between instructions
+    }
+
+    // ---------------- input ----------------
+    STM_DEV bool fire_pressed() { uint32_t act = m.ld8(O_ACTION); return act == 1 || act >= 10; }
+    STM_DEV uint32_t dir_bits()    // bit0 up, bit1 down, bit2 left, bit3 right
+    {
+        uint32_t act = m.ld8(O_ACTION);
+        if (act < 2 || act > 17) return 0;
+        uint32_t b = act >= 10 ? act - 8 : act;           // FIRE variants repeat codes 2..9
+        // nibble table for b = 2..9: 1 8 4 2 9 5 10 6
+        return (0x6A592481u >> (4 * (b - 2))) & 0xFu;
+    }
+    STM_DEV void update_latch()
+    {
+        if (!(m.ld8(O_VBLANK) & 0x40)) { m.st8(O_INPT_LATCH, 0); return; }
+        if (gp.controller == STM_CTRL_JOYSTICK && fire_pressed()) m.st8(O_INPT_LATCH, m.ld8(O_INPT_LATCH) | 1);
+    }
+    STM_DEV void set_action(uint32_t ale)
+    {
+        m.st8(O_ACTION, ale);
+        if (gp.controller == STM_CTRL_PADDLE) {
+            uint32_t d = dir_bits();
+            int pp = (int)m.ld8(O_PADDLE);
+            if (d & 8) pp -= STM_PADDLE_DELTA;
+            if (d & 4) pp += STM_PADDLE_DELTA;
+            pp = pp < STM_PADDLE_MIN ? STM_PADDLE_MIN : (pp > STM_PADDLE_MAX ? STM_PADDLE_MAX : pp);
+            m.st8(O_PADDLE, (uint32_t)pp);
+        }
+        update_latch();
+    }
+
+    // ---------------- TIA catch-up (out of line: see TiaLine below) ----------------
+    STM_DEV void catchup(uint32_t xe)
+    {
+        if (xe > STM_VIS_W) xe = STM_VIS_W;
+        if (xe > rx) rx = tia_catchup<M>(m, line, rx, xe, flags, render);
     }
 
     STM_DEV void end_line()
@@ -828,22 +880,17 @@ struct Emu {
     // run all lanes of a warp to the end of their scanline and wrap — i.e. render — them together.
     STM_DEV bool exec_core()
     {
-        // fetch: opcode + two operand bytes
-        uint32_t op, b1, b2;
+        // fetch + decode.  Cartridge code is predecoded (one 64-bit record per image byte: the hot
+        // decode word of the opcode there and its two operand bytes), so the common case is one load.
+        uint32_t w, b1, b2;
         uint32_t a13 = pc & 0x1FFF;
         if ((a13 & 0x1000) && (a13 & 0xFFF) <= 0xFFD) {
-            uint32_t off = (bank << 12) | (a13 & gp.rom_mask);
-            uint32_t wi = off >> 2;
-            uint32_t w_lo = m.rom32(wi);
-            uint32_t wrap = (gp.rom_mask >> 2);
-            uint32_t wi2 = ((wi + 1) & wrap) | (wi & ~wrap);
-            uint32_t w_hi = m.rom32(wi2);
-            uint32_t f = funnel_r(w_lo, w_hi, (off & 3) * 8);
-            op = f & 0xFF; b1 = (f >> 8) & 0xFF; b2 = (f >> 16) & 0xFF;
+            uint32_t ops;
+            m.fetch((bank << 12) | (a13 & gp.rom_mask), w, ops);
+            b1 = ops & 0xFF; b2 = ops >> 8;
         } else {
-            op = peek(pc); b1 = peek(pc + 1); b2 = peek(pc + 2);
+            w = m.opinfo(peek(pc)); b1 = peek(pc + 1); b2 = peek(pc + 2);
         }
-        const uint32_t w = m.opinfo(op);
         const uint32_t am = w & 7, kind = (w >> 5) & 3, grp = (w >> 13) & 31, data = w >> 18;
         uint32_t cyc = (w >> 7) & 15;
         uint32_t npc = (pc + ((w >> 11) & 3)) & 0xFFFF;
@@ -989,9 +1036,23 @@ struct Emu {
         flags &= ~(uint32_t)STM_F_FRAME_DONE;
         bool over = false;
         do {
+            // Run every lane to the end of its scanline.  (STM_MINPC: lowest-program-counter-first —
+            // in each round only the lanes whose (bank, pc) is the warp minimum execute, so lanes
+            // that took different sides of a branch fall back into step when their paths merge.
+            // Measured on B200: no gain over plain per-lane progress for these cartridges, so off.)
+            bool ended = over;
+#if STM_MINPC
+            for (;;) {
+                bool want = !ended && !(flags & STM_F_FRAME_DONE);
+                uint32_t key = want ? ((bank << 16) | pc) : 0xFFFFFFFFu;
+                uint32_t kmin = STM_WARP_MIN(lanes, key);
+                if (kmin == 0xFFFFFFFFu) break;
+                if (key == kmin) ended = exec_core();
+            }
+#else
+            while (!ended && !(flags & STM_F_FRAME_DONE)) ended = exec_core();
+#endif
             if (!over) {
-                bool ended = false;
-                while (!ended && !(flags & STM_F_FRAME_DONE)) ended = exec_core();
                 if (ended) finish_line();
                 over = (flags & STM_F_FRAME_DONE) != 0;
             }

@@ -52,6 +52,7 @@ struct stm_ctx {
     uint32_t rom_words = 0;
     uint32_t *d_rom = nullptr;       // cartridge image, as words
     uint32_t *d_lut = nullptr;       // 256-entry decode table
+    uint2 *d_pre = nullptr;          // predecoded cartridge: one record per image byte (emu_core.cuh build_predecode)
     uint32_t *d_scratch = nullptr;   // native frames
     uint8_t  *d_stepped = nullptr;   // per scratch env: 1 if the env was emulated by the last stm_step
     int scratch_envs = 0;
@@ -180,6 +181,7 @@ struct DevMem {
     uint8_t *blob;             // &sblob[tid] as bytes
     const uint32_t *rom;       // shared
     const uint32_t *lut;       // shared
+    const uint2 *pre;          // global, read-only path (L1-resident: 32 KB for a 4 KB cartridge)
     uint32_t *scr;             // native scratch of this env's tile, + lane
     uint32_t fsel;             // which of the two native frames is being drawn
 
@@ -191,7 +193,8 @@ struct DevMem {
     __device__ __forceinline__ uint32_t ld32(uint32_t o) const { return *(const uint32_t *)(blob + boff(o)); }
     __device__ __forceinline__ void st32(uint32_t o, uint32_t v) { *(uint32_t *)(blob + boff(o)) = v; }
     __device__ __forceinline__ uint32_t rom8(uint32_t i) const { return (rom[i >> 2] >> ((i & 3) * 8)) & 0xFFu; }
-    __device__ __forceinline__ uint32_t rom32(uint32_t wi) const { return rom[wi]; }
+    __device__ __forceinline__ void fetch(uint32_t off, uint32_t &w, uint32_t &ops) const
+    { uint2 v = __ldg(pre + off); w = v.x; ops = v.y; }
     __device__ __forceinline__ uint32_t opinfo(uint32_t op) const { return lut[op]; }
     // scr points at this lane's uint4 slot of (frame 0, row 0, quad 0); quads are kTileEnvs uint4 apart
     __device__ __forceinline__ uint32_t *quad(uint32_t row, uint32_t q) const
@@ -205,12 +208,12 @@ struct DevMem {
 
 struct StepArgs {
     uint8_t *states; const uint8_t *actions; float *rewards; uint8_t *done; int32_t *lives;
-    const uint32_t *rom; const uint32_t *lut; uint32_t *scratch; uint8_t *stepped;
+    const uint32_t *rom; const uint32_t *lut; const uint2 *pre; uint32_t *scratch; uint8_t *stepped;
     int n, frameskip, episodic_life, render; uint32_t rom_words; float weight;
     GameParams gp;
 };
 
-__global__ void __launch_bounds__(kStepThreads, 4)
+__global__ void __launch_bounds__(kStepThreads, 5)
 stm_step_kernel(const StepArgs a)
 {
     extern __shared__ __align__(16) uint32_t smem[];
@@ -241,7 +244,7 @@ stm_step_kernel(const StepArgs a)
 
     DevMem m;
     m.blob = reinterpret_cast<uint8_t *>(sblob + tid);
-    m.rom = srom; m.lut = slut;
+    m.rom = srom; m.lut = slut; m.pre = a.pre;
     m.scr = a.scratch ? a.scratch + (size_t)(env / kTileEnvs) * kTileWords + (env % kTileEnvs) * 4 : nullptr;
     m.fsel = 0;
     Emu<DevMem> e(m, a.gp);
@@ -416,7 +419,7 @@ int launch_step(stm_ctx *ctx, uint8_t *states, const uint8_t *actions, int n, in
 {
     StepArgs a;
     a.states = states; a.actions = actions; a.rewards = rewards; a.done = done; a.lives = lives;
-    a.rom = ctx->d_rom; a.lut = ctx->d_lut;
+    a.rom = ctx->d_rom; a.lut = ctx->d_lut; a.pre = ctx->d_pre;
     a.scratch = render ? ctx->d_scratch : nullptr;
     a.stepped = render ? ctx->d_stepped : nullptr;
     a.n = n; a.frameskip = frameskip; a.episodic_life = episodic_life; a.render = render;
@@ -529,6 +532,15 @@ int stm_ctx_create(stm_ctx **out, const stm_game_desc *desc, const uint8_t *rom,
         CUDA_TRY(ctx, cudaMalloc(&ctx->d_lut, sizeof(lut)));
         CUDA_TRY(ctx, cudaMemcpy(ctx->d_rom, rom, desc->rom_size, cudaMemcpyHostToDevice));
         CUDA_TRY(ctx, cudaMemcpy(ctx->d_lut, lut, sizeof(lut), cudaMemcpyHostToDevice));
+        {
+            uint32_t *pre = new (std::nothrow) uint32_t[2 * desc->rom_size];
+            if (!pre) return fail(ctx, STM_ERR_NOMEM, "stm_ctx_create: out of host memory");
+            build_predecode(rom, desc->rom_size, gp.rom_mask, pre);
+            cudaError_t e1 = cudaMalloc(&ctx->d_pre, 8ull * desc->rom_size);
+            if (e1 == cudaSuccess) e1 = cudaMemcpy(ctx->d_pre, pre, 8ull * desc->rom_size, cudaMemcpyHostToDevice);
+            delete[] pre;
+            CUDA_TRY(ctx, e1);
+        }
         size_t smem = (size_t)(64 * kStepThreads + ctx->rom_words + 256) * sizeof(uint32_t);
         CUDA_TRY(ctx, cudaFuncSetAttribute(stm_step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         return ensure_scratch(ctx, 4096);
@@ -543,7 +555,7 @@ int stm_ctx_destroy(stm_ctx *ctx)
 {
     if (!ctx) return STM_OK;
     cudaSetDevice(ctx->device);
-    cudaFree(ctx->d_rom); cudaFree(ctx->d_lut); cudaFree(ctx->d_scratch); cudaFree(ctx->d_stepped);
+    cudaFree(ctx->d_rom); cudaFree(ctx->d_lut); cudaFree(ctx->d_pre); cudaFree(ctx->d_scratch); cudaFree(ctx->d_stepped);
     for (int i = 0; i < 2; i++) {
         cudaFree(ctx->pool_state[i]); cudaFree(ctx->pool_reward[i]); cudaFree(ctx->pool_done[i]);
         cudaFree(ctx->pool_lives[i]); cudaFree(ctx->pool_stack[i]);

@@ -15,7 +15,13 @@ struct HostMem {
     uint32_t ld32(uint32_t o) const { uint32_t v; memcpy(&v, blob + o, 4); return v; }
     void st32(uint32_t o, uint32_t v) { memcpy(blob + o, &v, 4); }
     uint32_t rom8(uint32_t i) const { return rom[i]; }
-    uint32_t rom32(uint32_t wi) const { uint32_t v; memcpy(&v, rom + 4 * wi, 4); return v; }
+    uint32_t mask;
+    void fetch(uint32_t off, uint32_t &w, uint32_t &ops) const
+    {
+        uint32_t win = off & ~mask;
+        w = lut[rom[off]];
+        ops = rom[win | ((off + 1) & mask)] | (rom[win | ((off + 2) & mask)] << 8);
+    }
     uint32_t opinfo(uint32_t op) const { return lut[op]; }
     void px4(uint32_t row, uint32_t g, uint32_t w) { if (fb) memcpy(fb + row * 160 + 4 * g, &w, 4); }
     void px16(uint32_t row, uint32_t q, uint32_t a, uint32_t b, uint32_t c, uint32_t d)
@@ -47,7 +53,7 @@ void hc_frame(const stm_game_desc *d, const uint8_t *rom, uint8_t *blob, int ale
 {
     if (!g_lut_ok) { stm::build_hot_table(g_lut); g_lut_ok = true; }
     stm::GameParams gp; hc_fill_params(&gp, d);
-    HostMem m{blob, rom, g_lut, fb};
+    HostMem m{blob, rom, g_lut, fb, gp.rom_mask};
     stm::Emu<HostMem> e(m, gp);
     e.load();
     e.run_frame((uint32_t)ale_action, fb != nullptr);
@@ -63,7 +69,7 @@ void hc_exec_one(const stm_game_desc *d, const uint8_t *rom, uint8_t *blob)
 {
     if (!g_lut_ok) { stm::build_hot_table(g_lut); g_lut_ok = true; }
     stm::GameParams gp; hc_fill_params(&gp, d);
-    HostMem m{blob, rom, g_lut, nullptr};
+    HostMem m{blob, rom, g_lut, nullptr, gp.rom_mask};
     stm::Emu<HostMem> e(m, gp);
     e.load(); e.exec_one(); e.store();
 }
