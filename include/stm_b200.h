@@ -112,6 +112,41 @@ int stm_bfs_host(stm_ctx *ctx, const uint8_t *root_states, const uint8_t *root_s
 int stm_timing_enable(stm_ctx *ctx, int on);
 int stm_timing_read(stm_ctx *ctx, float *ms_by_kind, int *launches_by_kind);
 
+/* K5 — SoftTreeMax logits for R roots of a full-width tree (L = A^d leaves each), fused:
+ * m = val_coef*head + reward; per root action (L/A consecutive leaves x A head outputs) logsumexp(beta*m)
+ * - log(count) [cumulative == 0] or beta*mean(m) [cumulative != 0]; NaN -> 0; alpha-mix with the depth-0
+ * logits; eps-regularisation log((1-eps)*softmax + eps/A).
+ * Replaces policies/actor_critic_ts.py:60-95 and :147-188 and utils.py:52-57.
+ *   head R x L x A f32, rewards R x L f32, depth0 R x A f32 or NULL (alpha-mix term treated as 0),
+ *   values R x L f32 or NULL; logits R x A (out), raw R x A or NULL (z before the mix),
+ *   vmax R or NULL (max_l val_coef*values + reward: the use_leaves_v root value, :62-63). */
+int stm_logits_fwd(stm_ctx *ctx, const float *head, const float *rewards, const float *depth0,
+                   const float *values, int R, int L, int A, float val_coef, float beta, float alpha,
+                   float eps, int cumulative, float *logits, float *raw, float *vmax, void *stream);
+/* Backward of stm_logits_fwd w.r.t. head, depth0, beta and alpha (what evaluate_actions needs from
+ * autograd, actor_critic_ts.py:106-194).  dhead R x L x A, ddepth0 R x A or NULL, dbeta / dalpha: R
+ * per-root partial sums (the caller adds them up). */
+int stm_logits_bwd(stm_ctx *ctx, const float *head, const float *rewards, const float *depth0, int R,
+                   int L, int A, float val_coef, float beta, float alpha, float eps, int cumulative,
+                   const float *dlogits, float *dhead, float *ddepth0, float *dbeta, float *dalpha,
+                   void *stream);
+
+/* K4 — NatureCNN + heads.  stm_cnn_set_weights takes DEVICE pointers to fp32 parameters in the
+ * layout SB3 1.4.0's ActorCriticCnnPolicy holds them (features_extractor.cnn.{0,2,4}, .linear.0,
+ * action_net, value_net: conv (out,in,kh,kw), linear (out,in)) and re-tiles them to bf16 for the
+ * tensor cores (call again after every optimizer step; synchronises `stream`).
+ * stm_cnn_forward evaluates n observation stacks (n x 4 x 84 x 84 u8, as stm_bfs / stm_frames write
+ * them; the /255 of SB3's preprocess_obs is applied inside) and writes heads n x (A+1) f32:
+ * columns 0..A-1 = action_net(features), column A = value_net(features).
+ * Replaces extract_features -> mlp_extractor -> action_net / value_net,
+ * policies/actor_critic_ts.py:199-218 (cuDNN/cuBLAS fp32 there; bf16 x bf16 -> f32 tcgen05 here). */
+int stm_cnn_set_weights(stm_ctx *ctx, const float *conv1_w, const float *conv1_b, const float *conv2_w,
+                        const float *conv2_b, const float *conv3_w, const float *conv3_b,
+                        const float *fc_w, const float *fc_b, const float *action_w,
+                        const float *action_b, const float *value_w, const float *value_b,
+                        int n_actions, void *stream);
+int stm_cnn_forward(stm_ctx *ctx, const uint8_t *obs, long long n, float *heads, void *stream);
+
 /* number of kernels this ctx has launched since creation (bench.py's gpu_launches) */
 long long stm_launch_count(const stm_ctx *ctx);
 

@@ -70,6 +70,7 @@ struct stm_ctx {
     float *h_out_reward = nullptr; uint8_t *h_out_done = nullptr; int32_t *h_out_lives = nullptr;
     size_t h_roots = 0, h_leaves = 0;
     uint32_t reset_pc = 0;
+    void *cnn = nullptr;             // K4 state (stm_cnn.cu): tiled weights + activation scratch
     long long launches = 0;
     // optional per-kernel timing (stm_timing_*): CUDA events recorded around every launch
     bool timing = false;
@@ -490,6 +491,13 @@ int ensure_pool(stm_ctx *ctx, int which, size_t envs, size_t stack_envs)
 // =============================================================================================
 extern "C" {
 
+// shared with the other translation units of the library (stm_logits.cu, stm_cnn.cu)
+int stm_internal_fail(stm_ctx *ctx, int code, const char *msg) { return fail(ctx, code, "%s", msg); }
+void stm_internal_count_launch(stm_ctx *ctx) { if (ctx) ctx->launches++; }
+int stm_internal_device(const stm_ctx *ctx) { return ctx ? ctx->device : -1; }
+void **stm_internal_cnn_slot(stm_ctx *ctx) { return &ctx->cnn; }
+void stm_internal_cnn_free(void *p);
+
 const char *stm_last_error(const stm_ctx *ctx) { return ctx ? ctx->err : g_create_error; }
 size_t stm_state_bytes(const stm_ctx *) { return STM_STATE_BYTES; }
 int stm_num_actions(const stm_ctx *ctx) { return ctx ? ctx->desc.n_actions : 0; }
@@ -555,6 +563,7 @@ int stm_ctx_destroy(stm_ctx *ctx)
 {
     if (!ctx) return STM_OK;
     cudaSetDevice(ctx->device);
+    stm_internal_cnn_free(ctx->cnn);
     cudaFree(ctx->d_rom); cudaFree(ctx->d_lut); cudaFree(ctx->d_pre); cudaFree(ctx->d_scratch); cudaFree(ctx->d_stepped);
     for (int i = 0; i < 2; i++) {
         cudaFree(ctx->pool_state[i]); cudaFree(ctx->pool_reward[i]); cudaFree(ctx->pool_done[i]);

@@ -132,6 +132,27 @@ class Engine:
               self._h)
         return out
 
+    # ------------------------------------------------------------------------------------
+    PARAM_KEYS = ("cnn.0.weight", "cnn.0.bias", "cnn.2.weight", "cnn.2.bias", "cnn.4.weight", "cnn.4.bias",
+                  "linear.0.weight", "linear.0.bias", "action_net.weight", "action_net.bias",
+                  "value_net.weight", "value_net.bias")
+
+    def cnn_set_weights(self, params):
+        """params: dict of fp32 tensors keyed like PARAM_KEYS (SB3 naming without the
+        features_extractor prefix).  Re-tiles them to bf16 on the device."""
+        t = [params[k].detach().to(self.device, torch.float32).contiguous() for k in self.PARAM_KEYS]
+        A = t[8].shape[0]
+        check(lib().stm_cnn_set_weights(self._h, *[_ptr(x) for x in t], A, self._stream()), self._h)
+        self._cnn_actions = A
+
+    def cnn_forward(self, obs_u8):
+        """obs (n, 4, 84, 84) uint8 on the device -> (action head (n, A), value (n,)) fp32."""
+        n = obs_u8.shape[0]
+        A = self._cnn_actions
+        heads = torch.empty((n, A + 1), dtype=torch.float32, device=self.device)
+        check(lib().stm_cnn_forward(self._h, _ptr(obs_u8), n, _ptr(heads), self._stream()), self._h)
+        return heads[:, :A], heads[:, A]
+
     def timing(self, on=True):
         check(lib().stm_timing_enable(self._h, int(on)), self._h)
 

@@ -1,0 +1,70 @@
+"""K4 (NatureCNN + heads on tcgen05).  The oracle is a torch fp32 restatement of SB3's NatureCNN
+(oracle/policy_ref.py).  Tolerances, stated:
+  - against the SAME network evaluated in torch with bf16-rounded weights and bf16-rounded
+    inter-layer activations (what the kernel computes, fp32 accumulation): |err| <= 2e-3 * scale;
+  - against the plain fp32 network: |err| <= 3e-2 * scale  (bf16 has 8 mantissa bits),
+where scale = max |reference output| over the batch."""
+import numpy as np
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+
+def bf16_emulation(params, obs_u8):
+    r = lambda t: t.to(torch.bfloat16).float()
+    x = obs_u8.float()
+    x = r(F.relu(F.conv2d(x, r(params["cnn.0.weight"]), None, stride=4) / 255.0 + params["cnn.0.bias"].view(1, -1, 1, 1)))
+    x = r(F.relu(F.conv2d(x, r(params["cnn.2.weight"]), params["cnn.2.bias"], stride=2)))
+    x = r(F.relu(F.conv2d(x, r(params["cnn.4.weight"]), params["cnn.4.bias"], stride=1)))
+    f = r(F.relu(F.linear(x.flatten(1), r(params["linear.0.weight"]), params["linear.0.bias"])))
+    return F.linear(f, r(params["action_net.weight"]), params["action_net.bias"]), \
+        F.linear(f, r(params["value_net.weight"]), params["value_net.bias"])
+
+
+@pytest.mark.parametrize("n,A", [(1, 4), (5, 4), (130, 6), (700, 9), (33, 18)])
+def test_cnn_forward_matches_torch(n, A):
+    from oracle import policy_ref
+    from softtreemax_b200.engine import Engine
+    eng = Engine("synth_breakout")
+    try:
+        params = policy_ref.make_params(A, seed=4)
+        # make the heads non-trivial (SB3's 0.01-gain policy head would hide errors)
+        params["action_net.weight"] = params["action_net.weight"] * 50
+        g = torch.Generator().manual_seed(n)
+        obs = torch.randint(0, 256, (n, 4, 84, 84), generator=g, dtype=torch.uint8)
+        obs[:, :, 40:, :] //= 8                                     # some structure: dim lower half
+        eng.cnn_set_weights(params)
+        act, val = eng.cnn_forward(obs.to(eng.device))
+        torch.cuda.synchronize()
+        _, ref_a, ref_v = policy_ref.nature_cnn_forward(params, obs)
+        emu_a, emu_v = bf16_emulation(params, obs)
+        sa, sv = ref_a.abs().max().item(), ref_v.abs().max().item()
+        assert torch.isfinite(act).all() and torch.isfinite(val).all()
+        assert (act.cpu() - emu_a).abs().max().item() <= 2e-3 * sa, "vs bf16 emulation (action head)"
+        assert (val.cpu() - emu_v[:, 0]).abs().max().item() <= 2e-3 * sv, "vs bf16 emulation (value)"
+        assert (act.cpu() - ref_a).abs().max().item() <= 3e-2 * sa, "vs fp32 reference (action head)"
+        assert (val.cpu() - ref_v[:, 0]).abs().max().item() <= 3e-2 * sv, "vs fp32 reference (value)"
+    finally:
+        eng.close()
+
+
+def test_cnn_on_real_leaf_stacks(orc=None):
+    """Observation stacks produced by stm_bfs go straight into stm_cnn_forward (u8, no conversion)."""
+    from oracle import orc as _orc, policy_ref
+    from softtreemax_b200.engine import Engine
+    g = _orc.Game("synth_breakout")
+    eng = Engine("synth_breakout")
+    try:
+        roots, stacks = _orc.make_roots(g, 6, seed=8, base_steps=30, spread=9)
+        out = eng.bfs(torch.from_numpy(roots).to(eng.device), torch.from_numpy(stacks).to(eng.device), 2)
+        params = policy_ref.make_params(4, seed=1)
+        eng.cnn_set_weights(params)
+        act, val = eng.cnn_forward(out["stacks"])
+        torch.cuda.synchronize()
+        _, ref_a, ref_v = policy_ref.nature_cnn_forward(params, out["stacks"].cpu())
+        assert (act.cpu() - ref_a).abs().max().item() <= 3e-2 * ref_a.abs().max().item() + 1e-6
+        assert (val.cpu() - ref_v[:, 0]).abs().max().item() <= 3e-2 * ref_v.abs().max().item()
+    finally:
+        eng.close()
