@@ -1,0 +1,94 @@
+"""CuleEnv — mirror of environments/cule_env.py:14-107 (single root env with the DeepMind-style
+wrappers), with the emulator on the GPU instead of CuLE's CPU back-end (cule_env.py:20).
+No gym dependency (gym is not installable here): the class exposes the same attributes and the
+reset/step contract SB3's DummyVecEnv expects."""
+import math
+from collections import deque
+
+import numpy as np
+import torch
+
+from .atari import Env as AtariEnv, Rom as AtariRom, _Space
+
+
+class CuleEnv:
+    def __init__(self, device, env_kwargs, n_frame_stack=4, noop_max=30, clip_reward=True, fire_reset=True):
+        self.device = device
+        self.env_kwargs = env_kwargs
+        actions = AtariRom(env_kwargs["env_name"]).minimal_actions()
+        self.env = AtariEnv(num_envs=1, device="cuda:0" if str(device) in ("cpu", "auto") else device, **env_kwargs)
+        self.env.reset(initial_steps=1, verbose=1)
+        self.lives = 0
+        self.life_termination = False
+        self.n_frame_stack = n_frame_stack
+        self.state_buffer = deque([], maxlen=n_frame_stack)
+        self.training = True
+        self.noop_max = noop_max
+        self.clip_reward = clip_reward
+        self.fire_reset = fire_reset
+        self.reward_range = (-math.inf, math.inf)
+        self.metadata = {"render.modes": ["human", "rgb_array"]}
+        self.observation_space = _Space(shape=(n_frame_stack, 84, 84))
+        self.action_space = _Space(n=len(actions))
+        self.rng = np.random.RandomState(0)
+
+    def _reset_buffer(self):
+        for _ in range(self.n_frame_stack):
+            self.state_buffer.append(torch.zeros(84, 84, dtype=torch.uint8, device=self.env.device))
+
+    def _obs(self):
+        return torch.stack(list(self.state_buffer), 0).cpu().numpy()                      # cule_env.py:72,93
+
+    def reset(self):                                                                        # cule_env.py:43-54
+        obs = self.reset_no_fire()
+        if not self.fire_reset:
+            return obs
+        obs, _, done, _ = self.step(1)
+        if done:
+            self.reset_no_fire()
+        obs, _, done, _ = self.step(2)
+        if done:
+            self.reset_no_fire()
+        return obs
+
+    def reset_no_fire(self):                                                                # cule_env.py:56-72
+        if self.life_termination:
+            self.life_termination = False
+            obs, *_ = self.env.step(torch.tensor([0]))
+            obs = obs[0, :, :, 0]
+        else:
+            self._reset_buffer()
+            noops = self.rng.randint(self.noop_max + 1)
+            obs = self.env.reset(initial_steps=noops, verbose=1)[0, :, :, 0]
+        self.last_frame = obs
+        self.state_buffer.append(obs)
+        self.lives = int(self.env.lives[0].item())
+        return self._obs()
+
+    def step(self, action):                                                                 # cule_env.py:74-93
+        obs, reward, done, info = self.env.step(torch.tensor([action]))
+        info = {"ale.lives": info["ale.lives"], "orig_reward": float(reward[0].item())}
+        if self.clip_reward:
+            reward = torch.sign(reward)
+        obs = obs[0, :, :, 0]
+        self.state_buffer.append(obs)
+        self.last_frame = obs
+        lives = int(info["ale.lives"][0].item())
+        done = bool(done[0].item())
+        if self.training and lives < self.lives and lives > 0:       # lives > 0 for Q*bert (cule_env.py:88)
+            self.life_termination = True
+            done = True
+        self.lives = lives
+        return self._obs(), reward[0].cpu().numpy(), done, info
+
+    def train(self):
+        self.training = True
+
+    def eval(self):
+        self.training = False
+
+    def render(self, mode="human"):
+        raise NotImplementedError
+
+    def close(self):
+        pass
