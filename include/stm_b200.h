@@ -147,6 +147,24 @@ int stm_cnn_set_weights(stm_ctx *ctx, const float *conv1_w, const float *conv1_b
                         int n_actions, void *stream);
 int stm_cnn_forward(stm_ctx *ctx, const uint8_t *obs, long long n, float *heads, void *stream);
 
+/* (No counterpart in the reference: the reference never manages device memory itself.)
+ * stm_step(render=1) followed by stm_frames, for callers that must not cause a device allocation:
+ * hosts whose own pool already owns all GPU memory, so a cudaMalloc inside the library could only
+ * fail, and latency-critical loops that cannot take cudaMalloc's device-wide synchronisation.
+ * The native frames between the two kernels live in a scratch array built into the library image
+ * (about 8.6 MB on every GPU that loads the library, held until exit) instead of in allocated
+ * memory, so n is limited to STM_NOALLOC_MAX_ENVS; a larger n is refused with STM_ERR_ARG.
+ * The call itself never allocates or frees.  The first call on a device also looks up the device
+ * address of that array, so make that first call before starting any stream capture.
+ * All calls share the one array and it keeps the last call's contents (nothing in it needs
+ * clearing: everything read was written earlier in the same call); calls that overlap on the GPU
+ * race on it — issue them one after another.  Arguments as for stm_step and stm_frames. */
+#define STM_NOALLOC_MAX_ENVS 128
+int stm_step_frames_noalloc(stm_ctx *ctx, uint8_t *states, const uint8_t *actions, int n,
+                            int frameskip, int episodic_life, float weight, float *rewards,
+                            uint8_t *done, int32_t *lives, const uint8_t *parent_stacks,
+                            uint8_t *child_stacks, int fanout, void *stream);
+
 /* number of kernels this ctx has launched since creation (bench.py's gpu_launches) */
 long long stm_launch_count(const stm_ctx *ctx);
 

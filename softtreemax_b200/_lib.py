@@ -50,6 +50,8 @@ _SIGS = {
     "stm_timing_enable": (C.c_int, [C.c_void_p, C.c_int]),
     "stm_timing_read": (C.c_int, [C.c_void_p, C.POINTER(C.c_float), C.POINTER(C.c_int)]),
     "stm_launch_count": (C.c_longlong, [C.c_void_p]),
+    "stm_step_frames_noalloc": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_float,
+                                          C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]),
     "stm_cnn_set_weights": (C.c_int, [C.c_void_p] * 13 + [C.c_int, C.c_void_p]),
     "stm_cnn_forward": (C.c_int, [C.c_void_p, C.c_void_p, C.c_longlong, C.c_void_p, C.c_void_p]),
     "stm_logits_fwd": (C.c_int, [C.c_void_p] * 5 + [C.c_int] * 3 + [C.c_float] * 4 + [C.c_int] + [C.c_void_p] * 4),

@@ -763,3 +763,84 @@ int stm_bfs_host(stm_ctx *ctx, const uint8_t *root_states, const uint8_t *root_s
 }
 
 } // extern "C"
+
+// =============================================================================================
+// Allocation-free variant of "one agent step + observation stacks" (stm_step + stm_frames).
+//
+// The regular path keeps the native 160x210 frames that K2 writes and K3 reads in a buffer the ctx
+// obtains from cudaMalloc (and re-obtains when stm_set_scratch_envs grows it).  Some users of this
+// library must not trigger a device allocation from inside a call: a program that has handed the
+// whole GPU to its own pool at start-up (an inference server with a fixed arena, a PyTorch process
+// whose caching allocator owns the card) has nothing left for cudaMalloc to give, and a call made
+// from a latency-critical loop cannot afford cudaMalloc's implicit device-wide synchronisation.
+// For them the same two kernels run against a scratch area that is part of the library image:
+// a file-scope __device__ array, reserved on every GPU that loads the library, from load to exit.
+//
+// Size: STM_NOALLOC_MAX_ENVS = 128 envs -> 4 tiles x 2 frames x 210 rows x 160 B x 32 lanes
+// = 8 601 600 B, plus 128 B of "was stepped" flags.
+//
+// Rules that follow from sharing one array:
+//   - every call uses the same memory, and it still holds the previous call's frames.  Nothing in
+//     it has to start at zero — each byte K3 reads (sampled rows of the frames of envs that were
+//     stepped, and every env's flag) is written by K2 earlier in the same call — so nothing is
+//     cleared;
+//   - two calls that overlap on the GPU (different streams, or different threads' contexts) race
+//     on it.  Serialise them.
+// =============================================================================================
+namespace {
+
+constexpr int kNoAllocMaxEnvs = STM_NOALLOC_MAX_ENVS;
+static_assert(kNoAllocMaxEnvs % kTileEnvs == 0, "whole tiles");
+
+static __device__ __align__(256) uint32_t g_noalloc_frames[(size_t)(kNoAllocMaxEnvs / kTileEnvs) * kTileWords];
+static __device__ __align__(256) uint8_t g_noalloc_stepped[kNoAllocMaxEnvs];
+
+// In host code the two names above are host-side shadows of the device symbols, not device
+// addresses: the real addresses are looked up once per device and cached here.
+constexpr int kMaxDevices = 64;
+uint32_t *g_noalloc_frames_ptr[kMaxDevices];
+uint8_t *g_noalloc_stepped_ptr[kMaxDevices];
+bool g_noalloc_ready[kMaxDevices];
+
+} // namespace
+
+extern "C" int stm_step_frames_noalloc(stm_ctx *ctx, uint8_t *states, const uint8_t *actions, int n, int frameskip,
+                                       int episodic_life, float weight, float *rewards, uint8_t *done, int32_t *lives,
+                                       const uint8_t *parent_stacks, uint8_t *child_stacks, int fanout, void *stream)
+{
+    if (!ctx || !states || !rewards || !done || !lives || !parent_stacks || !child_stacks || n < 0 || frameskip < 1 || fanout < 1)
+        return fail(ctx, STM_ERR_ARG, "stm_step_frames_noalloc: bad argument");
+    if (n > kNoAllocMaxEnvs)
+        return fail(ctx, STM_ERR_ARG, "stm_step_frames_noalloc: n=%d exceeds the built-in scratch of %d envs "
+                                      "(use stm_step + stm_frames, whose scratch is allocated and resizable)", n, kNoAllocMaxEnvs);
+    if (((uintptr_t)states & 15) || (((uintptr_t)parent_stacks | (uintptr_t)child_stacks) & 3))
+        return fail(ctx, STM_ERR_ARG, "stm_step_frames_noalloc: states must be 16-byte and stacks 4-byte aligned");
+    const int dev = ctx->device;
+    if (dev < 0 || dev >= kMaxDevices) return fail(ctx, STM_ERR_ARG, "stm_step_frames_noalloc: device index %d unsupported", dev);
+    CUDA_TRY(ctx, cudaSetDevice(dev));
+    if (!g_noalloc_ready[dev]) {
+        // first call on this device: resolve the device addresses of the built-in scratch
+        CUDA_TRY(ctx, cudaGetSymbolAddress((void **)&g_noalloc_frames_ptr[dev], g_noalloc_frames));
+        CUDA_TRY(ctx, cudaGetSymbolAddress((void **)&g_noalloc_stepped_ptr[dev], g_noalloc_stepped));
+        g_noalloc_ready[dev] = true;
+    }
+    if (n == 0) return STM_OK;
+    cudaStream_t st = (cudaStream_t)stream;
+    StepArgs a;
+    a.states = states; a.actions = actions; a.rewards = rewards; a.done = done; a.lives = lives;
+    a.rom = ctx->d_rom; a.lut = ctx->d_lut; a.pre = ctx->d_pre;
+    a.scratch = g_noalloc_frames_ptr[dev];
+    a.stepped = g_noalloc_stepped_ptr[dev];
+    a.n = n; a.frameskip = frameskip; a.episodic_life = episodic_life; a.render = 1;
+    a.rom_words = ctx->rom_words; a.weight = weight; a.gp = ctx->gp;
+    const size_t smem = (size_t)(64 * kStepThreads + ctx->rom_words + 256) * sizeof(uint32_t);
+    stm_step_kernel<<<(n + kStepThreads - 1) / kStepThreads, kStepThreads, smem, st>>>(a);
+    ctx->launches++;
+    CUDA_TRY(ctx, cudaGetLastError());
+    dim3 grid((n + kTileEnvs - 1) / kTileEnvs, STM_OBS_H);
+    stm_frames_kernel<<<grid, kFrameThreads, 0, st>>>(g_noalloc_frames_ptr[dev], g_noalloc_stepped_ptr[dev], parent_stacks,
+                                                     child_stacks, n, fanout, frameskip >= 2 ? 2 : 1);
+    ctx->launches++;
+    CUDA_TRY(ctx, cudaGetLastError());
+    return STM_OK;
+}
