@@ -187,6 +187,70 @@ def main():
     per_kernel = eng.timing_read()
     eng.timing(False)
 
+    # ---------------- policy arm: bfs + NatureCNN on leaves and roots (K4) + SoftTreeMax logits (K5) ----------
+    from softtreemax_b200 import ops
+    import math
+    gtor = torch.Generator().manual_seed(4)                  # reference default seed, utils.py:67
+    shapes = {"cnn.0": (32, 4, 8, 8), "cnn.2": (64, 32, 4, 4), "cnn.4": (64, 64, 3, 3), "linear.0": (512, 3136),
+              "action_net": (A, 512), "value_net": (1, 512)}
+    params = {}
+    for k, shp in shapes.items():                            # random-init weights of the architecture (orthogonal, SB3 gains)
+        w = torch.empty(shp)
+        torch.nn.init.orthogonal_(w, gain={"action_net": 0.01, "value_net": 1.0}.get(k, math.sqrt(2)), generator=gtor)
+        params[k + ".weight"], params[k + ".bias"] = w, torch.zeros(shp[0])
+    eng.cnn_set_weights(params)
+    val_coef = 0.99 ** depth
+
+    def policy_step():
+        eng.bfs(states, stacks, depth, out=out)
+        head_leaf, _ = eng.cnn_forward(out["stacks"])
+        head_root, val_root = eng.cnn_forward(stacks)
+        logits, _, _ = ops.softtreemax_logits_full(eng, head_leaf.reshape(R, A ** depth, A), out["rewards"].reshape(R, -1),
+                                                  val_coef, 1.0, 1.0, 0.001, False)
+        return logits, val_root
+
+    for _ in range(2):
+        policy_step()
+    barrier()
+    p0, p1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    c_ms = 0.0
+    p0.record()
+    for _ in range(args.steps):
+        policy_step()
+    p1.record()
+    barrier()
+    ms_policy = p0.elapsed_time(p1)
+    # K4 alone, same inputs, for its tensor roofline
+    c0, c1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    c0.record()
+    for _ in range(args.steps):
+        eng.cnn_forward(out["stacks"])
+    c1.record()
+    torch.cuda.synchronize()
+    c_ms = c0.elapsed_time(c1)
+    # policy end to end: host roots in, host logits + values out
+    h_logits = torch.empty((R, A), dtype=torch.float32).pin_memory()
+    h_values = torch.empty((R,), dtype=torch.float32).pin_memory()
+    hs_pin, hk_pin = states.cpu().pin_memory(), stacks.cpu().pin_memory()
+
+    def policy_step_host():
+        states.copy_(hs_pin, non_blocking=True)
+        stacks.copy_(hk_pin, non_blocking=True)
+        lg, vr = policy_step()
+        h_logits.copy_(lg, non_blocking=True)
+        h_values.copy_(vr, non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+
+    policy_step_host()
+    barrier()
+    q0, q1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    q0.record()
+    for _ in range(args.steps):
+        policy_step_host()
+    q1.record()
+    barrier()
+    ms_policy_e2e = q0.elapsed_time(q1)
+
     # ---------------- end-to-end arm: host roots in, host rewards/done/lives out ----------------
     h_states = states.cpu().pin_memory()
     h_stacks = stacks.cpu().pin_memory()
@@ -207,10 +271,10 @@ def main():
     h2d = int(h_states.numel() + h_stacks.numel())
     d2h = int(L * (4 + 1 + 4))
 
-    t = torch.tensor([ms_total, ms_e2e], dtype=torch.float64, device=dev)
+    t = torch.tensor([ms_total, ms_e2e, ms_policy, ms_policy_e2e], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms_total, ms_e2e = float(t[0]), float(t[1])
+    ms_total, ms_e2e, ms_policy, ms_policy_e2e = (float(v) for v in t)
 
     if rank == 0:
         ms_step = ms_total / args.steps
@@ -249,6 +313,19 @@ def main():
                           "algorithmic_bytes_per_leaf": 49392},
             "K2_step": {"ms_per_step": step_ms / args.steps, "launches": step_n, "share_of_step": step_ms / ms_total},
         }
+        tf_peak = float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["bf16_tflops"]) \
+            if os.path.exists(os.path.join(ROOT, "MEASURED_PEAKS.json")) else 1590.0
+        cnn_tflops = L * args.steps * (18685952 + 1024 * (A + 1)) / (c_ms / 1e3) / 1e12
+        kernels["K4_cnn"] = {"bound": "tensor", "achieved": cnn_tflops, "peak": tf_peak, "unit": "TFLOP/s",
+                             "frac": cnn_tflops / tf_peak, "ms_per_step": c_ms / args.steps,
+                             "images_per_step": L, "dtype": "bf16 x bf16 -> f32 (tcgen05)"}
+        policy = {"metric": "softtreemax_policy_evals_per_sec", "value": world * R * args.steps / (ms_policy / 1e3),
+                  "unit": "evals/s", "ms_per_step": ms_policy / args.steps,
+                  "leaves_per_sec_through_cnn": world * L * args.steps / (ms_policy / 1e3),
+                  "e2e": {"value": world * R * args.steps / (ms_policy_e2e / 1e3), "unit": "evals/s",
+                          "h2d_bytes_per_step": int(hs_pin.numel() + hk_pin.numel()), "d2h_bytes_per_step": int(R * (A + 1) * 4),
+                          "api": "pinned host roots -> stm_bfs + stm_cnn_forward + stm_logits_fwd -> host logits, values"},
+                  "what": "bfs + NatureCNN (K4) on R*A^d leaves and R roots + SoftTreeMax logits (K5); random-init SB3-style weights"}
         cpu_rate, cpu_leaves, cpu_dt = cpu_oracle_rate(depth, args.cpu_seconds, os.cpu_count() or 1)
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
                 "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -256,7 +333,7 @@ def main():
                 "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                         "ms_per_step": ms_e2e / args.steps,
                         "api": "stm_bfs_host: pinned host roots in; rewards/done/lives to host; leaf stacks stay in HBM"},
-                "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "kernels": kernels,
+                "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "kernels": kernels, "policy": policy,
                 "cpu_baseline": {"value": cpu_rate, "unit": UNIT, "cores": os.cpu_count() or 1, "kind": "port",
                                  "sample": f"{cpu_leaves} leaves in {cpu_dt:.1f}s: 64 roots x depth {depth} repeated, oracle port (OpenMP)"}}
         print(json.dumps(line), flush=True)
