@@ -131,6 +131,9 @@ def main():
     ap.add_argument("--depth", type=int, default=2)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
+    ap.add_argument("--profile", action="store_true",
+                    help="bracket one bfs step + one policy step with cudaProfilerStart/Stop and exit "
+                         "(for `ncu --profile-from-start off`); prints no bench line")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
 
@@ -171,6 +174,22 @@ def main():
     for _ in range(args.warmup):
         eng.bfs(states, stacks, depth, out=out)
     barrier()
+    if args.profile:
+        from softtreemax_b200 import ops as _ops
+        eng.cnn_set_weights({k: torch.randn(s) * 0.05 for k, s in {
+            "cnn.0.weight": (32, 4, 8, 8), "cnn.0.bias": (32,), "cnn.2.weight": (64, 32, 4, 4), "cnn.2.bias": (64,),
+            "cnn.4.weight": (64, 64, 3, 3), "cnn.4.bias": (64,), "linear.0.weight": (512, 3136), "linear.0.bias": (512,),
+            "action_net.weight": (A, 512), "action_net.bias": (A,), "value_net.weight": (1, 512), "value_net.bias": (1,)}.items()})
+        eng.cnn_forward(stacks)
+        torch.cuda.synchronize()
+        torch.cuda.profiler.start()
+        eng.bfs(states, stacks, depth, out=out)
+        hl, _ = eng.cnn_forward(out["stacks"])
+        _ops.softtreemax_logits_full(eng, hl.reshape(R, A ** depth, A), out["rewards"].reshape(R, -1), 0.98, 1.0, 1.0, 0.001, False)
+        torch.cuda.synchronize()
+        torch.cuda.profiler.stop()
+        eng.close()
+        return
     eng.timing(True)
     launches0 = eng.launch_count
     sampler = ClockSampler(local)
