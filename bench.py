@@ -131,6 +131,7 @@ def main():
     ap.add_argument("--depth", type=int, default=2)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
+    ap.add_argument("--scratch-envs", type=int, default=262144, help="envs per K2/K3 pass (native-frame scratch: 67 KB each)")
     ap.add_argument("--profile", action="store_true",
                     help="bracket one bfs step + one policy step with cudaProfilerStart/Stop and exit "
                          "(for `ncu --profile-from-start off`); prints no bench line")
@@ -156,7 +157,7 @@ def main():
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     A, depth, R = 4, args.depth, args.roots
     L = R * A ** depth
-    eng = Engine(GAME, device=local, scratch_envs=min(L, 65536))
+    eng = Engine(GAME, device=local, scratch_envs=min(L, args.scratch_envs))
     dev = eng.device
     # every rank owns its own shard of roots (different seeds => different states per rank)
     states, stacks = make_roots(eng, R, seed=1234 + rank)

@@ -40,6 +40,9 @@ static_assert(offsetof(stm_env_state, pc) == O_PC && offsetof(stm_env_state, tim
 constexpr int kTileEnvs = 32;                                   // envs per native-scratch tile (= warp)
 constexpr size_t kTileWords = 2ull * STM_VIS_H * 40 * kTileEnvs; // u32 per tile (2 frames)
 constexpr int kStepThreads = 128;
+#ifndef STM_STEP_MIN_CTAS
+#define STM_STEP_MIN_CTAS 4   /* measured: 4 CTAs/SM without spills beats 5 with */
+#endif
 
 thread_local char g_create_error[256] = "";
 
@@ -214,7 +217,7 @@ struct StepArgs {
     GameParams gp;
 };
 
-__global__ void __launch_bounds__(kStepThreads, 5)
+__global__ void __launch_bounds__(kStepThreads, STM_STEP_MIN_CTAS)
 stm_step_kernel(const StepArgs a)
 {
     extern __shared__ __align__(16) uint32_t smem[];
