@@ -291,15 +291,13 @@ def main():
     h2d = int(h_states.numel() + h_stacks.numel())
     d2h = int(L * (4 + 1 + 4))
 
-    t = torch.tensor([ms_total, ms_e2e, ms_policy, ms_policy_e2e], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms_total, ms_e2e, ms_policy, ms_policy_e2e = (float(v) for v in t)
+    from softtreemax_b200 import shard
+    ms_total, ms_e2e, ms_policy, ms_policy_e2e = shard.max_over_ranks([ms_total, ms_e2e, ms_policy, ms_policy_e2e], dev)
 
     if rank == 0:
         ms_step = ms_total / args.steps
-        value = world * L * args.steps / (ms_total / 1e3)
-        e2e = world * L * args.steps / (ms_e2e / 1e3)
+        value = shard.whole_job_rate(L * args.steps, world, ms_total)
+        e2e = shard.whole_job_rate(L * args.steps, world, ms_e2e)
         hbm_peak, peak_src = peaks()
         S = 256
         step_ms, step_n = per_kernel["step"]
