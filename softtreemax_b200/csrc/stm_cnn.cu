@@ -15,10 +15,17 @@
 // canonical K-major layout (8x8 core matrices, no swizzle), while the previous slice is being
 // multiplied.  Weights are pre-tiled once into the same layout, so a slice of W is a linear copy.
 //
-// Per CTA: 128 threads.  All threads gather; thread 0 issues tcgen05.mma (M = 128, N = layer width,
-// K = 16 per instruction, 4 per 64-wide slice) into a TMEM accumulator and commits to an mbarrier;
-// two shared-memory stages so that gathering slice i+1 overlaps the MMAs of slice i; the epilogue
-// reads TMEM with tcgen05.ld (each warp its 32 lanes), applies scale + bias (+ ReLU) and stores.
+// Per CTA (persistent: CTAs loop over 128-row output tiles): 9 warps, warp-specialised.
+//   warps 0-3  producers: gather the A slice of (tile, k-slice) into a 4-stage shared-memory ring
+//              (loads of the next slice are in flight while the current one is converted and
+//              stored), fence.proxy.async, arrive on full[stage];
+//   warp  8    one thread issues tcgen05.mma (M = 128, N = layer width, K = 16 per instruction, 4 per
+//              64-wide slice) into one of TWO TMEM accumulators, tcgen05.commit -> empty[stage],
+//              and after the last slice of a tile -> tmem_full[buf];
+//   warps 4-7  epilogue: tcgen05.ld (each warp its 32 TMEM lanes), scale + bias (+ ReLU), store;
+//              arrive on tmem_empty[buf] — so the epilogue of tile i overlaps the MMAs of tile i+1.
+// The whole weight matrix of conv1/conv2/conv3/heads (16-72 KB) stays resident in shared memory
+// for the life of the CTA; only fc (3.2 MB) streams its W slices through the ring.
 #include <cuda_runtime.h>
 #include <cuda_bf16.h>
 #include <stdint.h>
@@ -32,7 +39,6 @@ extern "C" void **stm_internal_cnn_slot(stm_ctx *ctx);
 
 namespace {
 
-constexpr int kThreads = 128;
 constexpr int kTileM = 128;
 constexpr int kChunkK = 64;                         // K elements per shared-memory slice
 constexpr int kABytes = kTileM * kChunkK * 2;       // 16 KB
@@ -110,136 +116,216 @@ __device__ __forceinline__ uint4 u8x8_to_bf16x8(uint32_t lo, uint32_t hi)
     return r;
 }
 
-template <int N>
-__global__ void __launch_bounds__(kThreads)
+constexpr int kStages = 4;
+constexpr int kProducerThreads = 128, kEpilogueThreads = 128;
+constexpr int kThreads2 = kProducerThreads + kEpilogueThreads + 32;      // + the MMA warp
+
+__device__ __forceinline__ void mbar_arrive(uint64_t *bar)
+{ asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" :: "r"(smem_u32(bar)) : "memory"); }
+
+template <int N, bool kResidentW>
+__global__ void __launch_bounds__(kThreads2, 2)
 stm_cnn_gemm_kernel(const void *__restrict__ in, const __nv_bfloat16 *__restrict__ wt, const float *__restrict__ bias,
                     void *__restrict__ out, long long M_total, LayerGeom g, int n_off, int N_total)
 {
     constexpr int kBBytes = N * kChunkK * 2;
     extern __shared__ __align__(1024) uint8_t smem[];
-    uint8_t *sA[2] = { smem, smem + kABytes };
-    uint8_t *sB[2] = { smem + 2 * kABytes, smem + 2 * kABytes + kBBytes };
-    __shared__ __align__(8) uint64_t bar[2];
+    uint8_t *sA = smem;                                   // kStages x 16 KB
+    uint8_t *sB = smem + kStages * kABytes;               // resident: nchunks x kBBytes; streamed: kStages x kBBytes
+    __shared__ __align__(8) uint64_t full[kStages], empty[kStages], tfull[2], tempty[2];
     __shared__ uint32_t tmem_base_s;
     const int tid = threadIdx.x, warp = tid >> 5;
+    const int nchunks = g.K / kChunkK;
+    const long long ntiles = (M_total + kTileM - 1) / kTileM;
+    constexpr uint32_t kCols = (2 * N < 32) ? 32 : 2 * N;             // two accumulators
 
-    if (warp == 0) {
+    if (warp == 8) {
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;"
-                     :: "r"(smem_u32(&tmem_base_s)), "r"((uint32_t)(N < 32 ? 32 : N)) : "memory");
+                     :: "r"(smem_u32(&tmem_base_s)), "r"(kCols) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     }
     if (tid == 0) {
-        mbar_init(&bar[0], 1); mbar_init(&bar[1], 1);
+        for (int i = 0; i < kStages; i++) { mbar_init(&full[i], kProducerThreads); mbar_init(&empty[i], 1); }
+        for (int i = 0; i < 2; i++) { mbar_init(&tfull[i], 1); mbar_init(&tempty[i], kEpilogueThreads); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
+    if (kResidentW) {
+        // whole (pre-tiled) weight matrix of this N range: nchunks slices of kBBytes
+        for (int kc = 0; kc < nchunks; kc++) {
+            const uint4 *wsrc = reinterpret_cast<const uint4 *>(wt + (size_t)kc * N_total * kChunkK + (size_t)n_off * kChunkK);
+            uint4 *wdst = reinterpret_cast<uint4 *>(sB + (size_t)kc * kBBytes);
+            for (int i = tid; i < kBBytes / 16; i += kThreads2) wdst[i] = __ldg(wsrc + i);
+        }
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    }
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-    const uint32_t tmem_d = tmem_base_s;
+    const uint32_t tmem_base = tmem_base_s;
 
-    // this thread's output row
-    const long long m = (long long)blockIdx.x * kTileM + tid;
-    const bool row_ok = m < M_total;
-    const long long img = row_ok ? m / g.P : 0;
-    const int pos = row_ok ? (int)(m % g.P) : 0;
-    const int oy = pos / g.OW, ox = pos % g.OW;
-    const uint32_t a_row_off = (uint32_t)(tid >> 3) * 1024u + (uint32_t)(tid & 7) * 16u;
-
-    const int nchunks = g.K / kChunkK;
-    const uint32_t idesc = make_idesc(N);
-    const __nv_bfloat16 *wbase = wt + (size_t)n_off * kChunkK;     // tiles of this N range inside a chunk
-
-    for (int kc = 0; kc < nchunks; kc++) {
-        const int st = kc & 1;
-        if (kc >= 2) mbar_wait(&bar[st], ((kc >> 1) - 1) & 1);      // MMAs that read this stage are done
-        // ---- gather A slice: row `tid`, 64 K elements = 8 pieces of 16 bytes ----
-        uint8_t *arow = sA[st] + a_row_off;
-        if (g.mode == MODE_CONV1) {
-            // slice kc = input channel; piece kg = kernel row kh; 8 u8 along kw
-            const uint8_t *src = reinterpret_cast<const uint8_t *>(in) + ((size_t)img * g.C + kc) * g.IH * g.IW
-                                 + (size_t)(oy * g.S) * g.IW + ox * g.S;
-            #pragma unroll
-            for (int kg = 0; kg < 8; kg++) {
-                uint4 v = make_uint4(0, 0, 0, 0);
-                if (row_ok) {
-                    const uint32_t *p = reinterpret_cast<const uint32_t *>(src + kg * g.IW);
-                    v = u8x8_to_bf16x8(__ldg(p), __ldg(p + 1));
+    if (warp < 4 && g.mode != MODE_CONV1) {
+        // ===================== producers, bf16 NHWC input: cp.async, kDepth slices in flight =====================
+        // The stream of (tile, k-slice) work items is issued kDepth items ahead of the one being
+        // published: 16-byte cp.async copies land straight in the ring (no registers), and an item is
+        // handed to the MMA thread once its group has completed and been fenced to the async proxy.
+        constexpr int kDepth = kStages - 1;
+        const uint32_t a_row_off = (uint32_t)(tid >> 3) * 1024u + (uint32_t)(tid & 7) * 16u;
+        const long long my_tiles = blockIdx.x < ntiles ? (ntiles - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
+        const long long items = my_tiles * nchunks;
+        long long tile = blockIdx.x;
+        int kc = 0;
+        const __nv_bfloat16 *src16 = nullptr;
+        bool row_ok = false;
+        for (long long i = 0; i < items + kDepth; i++) {
+            if (i < items) {
+                if (kc == 0) {
+                    const long long m = tile * kTileM + tid;
+                    row_ok = m < M_total;
+                    const long long img = row_ok ? m / g.P : 0;
+                    const int pos = row_ok ? (int)(m % g.P) : 0;
+                    const int oy = pos / g.OW, ox = pos % g.OW;
+                    src16 = reinterpret_cast<const __nv_bfloat16 *>(in) + (((size_t)img * g.IH + oy * g.S) * g.IW + ox * g.S) * g.C;
                 }
-                *reinterpret_cast<uint4 *>(arow + kg * 128) = v;
-            }
-        } else {
-            const int k0 = kc * kChunkK;
-            const int kh = k0 / g.KWC, koff = k0 % g.KWC;
-            const __nv_bfloat16 *src = reinterpret_cast<const __nv_bfloat16 *>(in)
-                + (((size_t)img * g.IH + (oy * g.S + kh)) * g.IW + ox * g.S) * g.C + koff;
-            #pragma unroll
-            for (int kg = 0; kg < 8; kg++) {
-                uint4 v = make_uint4(0, 0, 0, 0);
-                if (row_ok) v = __ldg(reinterpret_cast<const uint4 *>(src) + kg);
-                *reinterpret_cast<uint4 *>(arow + kg * 128) = v;
-            }
-        }
-        // ---- copy W slice (pre-tiled: linear) ----
-        {
-            const uint4 *wsrc = reinterpret_cast<const uint4 *>(wbase + (size_t)kc * N_total * kChunkK);
-            uint4 *wdst = reinterpret_cast<uint4 *>(sB[st]);
-            #pragma unroll 4
-            for (int i = tid; i < kBBytes / 16; i += kThreads) wdst[i] = __ldg(wsrc + i);
-        }
-        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic-proxy writes -> visible to the tensor core
-        __syncthreads();
-        if (tid == 0) {
-            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-            const uint32_t a0 = smem_u32(sA[st]), b0 = smem_u32(sB[st]);
-            #pragma unroll
-            for (int j = 0; j < kChunkK / 16; j++)
-                umma(tmem_d, make_desc(a0 + j * 256), make_desc(b0 + j * 256), idesc, (kc | j) ? 1u : 0u);
-            umma_commit(&bar[st]);
-        }
-    }
-    // wait for the last commit of each stage (a commit covers every earlier MMA)
-    {
-        const int last = nchunks - 1;
-        mbar_wait(&bar[last & 1], (last >> 1) & 1);
-        if (nchunks >= 2) { const int prev = last - 1; mbar_wait(&bar[prev & 1], (prev >> 1) & 1); }
-    }
-    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-
-    // ---- epilogue: TMEM -> registers -> scale, bias, ReLU -> global ----
-    const uint32_t taddr = tmem_d + ((uint32_t)(warp * 32) << 16);
-    #pragma unroll 1
-    for (int c0 = 0; c0 < N; c0 += 8) {
-        uint32_t r[8];
-        asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
-                     : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7])
-                     : "r"(taddr + (uint32_t)c0));
-        asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-        if (row_ok) {
-            float v[8];
-            #pragma unroll
-            for (int j = 0; j < 8; j++) {
-                int n = n_off + c0 + j;
-                float x = __uint_as_float(r[j]) * g.scale + (n < g.n_real ? bias[n] : 0.f);
-                v[j] = g.relu ? fmaxf(x, 0.f) : x;
-            }
-            if (g.out_f32) {
-                float *o = reinterpret_cast<float *>(out) + (size_t)m * g.n_real;
+                const uint32_t st = (uint32_t)(i % kStages), ph = (uint32_t)((i / kStages) & 1);
+                mbar_wait(&empty[st], ph ^ 1);
+                const int k0 = kc * kChunkK;
+                const int kh = k0 / g.KWC, koff = k0 - kh * g.KWC;
+                const uint8_t *p = reinterpret_cast<const uint8_t *>(src16 + (size_t)kh * g.IW * g.C + koff);
+                const uint32_t dst = smem_u32(sA + st * kABytes + a_row_off);
+                const uint32_t nbytes = row_ok ? 16u : 0u;                      // 0 => zero fill
                 #pragma unroll
-                for (int j = 0; j < 8; j++) if (n_off + c0 + j < g.n_real) o[n_off + c0 + j] = v[j];
-            } else {
-                uint4 pk;
-                __nv_bfloat162 t0 = __floats2bfloat162_rn(v[0], v[1]), t1 = __floats2bfloat162_rn(v[2], v[3]);
-                __nv_bfloat162 t2 = __floats2bfloat162_rn(v[4], v[5]), t3 = __floats2bfloat162_rn(v[6], v[7]);
-                pk.x = *reinterpret_cast<uint32_t *>(&t0); pk.y = *reinterpret_cast<uint32_t *>(&t1);
-                pk.z = *reinterpret_cast<uint32_t *>(&t2); pk.w = *reinterpret_cast<uint32_t *>(&t3);
-                *reinterpret_cast<uint4 *>(reinterpret_cast<__nv_bfloat16 *>(out) + (size_t)m * N_total + n_off + c0) = pk;
+                for (int kg = 0; kg < 8; kg++)
+                    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" :: "r"(dst + kg * 128), "l"(p + kg * 16), "r"(nbytes) : "memory");
+                if (!kResidentW) {
+                    const uint8_t *wsrc = reinterpret_cast<const uint8_t *>(wt + (size_t)kc * N_total * kChunkK + (size_t)n_off * kChunkK);
+                    const uint32_t wdst = smem_u32(sB + st * kBBytes);
+                    #pragma unroll 4
+                    for (int j = tid; j < kBBytes / 16; j += kProducerThreads)
+                        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" :: "r"(wdst + j * 16), "l"(wsrc + (size_t)j * 16) : "memory");
+                }
+                if (++kc == nchunks) { kc = 0; tile += gridDim.x; }
             }
+            asm volatile("cp.async.commit_group;" ::: "memory");              // (an empty group past the end keeps the count regular)
+            if (i >= kDepth) {
+                asm volatile("cp.async.wait_group %0;" :: "n"(kDepth) : "memory");
+                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                mbar_arrive(&full[(i - kDepth) % kStages]);
+            }
+        }
+    } else if (warp < 4) {
+        // ===================== producers, u8 NCHW input (conv1): registers, converted to bf16 =====================
+        const uint32_t a_row_off = (uint32_t)(tid >> 3) * 1024u + (uint32_t)(tid & 7) * 16u;
+        uint32_t it = 0;
+        for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+            const long long m = tile * kTileM + tid;
+            const bool row_ok = m < M_total;
+            const long long img = row_ok ? m / g.P : 0;
+            const int pos = row_ok ? (int)(m % g.P) : 0;
+            const int oy = pos / g.OW, ox = pos % g.OW;
+            const uint8_t *src8 = reinterpret_cast<const uint8_t *>(in) + (size_t)img * g.C * g.IH * g.IW
+                                  + (size_t)(oy * g.S) * g.IW + ox * g.S;
+            uint2 cur[8], nxt[8];
+            auto load = [&](int kc, uint2 *r) {
+                const uint8_t *p8 = src8 + (size_t)kc * g.IH * g.IW;
+                #pragma unroll
+                for (int kg = 0; kg < 8; kg++) {
+                    const uint32_t *p = reinterpret_cast<const uint32_t *>(p8 + kg * g.IW);
+                    r[kg].x = row_ok ? __ldg(p) : 0u; r[kg].y = row_ok ? __ldg(p + 1) : 0u;
+                }
+            };
+            load(0, nxt);
+            for (int kc = 0; kc < nchunks; kc++, it++) {
+                #pragma unroll
+                for (int kg = 0; kg < 8; kg++) cur[kg] = nxt[kg];
+                if (kc + 1 < nchunks) load(kc + 1, nxt);
+                const uint32_t st = it % kStages, ph = (it / kStages) & 1;
+                mbar_wait(&empty[st], ph ^ 1);                      // slot free (first pass: returns at once)
+                uint8_t *arow = sA + st * kABytes + a_row_off;
+                #pragma unroll
+                for (int kg = 0; kg < 8; kg++)
+                    *reinterpret_cast<uint4 *>(arow + kg * 128) = u8x8_to_bf16x8(cur[kg].x, cur[kg].y);
+                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                mbar_arrive(&full[st]);
+            }
+        }
+    } else if (warp == 8) {
+        // ===================== MMA issuer =====================
+        if ((tid & 31) == 0) {
+            const uint32_t idesc = make_idesc(N);
+            uint32_t it = 0, t = 0;
+            for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x, t++) {
+                const uint32_t buf = t & 1;
+                mbar_wait(&tempty[buf], ((t >> 1) & 1) ^ 1);        // the epilogue has drained this accumulator
+                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                const uint32_t tmem_d = tmem_base + buf * N;
+                for (int kc = 0; kc < nchunks; kc++, it++) {
+                    const uint32_t st = it % kStages, ph = (it / kStages) & 1;
+                    mbar_wait(&full[st], ph);
+                    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                    const uint32_t a0 = smem_u32(sA + st * kABytes);
+                    const uint32_t b0 = smem_u32(sB + (kResidentW ? (size_t)kc : (size_t)st) * kBBytes);
+                    #pragma unroll
+                    for (int j = 0; j < kChunkK / 16; j++)
+                        umma(tmem_d, make_desc(a0 + j * 256), make_desc(b0 + j * 256), idesc, (kc | j) ? 1u : 0u);
+                    umma_commit(&empty[st]);                        // frees the slot when these MMAs are done
+                }
+                umma_commit(&tfull[buf]);                           // accumulator complete
+            }
+        }
+    } else {
+        // ===================== epilogue =====================
+        const int et = tid - kProducerThreads;                     // 0..127 = TMEM lane = row in tile
+        const int ew = et >> 5;
+        uint32_t t = 0;
+        for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x, t++) {
+            const uint32_t buf = t & 1;
+            mbar_wait(&tfull[buf], (t >> 1) & 1);
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            const long long m = tile * kTileM + et;
+            const bool row_ok = m < M_total;
+            const uint32_t taddr = tmem_base + buf * N + ((uint32_t)(ew * 32) << 16);
+            #pragma unroll 1
+            for (int c0 = 0; c0 < N; c0 += 16) {
+                uint32_t r[16];
+                asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+                             "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+                             : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+                               "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+                             : "r"(taddr + (uint32_t)c0));
+                asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+                if (row_ok) {
+                    float v[16];
+                    #pragma unroll
+                    for (int j = 0; j < 16; j++) {
+                        int n = n_off + c0 + j;
+                        float x = __uint_as_float(r[j]) * g.scale + (n < g.n_real ? __ldg(bias + n) : 0.f);
+                        v[j] = g.relu ? fmaxf(x, 0.f) : x;
+                    }
+                    if (g.out_f32) {
+                        float *o = reinterpret_cast<float *>(out) + (size_t)m * g.n_real;
+                        #pragma unroll
+                        for (int j = 0; j < 16; j++) if (n_off + c0 + j < g.n_real) o[n_off + c0 + j] = v[j];
+                    } else {
+                        uint32_t pk[8];
+                        #pragma unroll
+                        for (int j = 0; j < 8; j++) {
+                            __nv_bfloat162 t2 = __floats2bfloat162_rn(v[2 * j], v[2 * j + 1]);
+                            pk[j] = *reinterpret_cast<uint32_t *>(&t2);
+                        }
+                        uint4 *o = reinterpret_cast<uint4 *>(reinterpret_cast<__nv_bfloat16 *>(out) + (size_t)m * N_total + n_off + c0);
+                        o[0] = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+                        o[1] = make_uint4(pk[4], pk[5], pk[6], pk[7]);
+                    }
+                }
+            }
+            asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+            mbar_arrive(&tempty[buf]);
         }
     }
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
-    if (warp == 0)
-        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" :: "r"(tmem_d), "r"((uint32_t)(N < 32 ? 32 : N)) : "memory");
+    if (warp == 8)
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" :: "r"(tmem_base), "r"(kCols) : "memory");
 }
 
 // fp32 torch-layout weights (n_real, K) -> bf16, K reordered (k = s*C + c <- column c*KHW + s), zero padded
@@ -266,18 +352,21 @@ struct CnnState {
     long long cap_images = 0;
 };
 
-template <int N>
+template <int N, bool kResidentW>
 int launch_layer(stm_ctx *ctx, const void *in, const __nv_bfloat16 *w, const float *b, void *out, long long M,
                  const LayerGeom &g, int n_off, int N_total, cudaStream_t st)
 {
     static bool attr_done = false;
-    size_t smem = 2 * kABytes + 2 * (size_t)N * kChunkK * 2 + 1024;
+    const int nchunks = g.K / kChunkK;
+    size_t smem = (size_t)kStages * kABytes + (size_t)(kResidentW ? nchunks : kStages) * N * kChunkK * 2;
     if (!attr_done) {
-        cudaFuncSetAttribute(stm_cnn_gemm_kernel<N>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        cudaFuncSetAttribute(stm_cnn_gemm_kernel<N, kResidentW>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 2048);
         attr_done = true;
     }
     long long tiles = (M + kTileM - 1) / kTileM;
-    stm_cnn_gemm_kernel<N><<<(unsigned)tiles, kThreads, smem, st>>>(in, w, b, out, M, g, n_off, N_total);
+    int per_sm = smem <= 100 * 1024 ? 2 : 1;                         // persistent: fill every SM, CTAs loop over tiles
+    long long grid = tiles < 148LL * per_sm ? tiles : 148LL * per_sm;
+    stm_cnn_gemm_kernel<N, kResidentW><<<(unsigned)grid, kThreads2, smem, st>>>(in, w, b, out, M, g, n_off, N_total);
     stm_internal_count_launch(ctx);
     cudaError_t e = cudaGetLastError();
     return e == cudaSuccess ? STM_OK : stm_internal_fail(ctx, STM_ERR_CUDA, cudaGetErrorString(e));
@@ -373,16 +462,16 @@ int stm_cnn_forward(stm_ctx *ctx, const uint8_t *obs, long long n, float *heads,
         long long c = n - i0 < chunk ? n - i0 : chunk;
         int rc;
         LayerGeom g1 = { MODE_CONV1, 400, 20, 84, 84, 4, 0, 4, 256, 32, 1, 0, 1.0f / 255.0f };
-        if ((rc = launch_layer<32>(ctx, obs + (size_t)i0 * 4 * 84 * 84, s->w[0], s->b[0], s->act1, c * 400, g1, 0, 32, st))) return rc;
+        if ((rc = launch_layer<32, true>(ctx, obs + (size_t)i0 * 4 * 84 * 84, s->w[0], s->b[0], s->act1, c * 400, g1, 0, 32, st))) return rc;
         LayerGeom g2 = { MODE_NHWC, 81, 9, 20, 20, 32, 4 * 32, 2, 512, 64, 1, 0, 1.0f };
-        if ((rc = launch_layer<64>(ctx, s->act1, s->w[1], s->b[1], s->act2, c * 81, g2, 0, 64, st))) return rc;
+        if ((rc = launch_layer<64, true>(ctx, s->act1, s->w[1], s->b[1], s->act2, c * 81, g2, 0, 64, st))) return rc;
         LayerGeom g3 = { MODE_NHWC, 49, 7, 9, 9, 64, 3 * 64, 1, 576, 64, 1, 0, 1.0f };
-        if ((rc = launch_layer<64>(ctx, s->act2, s->w[2], s->b[2], s->act3, c * 49, g3, 0, 64, st))) return rc;
+        if ((rc = launch_layer<64, true>(ctx, s->act2, s->w[2], s->b[2], s->act3, c * 49, g3, 0, 64, st))) return rc;
         LayerGeom g4 = { MODE_NHWC, 1, 1, 1, 1, 3136, 3136, 1, 3136, 512, 1, 0, 1.0f };
         for (int half = 0; half < 2; half++)
-            if ((rc = launch_layer<256>(ctx, s->act3, s->w[3], s->b[3], s->feat, c, g4, half * 256, 512, st))) return rc;
+            if ((rc = launch_layer<256, false>(ctx, s->act3, s->w[3], s->b[3], s->feat, c, g4, half * 256, 512, st))) return rc;
         LayerGeom g5 = { MODE_NHWC, 1, 1, 1, 1, 512, 512, 1, 512, A1, 0, 1, 1.0f };
-        if ((rc = launch_layer<32>(ctx, s->feat, s->w[4], s->b[4], heads + (size_t)i0 * A1, c, g5, 0, 32, st))) return rc;
+        if ((rc = launch_layer<32, true>(ctx, s->feat, s->w[4], s->b[4], heads + (size_t)i0 * A1, c, g5, 0, 32, st))) return rc;
     }
     return STM_OK;
 }
