@@ -11,6 +11,7 @@ ROM_DIR = os.path.join(os.path.dirname(os.path.abspath(__file__)), "roms")
 ENV_ALIASES = {
     "Breakout": "synth_breakout",
     "Pong": "synth_pong",
+    "MsPacman": "synth_pacman",
 }
 
 

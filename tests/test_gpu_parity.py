@@ -66,7 +66,7 @@ def test_k1_clone_bitexact(engines, n, fanout):
     assert np.array_equal(out[3].cpu().numpy(), lv[idx])
 
 
-@pytest.mark.parametrize("name", ["synth_breakout", "synth_pong", "synth_torture"])
+@pytest.mark.parametrize("name", ["synth_breakout", "synth_pong", "synth_pacman", "synth_torture"])
 @pytest.mark.parametrize("frameskip", [4, 1, 2])
 def test_k2_k3_one_level_bitexact(orc, engines, name, frameskip):
     g = orc.Game(name)
@@ -142,7 +142,8 @@ def test_random_rom_step_bitexact(orc, seed):
 
 
 @pytest.mark.parametrize("name,R,depth", [("synth_breakout", 5, 1), ("synth_breakout", 3, 2), ("synth_breakout", 2, 3),
-                                          ("synth_pong", 2, 2), ("synth_torture", 1, 1), ("synth_torture", 3, 2)])
+                                          ("synth_pong", 2, 2), ("synth_pacman", 3, 2), ("synth_torture", 1, 1),
+                                          ("synth_torture", 3, 2)])
 def test_bfs_matches_oracle(orc, engines, name, R, depth):
     g = orc.Game(name)
     eng = engines(name)

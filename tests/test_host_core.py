@@ -49,7 +49,7 @@ def run_pair(orc, H, game, nframes, seed, render_every=1):
         assert (do[0], ro[0], lo[0]) == (dh[0], rh[0], lh[0])
 
 
-@pytest.mark.parametrize("name", ["synth_breakout", "synth_pong", "synth_torture"])
+@pytest.mark.parametrize("name", ["synth_breakout", "synth_pong", "synth_pacman", "synth_torture"])
 def test_games_match_oracle(orc, host_core, name):
     run_pair(orc, _bind(host_core, orc), orc.Game(name), 240, seed=3)
 

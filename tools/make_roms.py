@@ -109,6 +109,7 @@ def region(name, end, extra=""):
 def breakout_source(variant):
     """variant: 'breakout' (paddle, lives), 'pong' (joystick, opponent score), 'pacman' (F8)."""
     paddle = variant == "breakout"
+    banked = variant == "pacman"
     src = TIA + """
 frameCnt = $80
 ballX = $81
@@ -126,6 +127,7 @@ lives = $B9
 gameOver = $BA
 scoreHi = $CC
 scoreLo = $CD
+padSize = $BB
 
 BALL_H = 4
 BRICK_TOP = 32
@@ -172,6 +174,7 @@ MainLoop:
     STA VBLANK
     INC frameCnt
     JSR GameLogic
+""" + ("    JSR CallBank1\n" if banked else "") + """
     ; position paddle (P0) and ball (BL)
     LDA padX
     LDX #0
@@ -321,9 +324,19 @@ noRight:
     LDA #4
 pl1: STA padX
 noLeft:
+""" + ("""
+    LDA SWCHA           ; no FIRE in this action set: any stick direction launches the ball
+    AND #$F0
+    CMP #$F0
+    BEQ noDir
+    LDA #0
+    BEQ stDir
+noDir: LDA #$80
+stDir: STA temp
+""" if banked else """
     LDA INPT4
     STA temp
-"""
+""")
     src += """
     LDA ballLive
     BNE inPlay
@@ -494,7 +507,24 @@ BitTab:
     .byte $01,$02,$04,$08,$10,$20,$40,$80
 RowScore:
     .byte $07,$07,$04,$04,$01,$01
-
+"""
+    if banked:
+        src += """
+; ---- F8 bank switching: these addresses exist in both banks ----
+    .org $FFD0
+CallBank1:
+    LDA $1FF9           ; -> bank 1: the next fetch ($FFD3) comes from bank 1 (JSR Bank1Logic ; LDA $1FF8)
+    NOP
+    NOP
+    NOP
+    NOP
+    NOP
+    NOP
+    LDA padSize         ; $FFD9: bank 1 switched back to bank 0 just before this address
+    STA NUSIZ0
+    RTS
+"""
+    src += """
     .org $FFFA
     .word Reset, Reset, Reset
 """
@@ -642,6 +672,40 @@ RegTab:
 """
 
 
+def pacman_bank1_source():
+    """Bank 1 of the F8 cartridge: entered through the trampoline at $FE00; joystick UP / DOWN pick the
+    paddle width (quad / single), anything else restores double width."""
+    return TIA + """
+padSize = $BB
+    .org $F000
+Bank1Logic:
+    LDA SWCHA
+    AND #$10            ; up (0 = pushed)
+    BNE notUp
+    LDA #7
+    STA padSize
+    RTS
+notUp:
+    LDA SWCHA
+    AND #$20            ; down
+    BNE notDown
+    LDA #0
+    STA padSize
+    RTS
+notDown:
+    LDA #5
+    STA padSize
+    RTS
+
+    .org $FFD0
+    .byte $EA, $EA, $EA ; (bank 0 executes LDA $1FF9 here)
+    JSR Bank1Logic      ; at $FFD3 in bank 1
+    LDA $1FF8           ; -> bank 0, which continues at $FFD9
+    .org $FFFA
+    .word $F000, $F000, $F000
+"""
+
+
 ALE = dict(NOOP=0, FIRE=1, UP=2, RIGHT=3, LEFT=4, DOWN=5, UPRIGHT=6, UPLEFT=7, DOWNRIGHT=8,
            DOWNLEFT=9, UPFIRE=10, RIGHTFIRE=11, LEFTFIRE=12, DOWNFIRE=13)
 
@@ -666,6 +730,18 @@ def build():
         actions=[ALE["NOOP"], ALE["FIRE"], ALE["RIGHT"], ALE["LEFT"], ALE["RIGHTFIRE"], ALE["LEFTFIRE"]],
         score_addr=[255, 76, 77], score2_addr=[255, 255, 56],
         lives_addr=255, lives_shift=0, lives_mask=255, term_addr=58, term_mask=255, term_value=1)
+
+    bank0, _ = assemble(breakout_source("pacman"), origin=0xF000, size=4096)
+    bank1, _ = assemble(pacman_bank1_source(), origin=0xF000, size=4096)
+    bank1 = bytearray(bank1)
+    bank1[0xFFC:0x1000] = bank0[0xFFC:0x1000]           # both banks carry the reset vector of bank 0
+    open(os.path.join(out, "synth_pacman.bin"), "wb").write(bank0 + bytes(bank1))
+    games["synth_pacman"] = dict(
+        file="synth_pacman.bin", stands_for="MsPacman", bank_scheme=1, controller=0,
+        actions=[ALE["NOOP"], ALE["UP"], ALE["RIGHT"], ALE["LEFT"], ALE["DOWN"], ALE["UPRIGHT"], ALE["UPLEFT"],
+                 ALE["DOWNRIGHT"], ALE["DOWNLEFT"]],
+        score_addr=[255, 76, 77], score2_addr=[255, 255, 255],
+        lives_addr=57, lives_shift=0, lives_mask=255, term_addr=57, term_mask=255, term_value=0)
 
     rom, _ = assemble(torture_source(), origin=0xF000, size=4096)
     open(os.path.join(out, "synth_torture.bin"), "wb").write(rom)
