@@ -552,7 +552,8 @@ int stm_ctx_create(stm_ctx **out, const stm_game_desc *desc, const uint8_t *rom,
             delete[] pre;
             CUDA_TRY(ctx, e1);
         }
-        size_t smem = (size_t)(64 * kStepThreads + ctx->rom_words + 256) * sizeof(uint32_t);
+        // the attribute is per kernel, not per ctx: always allow the largest cartridge (8 KB)
+        size_t smem = (size_t)(64 * kStepThreads + 8192 / 4 + 256) * sizeof(uint32_t);
         CUDA_TRY(ctx, cudaFuncSetAttribute(stm_step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         return ensure_scratch(ctx, 4096);
     };
