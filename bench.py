@@ -26,6 +26,10 @@ GAME = "synth_breakout"          # stands for BreakoutNoFrameskip-v4 (A = 4)
 METRIC = "tree_leaf_states_per_sec"
 UNIT = "leaves/s"
 CYCLES_PER_NODE_STEP = 4 * 262 * 76          # emulated CPU cycles per node-step (NTSC nominal)
+# DRAM bytes per env of one K2 launch, from the `ncu --set full` capture summarised in
+# profiles/r01_k2_step_ncu_full_summary.txt: (dram__bytes_read.sum + dram__bytes_write.sum) / 65 536 envs.
+# It is the native-frame scratch (2 frames x 168 sampled rows x 160 B) plus the 512 B state round trip.
+K2_NCU_DRAM_BYTES_PER_ENV = (59.884544e6 + 3.432066e9) / 65536
 
 
 def peaks():
@@ -154,6 +158,7 @@ def main():
         raise SystemExit("bench.py needs a CUDA device: the product path has no CPU fallback")
     torch.cuda.set_device(local)
     if world > 1:
+        os.environ["NCCL_DEBUG"] = "WARN"            # keep NCCL's version banner off stdout: one JSON line only
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     A, depth, R = 4, args.depth, args.roots
     L = R * A ** depth
@@ -240,6 +245,45 @@ def main():
     p1.record()
     barrier()
     ms_policy = p0.elapsed_time(p1)
+    # pipelined: tree expansion of batch i+1 (stream A) overlaps CNN + logits of batch i (stream B);
+    # two leaf buffers, events for the hand-offs.  K2 leaves issue slots and the tensor pipe idle,
+    # K4 leaves the ALUs idle: they co-run.
+    out2 = dict(stacks=torch.empty_like(out["stacks"]), rewards=torch.empty_like(out["rewards"]),
+                done=torch.empty_like(out["done"]), lives=torch.empty_like(out["lives"]), states=None)
+    bufs = [out, out2]
+    s_tree, s_net = torch.cuda.Stream(device=dev), torch.cuda.Stream(device=dev)
+    ready = [torch.cuda.Event(), torch.cuda.Event()]
+    free = [torch.cuda.Event(), torch.cuda.Event()]
+
+    def pipelined(nsteps):
+        main = torch.cuda.current_stream()
+        s_tree.wait_stream(main)
+        s_net.wait_stream(main)
+        for i in range(nsteps):
+            b = i & 1
+            with torch.cuda.stream(s_tree):
+                if i >= 2:
+                    s_tree.wait_event(free[b])
+                eng.bfs(states, stacks, depth, out=bufs[b])
+                ready[b].record(s_tree)
+            with torch.cuda.stream(s_net):
+                s_net.wait_event(ready[b])
+                hl, _ = eng.cnn_forward(bufs[b]["stacks"])
+                eng.cnn_forward(stacks)
+                ops.softtreemax_logits_full(eng, hl.reshape(R, A ** depth, A), bufs[b]["rewards"].reshape(R, -1),
+                                            val_coef, 1.0, 1.0, 0.001, False)
+                free[b].record(s_net)
+        main.wait_stream(s_tree)
+        main.wait_stream(s_net)
+
+    pipelined(2)
+    barrier()
+    r0, r1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    r0.record()
+    pipelined(args.steps)
+    r1.record()
+    barrier()
+    ms_pipe = r0.elapsed_time(r1)
     # K4 alone, same inputs, for its tensor roofline
     c0, c1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     c0.record()
@@ -292,7 +336,8 @@ def main():
     d2h = int(L * (4 + 1 + 4))
 
     from softtreemax_b200 import shard
-    ms_total, ms_e2e, ms_policy, ms_policy_e2e = shard.max_over_ranks([ms_total, ms_e2e, ms_policy, ms_policy_e2e], dev)
+    ms_total, ms_e2e, ms_policy, ms_policy_e2e, ms_pipe = shard.max_over_ranks(
+        [ms_total, ms_e2e, ms_policy, ms_policy_e2e, ms_pipe], dev)
 
     if rank == 0:
         ms_step = ms_total / args.steps
@@ -314,7 +359,10 @@ def main():
         k2 = gbs(k2_bytes, step_ms)
         roofline = {"kernel": "stm_step_kernel (K2: 6507+TIA+RIOT agent step)", "bound": "hbm",
                     "achieved": k2, "peak": hbm_peak, "unit": "GB/s", "frac": k2 / hbm_peak if k2 else None,
-                    "traffic": None, "peak_source": peak_src,
+                    "traffic": K2_NCU_DRAM_BYTES_PER_ENV * node_steps / max(1, step_n / args.steps),
+                    "traffic_source": "ncu --set full, profiles/r01_k2_step_ncu_full_summary.txt (per env) x envs per launch",
+                    "algorithmic_bytes_per_launch": k2_bytes / max(1, step_n / args.steps),
+                    "peak_source": peak_src,
                     "avg_launch_ms": step_ms / max(1, step_n), "launches": step_n,
                     "share_of_step": step_ms / ms_total,
                     "note": "K2 is issue-slot bound, not HBM bound (SURVEY §8d): its HBM floor is 2*S B/node-step, so the HBM "
@@ -340,6 +388,9 @@ def main():
         policy = {"metric": "softtreemax_policy_evals_per_sec", "value": world * R * args.steps / (ms_policy / 1e3),
                   "unit": "evals/s", "ms_per_step": ms_policy / args.steps,
                   "leaves_per_sec_through_cnn": world * L * args.steps / (ms_policy / 1e3),
+                  "pipelined": {"value": world * R * args.steps / (ms_pipe / 1e3), "unit": "evals/s",
+                                "ms_per_step": ms_pipe / args.steps,
+                                "how": "two streams: bfs of batch i+1 overlaps CNN + logits of batch i (double-buffered leaves)"},
                   "e2e": {"value": world * R * args.steps / (ms_policy_e2e / 1e3), "unit": "evals/s",
                           "h2d_bytes_per_step": int(hs_pin.numel() + hk_pin.numel()), "d2h_bytes_per_step": int(R * (A + 1) * 4),
                           "api": "pinned host roots -> stm_bfs + stm_cnn_forward + stm_logits_fwd -> host logits, values"},

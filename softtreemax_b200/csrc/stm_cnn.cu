@@ -361,6 +361,7 @@ int launch_layer(stm_ctx *ctx, const void *in, const __nv_bfloat16 *w, const flo
     size_t smem = (size_t)kStages * kABytes + (size_t)(kResidentW ? nchunks : kStages) * N * kChunkK * 2;
     if (!attr_done) {
         cudaFuncSetAttribute(stm_cnn_gemm_kernel<N, kResidentW>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 2048);
+        cudaFuncSetAttribute(stm_cnn_gemm_kernel<N, kResidentW>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
         attr_done = true;
     }
     long long tiles = (M + kTileM - 1) / kTileM;

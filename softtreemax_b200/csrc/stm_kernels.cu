@@ -555,6 +555,9 @@ int stm_ctx_create(stm_ctx **out, const stm_game_desc *desc, const uint8_t *rom,
         // the attribute is per kernel, not per ctx: always allow the largest cartridge (8 KB)
         size_t smem = (size_t)(64 * kStepThreads + 8192 / 4 + 256) * sizeof(uint32_t);
         CUDA_TRY(ctx, cudaFuncSetAttribute(stm_step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        // same L1/shared split as K4's kernels, so that CTAs of both can be resident on one SM when
+        // the policy pipeline runs tree expansion and the CNN on two streams
+        CUDA_TRY(ctx, cudaFuncSetAttribute(stm_step_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
         return ensure_scratch(ctx, 4096);
     };
     rc = body();
