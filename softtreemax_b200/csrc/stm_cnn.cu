@@ -116,14 +116,13 @@ __device__ __forceinline__ uint4 u8x8_to_bf16x8(uint32_t lo, uint32_t hi)
     return r;
 }
 
-constexpr int kStages = 4;
 constexpr int kProducerThreads = 128, kEpilogueThreads = 128;
 constexpr int kThreads2 = kProducerThreads + kEpilogueThreads + 32;      // + the MMA warp
 
 __device__ __forceinline__ void mbar_arrive(uint64_t *bar)
 { asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" :: "r"(smem_u32(bar)) : "memory"); }
 
-template <int N, bool kResidentW>
+template <int N, bool kResidentW, int kStages>
 __global__ void __launch_bounds__(kThreads2, 2)
 stm_cnn_gemm_kernel(const void *__restrict__ in, const __nv_bfloat16 *__restrict__ wt, const float *__restrict__ bias,
                     void *__restrict__ out, long long M_total, LayerGeom g, int n_off, int N_total)
@@ -352,7 +351,7 @@ struct CnnState {
     long long cap_images = 0;
 };
 
-template <int N, bool kResidentW>
+template <int N, bool kResidentW, int kStages>
 int launch_layer(stm_ctx *ctx, const void *in, const __nv_bfloat16 *w, const float *b, void *out, long long M,
                  const LayerGeom &g, int n_off, int N_total, cudaStream_t st)
 {
@@ -360,14 +359,14 @@ int launch_layer(stm_ctx *ctx, const void *in, const __nv_bfloat16 *w, const flo
     const int nchunks = g.K / kChunkK;
     size_t smem = (size_t)kStages * kABytes + (size_t)(kResidentW ? nchunks : kStages) * N * kChunkK * 2;
     if (!attr_done) {
-        cudaFuncSetAttribute(stm_cnn_gemm_kernel<N, kResidentW>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 2048);
-        cudaFuncSetAttribute(stm_cnn_gemm_kernel<N, kResidentW>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+        cudaFuncSetAttribute(stm_cnn_gemm_kernel<N, kResidentW, kStages>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 2048);
+        cudaFuncSetAttribute(stm_cnn_gemm_kernel<N, kResidentW, kStages>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
         attr_done = true;
     }
     long long tiles = (M + kTileM - 1) / kTileM;
     int per_sm = smem <= 100 * 1024 ? 2 : 1;                         // persistent: fill every SM, CTAs loop over tiles
     long long grid = tiles < 148LL * per_sm ? tiles : 148LL * per_sm;
-    stm_cnn_gemm_kernel<N, kResidentW><<<(unsigned)grid, kThreads2, smem, st>>>(in, w, b, out, M, g, n_off, N_total);
+    stm_cnn_gemm_kernel<N, kResidentW, kStages><<<(unsigned)grid, kThreads2, smem, st>>>(in, w, b, out, M, g, n_off, N_total);
     stm_internal_count_launch(ctx);
     cudaError_t e = cudaGetLastError();
     return e == cudaSuccess ? STM_OK : stm_internal_fail(ctx, STM_ERR_CUDA, cudaGetErrorString(e));
@@ -463,16 +462,16 @@ int stm_cnn_forward(stm_ctx *ctx, const uint8_t *obs, long long n, float *heads,
         long long c = n - i0 < chunk ? n - i0 : chunk;
         int rc;
         LayerGeom g1 = { MODE_CONV1, 400, 20, 84, 84, 4, 0, 4, 256, 32, 1, 0, 1.0f / 255.0f };
-        if ((rc = launch_layer<32, true>(ctx, obs + (size_t)i0 * 4 * 84 * 84, s->w[0], s->b[0], s->act1, c * 400, g1, 0, 32, st))) return rc;
+        if ((rc = launch_layer<32, true, 4>(ctx, obs + (size_t)i0 * 4 * 84 * 84, s->w[0], s->b[0], s->act1, c * 400, g1, 0, 32, st))) return rc;
         LayerGeom g2 = { MODE_NHWC, 81, 9, 20, 20, 32, 4 * 32, 2, 512, 64, 1, 0, 1.0f };
-        if ((rc = launch_layer<64, true>(ctx, s->act1, s->w[1], s->b[1], s->act2, c * 81, g2, 0, 64, st))) return rc;
+        if ((rc = launch_layer<64, true, 8>(ctx, s->act1, s->w[1], s->b[1], s->act2, c * 81, g2, 0, 64, st))) return rc;
         LayerGeom g3 = { MODE_NHWC, 49, 7, 9, 9, 64, 3 * 64, 1, 576, 64, 1, 0, 1.0f };
-        if ((rc = launch_layer<64, true>(ctx, s->act2, s->w[2], s->b[2], s->act3, c * 49, g3, 0, 64, st))) return rc;
+        if ((rc = launch_layer<64, true, 8>(ctx, s->act2, s->w[2], s->b[2], s->act3, c * 49, g3, 0, 64, st))) return rc;
         LayerGeom g4 = { MODE_NHWC, 1, 1, 1, 1, 3136, 3136, 1, 3136, 512, 1, 0, 1.0f };
         for (int half = 0; half < 2; half++)
-            if ((rc = launch_layer<256, false>(ctx, s->act3, s->w[3], s->b[3], s->feat, c, g4, half * 256, 512, st))) return rc;
+            if ((rc = launch_layer<256, false, 4>(ctx, s->act3, s->w[3], s->b[3], s->feat, c, g4, half * 256, 512, st))) return rc;
         LayerGeom g5 = { MODE_NHWC, 1, 1, 1, 1, 512, 512, 1, 512, A1, 0, 1, 1.0f };
-        if ((rc = launch_layer<32, true>(ctx, s->feat, s->w[4], s->b[4], heads + (size_t)i0 * A1, c, g5, 0, 32, st))) return rc;
+        if ((rc = launch_layer<32, true, 4>(ctx, s->feat, s->w[4], s->b[4], heads + (size_t)i0 * A1, c, g5, 0, 32, st))) return rc;
     }
     return STM_OK;
 }

@@ -296,15 +296,22 @@ stm_frames_kernel(const uint32_t *__restrict__ scratch, const uint8_t *__restric
                   const uint8_t *__restrict__ parent, uint8_t *__restrict__ child,
                   int n, int fanout, int nframes)
 {
-    __shared__ uint32_t srows[4][kTileEnvs * kPitch];      // [frame*2 + {y0,y1}]
+    __shared__ uint32_t srows[4][kTileEnvs * kPitch];      // [frame*2 + {y0,y1}], GREY values (LUT applied while staging)
     __shared__ uint8_t sgray[128];
+    __shared__ uint8_t sx0[STM_OBS_W], sfx[STM_OBS_W];     // source column and weight of every output column
     const int tile = blockIdx.x, oy = blockIdx.y, tid = threadIdx.x;
     const int env0 = tile * kTileEnvs;
     const int nenv = min(kTileEnvs, n - env0);
     if (tid < 128) sgray[tid] = c_gray[tid];
+    if (tid < STM_OBS_W) { int nx = 80 * tid + 19; sx0[tid] = (uint8_t)(nx / 42); sfx[tid] = (uint8_t)(nx % 42); }
+    __syncthreads();
     const int ny = 10 * oy + 3, y0 = ny >> 2, fy = ny & 3;
     const int y1 = min(y0 + 1, STM_VIS_H - 1);
     const uint4 *tbase = reinterpret_cast<const uint4 *>(scratch + (size_t)tile * kTileWords);
+    auto grey4 = [&](uint32_t w) -> uint32_t {
+        return (uint32_t)sgray[w & 127] | ((uint32_t)sgray[(w >> 8) & 127] << 8) |
+               ((uint32_t)sgray[(w >> 16) & 127] << 16) | ((uint32_t)sgray[(w >> 24) & 127] << 24);
+    };
     for (int i = tid; i < 4 * 10 * kTileEnvs; i += kFrameThreads) {
         int lane = i & 31, q = (i >> 5) % 10, rs = i / (10 * 32);
         int frame = rs >> 1, row = (rs & 1) ? y1 : y0;
@@ -312,42 +319,53 @@ stm_frames_kernel(const uint32_t *__restrict__ scratch, const uint8_t *__restric
         if (frame >= 2 - nframes)        // with a single rendered frame only slot 1 holds data
             v = tbase[((size_t)(frame * STM_VIS_H + row) * 10 + q) * kTileEnvs + lane];
         uint32_t *d = &srows[rs][lane * kPitch + 4 * q];
-        d[0] = v.x; d[1] = v.y; d[2] = v.z; d[3] = v.w;
+        if (frame >= 2 - nframes) { d[0] = grey4(v.x); d[1] = grey4(v.y); d[2] = grey4(v.z); d[3] = grey4(v.w); }
+        else { d[0] = 0; d[1] = 0; d[2] = 0; d[3] = 0; }
     }
     __syncthreads();
-    // new frame -> child[env][3][oy][:]
-    for (int i = tid; i < nenv * 21; i += kFrameThreads) {
-        int e = i / 21, wq = i % 21;
-        uint32_t packed = 0;
-        if (stepped[env0 + e]) {
+    // new frame -> child[env][3][oy][:]: 8 threads per env, each up to 3 packed words
+    {
+        const int e = tid >> 3, sub = tid & 7;
+        if (e < nenv) {
+            const bool live = stepped[env0 + e] != 0;
             const uint8_t *r00 = reinterpret_cast<const uint8_t *>(&srows[0][e * kPitch]);
             const uint8_t *r01 = reinterpret_cast<const uint8_t *>(&srows[1][e * kPitch]);
             const uint8_t *r10 = reinterpret_cast<const uint8_t *>(&srows[2][e * kPitch]);
             const uint8_t *r11 = reinterpret_cast<const uint8_t *>(&srows[3][e * kPitch]);
-            #pragma unroll
-            for (int k = 0; k < 4; k++) {
-                int ox = 4 * wq + k;
-                int nx = 80 * ox + 19, x0 = nx / 42, fx = nx - 42 * x0;
-                int x1 = min(x0 + 1, STM_VIS_W - 1);
-                int a00 = sgray[r00[x0] & 127], a01 = sgray[r00[x1] & 127];
-                int a10 = sgray[r01[x0] & 127], a11 = sgray[r01[x1] & 127];
-                int va = ((4 - fy) * ((42 - fx) * a00 + fx * a01) + fy * ((42 - fx) * a10 + fx * a11) + 84) / 168;
-                int b00 = sgray[r10[x0] & 127], b01 = sgray[r10[x1] & 127];
-                int b10 = sgray[r11[x0] & 127], b11 = sgray[r11[x1] & 127];
-                int vb = ((4 - fy) * ((42 - fx) * b00 + fx * b01) + fy * ((42 - fx) * b10 + fx * b11) + 84) / 168;
-                packed |= (uint32_t)max(va, vb) << (8 * k);
+            uint32_t *dst = reinterpret_cast<uint32_t *>(child + ((size_t)(env0 + e) * STM_STACK + 3) * STM_OBS_BYTES + oy * STM_OBS_W);
+            const int wy0 = 4 - fy, wy1 = fy;
+            for (int wq = sub; wq < 21; wq += 8) {
+                uint32_t packed = 0;
+                if (live) {
+                    #pragma unroll
+                    for (int k = 0; k < 4; k++) {
+                        const int ox = 4 * wq + k;
+                        const int x0 = sx0[ox], fx = sfx[ox], x1 = min(x0 + 1, STM_VIS_W - 1);
+                        const int w00 = wy0 * (42 - fx), w01 = wy0 * fx, w10 = wy1 * (42 - fx), w11 = wy1 * fx;
+                        const uint32_t va = (uint32_t)(w00 * r00[x0] + w01 * r00[x1] + w10 * r01[x0] + w11 * r01[x1] + 84) / 168u;
+                        const uint32_t vb = (uint32_t)(w00 * r10[x0] + w01 * r10[x1] + w10 * r11[x0] + w11 * r11[x1] + 84) / 168u;
+                        packed |= max(va, vb) << (8 * k);
+                    }
+                }
+                dst[wq] = packed;
             }
         }
-        uint32_t *dst = reinterpret_cast<uint32_t *>(child + ((size_t)(env0 + e) * STM_STACK + 3) * STM_OBS_BYTES + oy * STM_OBS_W);
-        dst[wq] = packed;
     }
-    // stack shift: child[env][0..2][oy] = parent[env / fanout][1..3][oy]
-    for (int i = tid; i < nenv * 63; i += kFrameThreads) {
-        int e = i / 63, r = i % 63, f = r / 21, wq = r % 21;
-        size_t pe = (size_t)(env0 + e) / fanout;
-        const uint32_t *s = reinterpret_cast<const uint32_t *>(parent + (pe * STM_STACK + f + 1) * STM_OBS_BYTES + oy * STM_OBS_W);
-        uint32_t *d = reinterpret_cast<uint32_t *>(child + ((size_t)(env0 + e) * STM_STACK + f) * STM_OBS_BYTES + oy * STM_OBS_W);
-        d[wq] = s[wq];
+    // stack shift: child[env][0..2] = parent[env / fanout][1..3], 21 168 contiguous bytes per env; this CTA
+    // moves its 1/84 share of the tile's 32 x 1 323 sixteen-byte pieces
+    {
+        constexpr int kPieces = 3 * STM_OBS_BYTES / 16;                 // 1 323 per env
+        constexpr int kShare = (kTileEnvs * kPieces + STM_OBS_H - 1) / STM_OBS_H;   // 504
+        for (int k = tid; k < kShare; k += kFrameThreads) {
+            int q = oy * kShare + k;
+            int e = q / kPieces, off = q - e * kPieces;
+            if (e < nenv) {
+                size_t pe = (size_t)(env0 + e) / fanout;
+                const uint4 *s = reinterpret_cast<const uint4 *>(parent + (pe * STM_STACK + 1) * STM_OBS_BYTES) + off;
+                uint4 *d = reinterpret_cast<uint4 *>(child + (size_t)(env0 + e) * STM_STACK * STM_OBS_BYTES) + off;
+                *d = *s;
+            }
+        }
     }
 }
 
@@ -659,7 +677,7 @@ int stm_frames(stm_ctx *ctx, const uint8_t *parent_stacks, uint8_t *child_stacks
     if (!ctx || !parent_stacks || !child_stacks || n < 0 || fanout < 1) return fail(ctx, STM_ERR_ARG, "stm_frames: bad argument");
     if (n > ctx->scratch_envs) return fail(ctx, STM_ERR_ARG, "stm_frames: n exceeds the native-frame scratch");
     if (ctx->last_render_frames == 0) return fail(ctx, STM_ERR_ARG, "stm_frames: no rendered stm_step precedes this call");
-    if (((uintptr_t)parent_stacks | (uintptr_t)child_stacks) & 3) return fail(ctx, STM_ERR_ARG, "stm_frames: stacks must be 4-byte aligned");
+    if (((uintptr_t)parent_stacks | (uintptr_t)child_stacks) & 15) return fail(ctx, STM_ERR_ARG, "stm_frames: stacks must be 16-byte aligned");
     if (n == 0) return STM_OK;
     return launch_frames(ctx, parent_stacks, child_stacks, n, fanout, (cudaStream_t)stream);
 }
@@ -820,8 +838,8 @@ extern "C" int stm_step_frames_noalloc(stm_ctx *ctx, uint8_t *states, const uint
     if (n > kNoAllocMaxEnvs)
         return fail(ctx, STM_ERR_ARG, "stm_step_frames_noalloc: n=%d exceeds the built-in scratch of %d envs "
                                       "(use stm_step + stm_frames, whose scratch is allocated and resizable)", n, kNoAllocMaxEnvs);
-    if (((uintptr_t)states & 15) || (((uintptr_t)parent_stacks | (uintptr_t)child_stacks) & 3))
-        return fail(ctx, STM_ERR_ARG, "stm_step_frames_noalloc: states must be 16-byte and stacks 4-byte aligned");
+    if (((uintptr_t)states | (uintptr_t)parent_stacks | (uintptr_t)child_stacks) & 15)
+        return fail(ctx, STM_ERR_ARG, "stm_step_frames_noalloc: states and stacks must be 16-byte aligned");
     const int dev = ctx->device;
     if (dev < 0 || dev >= kMaxDevices) return fail(ctx, STM_ERR_ARG, "stm_step_frames_noalloc: device index %d unsupported", dev);
     CUDA_TRY(ctx, cudaSetDevice(dev));
