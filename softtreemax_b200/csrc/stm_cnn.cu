@@ -12,7 +12,7 @@
 //   heads  M = n      K = 512             N = 32    (A action logits + 1 value, zero padded), fp32 out
 // "Implicit": the im2col matrix is never written to HBM — each CTA gathers its 128-row x 64-column
 // slice of A straight from the activation tensor into shared memory, already in the tensor core's
-// canonical K-major layout (8x8 core matrices, no swizzle), while the previous slice is being
+// 128-byte-swizzled K-major layout, while the previous slice is being
 // multiplied.  Weights are pre-tiled once into the same layout, so a slice of W is a linear copy.
 //
 // Per CTA (persistent: CTAs loop over 128-row output tiles): 9 warps, warp-specialised.
@@ -30,6 +30,7 @@
 #include <cuda_bf16.h>
 #include <stdint.h>
 #include <new>
+#include <cstdlib>
 #include "../../include/stm_b200.h"
 
 extern "C" int stm_internal_fail(stm_ctx *ctx, int code, const char *msg);
@@ -56,6 +57,7 @@ struct LayerGeom {
     int relu;
     int out_f32;     // 1: fp32 output with row stride n_real; 0: bf16 output with row stride N
     float scale;     // multiplies the accumulator before the bias (1/255 for conv1)
+    int debug;       // timing experiments only: bit0 producers skip loads, bit1 MMA thread skips the MMAs, bit2 epilogue skips stores
 };
 
 __device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -73,17 +75,23 @@ __device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity)
         :: "r"(smem_u32(bar)), "r"(parity) : "memory");
 }
 
-// shared-memory matrix descriptor: K-major, no swizzle; LBO = 128 B (next core matrix along K),
-// SBO = 1024 B (next 8-row group: 8 core matrices of one 64-wide slice lie between)
+// shared-memory matrix descriptor: K-major, 128-byte swizzle.  A slice is [rows][64 bf16] = one 128-byte
+// line per row; the eight 16-byte pieces of row r are stored at piece position (c ^ (r & 7)) — what TMA's
+// SWIZZLE_128B would produce — so that both "one lane per row" and "eight lanes per row" writers are
+// bank-conflict-light and the tensor core reads conflict-free.  SBO = 1024 B (next 8-row group); LBO is
+// unused for a slice exactly one swizzle span wide; tile bases are 1024-byte aligned; successive K = 16
+// MMAs advance the start address by 32 bytes inside the span.
 __device__ __forceinline__ uint64_t make_desc(uint32_t saddr)
 {
     uint64_t d = 0;
     d |= (uint64_t)((saddr & 0x3FFFF) >> 4);
-    d |= (uint64_t)(128 >> 4) << 16;
+    d |= (uint64_t)1 << 16;
     d |= (uint64_t)(1024 >> 4) << 32;
     d |= (uint64_t)1 << 46;
+    d |= (uint64_t)2 << 61;
     return d;
 }
+__device__ __forceinline__ uint32_t swz(uint32_t row, uint32_t piece) { return row * 128u + ((piece ^ (row & 7u)) << 4); }
 // instruction descriptor, kind::f16: D = f32, A = B = bf16, both K-major, M = 128
 __device__ __forceinline__ uint32_t make_idesc(int N)
 {
@@ -128,7 +136,8 @@ stm_cnn_gemm_kernel(const void *__restrict__ in, const __nv_bfloat16 *__restrict
                     void *__restrict__ out, long long M_total, LayerGeom g, int n_off, int N_total)
 {
     constexpr int kBBytes = N * kChunkK * 2;
-    extern __shared__ __align__(1024) uint8_t smem[];
+    extern __shared__ __align__(1024) uint8_t smem_raw[];
+    uint8_t *smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);      // swizzled tiles need 1024-byte bases
     uint8_t *sA = smem;                                   // kStages x 16 KB
     uint8_t *sB = smem + kStages * kABytes;               // resident: nchunks x kBBytes; streamed: kStages x kBBytes
     __shared__ __align__(8) uint64_t full[kStages], empty[kStages], tfull[2], tempty[2];
@@ -168,33 +177,46 @@ stm_cnn_gemm_kernel(const void *__restrict__ in, const __nv_bfloat16 *__restrict
         // published: 16-byte cp.async copies land straight in the ring (no registers), and an item is
         // handed to the MMA thread once its group has completed and been fenced to the async proxy.
         constexpr int kDepth = kStages - 1;
-        const uint32_t a_row_off = (uint32_t)(tid >> 3) * 1024u + (uint32_t)(tid & 7) * 16u;
+        // eight consecutive lanes fetch the eight 16-byte pieces of one row's 128-byte K slice: every
+        // warp-level copy touches four whole lines of global memory and four whole lines of shared memory
+        const uint32_t piece = (uint32_t)tid & 7u, row0 = (uint32_t)tid >> 3;          // rows row0 + 16 j
         const long long my_tiles = blockIdx.x < ntiles ? (ntiles - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
         const long long items = my_tiles * nchunks;
         long long tile = blockIdx.x;
         int kc = 0;
-        const __nv_bfloat16 *src16 = nullptr;
-        bool row_ok = false;
+        const uint8_t *rowp[8];
+        uint32_t okmask = 0;
         for (long long i = 0; i < items + kDepth; i++) {
             if (i < items) {
                 if (kc == 0) {
-                    const long long m = tile * kTileM + tid;
-                    row_ok = m < M_total;
-                    const long long img = row_ok ? m / g.P : 0;
-                    const int pos = row_ok ? (int)(m % g.P) : 0;
-                    const int oy = pos / g.OW, ox = pos % g.OW;
-                    src16 = reinterpret_cast<const __nv_bfloat16 *>(in) + (((size_t)img * g.IH + oy * g.S) * g.IW + ox * g.S) * g.C;
+                    okmask = 0;
+                    #pragma unroll
+                    for (int j = 0; j < 8; j++) {
+                        const long long m = tile * kTileM + row0 + 16 * j;
+                        const bool ok = m < M_total;
+                        const long long img = ok ? m / g.P : 0;
+                        const int pos = ok ? (int)(m % g.P) : 0;
+                        const int oy = pos / g.OW, ox = pos % g.OW;
+                        rowp[j] = reinterpret_cast<const uint8_t *>(reinterpret_cast<const __nv_bfloat16 *>(in)
+                                  + (((size_t)img * g.IH + oy * g.S) * g.IW + ox * g.S) * g.C) + piece * 16;
+                        okmask |= (ok ? 1u : 0u) << j;
+                    }
                 }
                 const uint32_t st = (uint32_t)(i % kStages), ph = (uint32_t)((i / kStages) & 1);
                 mbar_wait(&empty[st], ph ^ 1);
                 const int k0 = kc * kChunkK;
                 const int kh = k0 / g.KWC, koff = k0 - kh * g.KWC;
-                const uint8_t *p = reinterpret_cast<const uint8_t *>(src16 + (size_t)kh * g.IW * g.C + koff);
-                const uint32_t dst = smem_u32(sA + st * kABytes + a_row_off);
-                const uint32_t nbytes = row_ok ? 16u : 0u;                      // 0 => zero fill
+                const size_t goff = ((size_t)kh * g.IW * g.C + koff) * 2;
+                const uint32_t dst0 = smem_u32(sA + st * kABytes);
+                if (!(g.debug & 1)) {
                 #pragma unroll
-                for (int kg = 0; kg < 8; kg++)
-                    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" :: "r"(dst + kg * 128), "l"(p + kg * 16), "r"(nbytes) : "memory");
+                for (int j = 0; j < 8; j++) {
+                    const uint32_t r = row0 + 16 * j;
+                    const uint32_t nbytes = (okmask >> j) & 1u ? 16u : 0u;         // 0 => zero fill
+                    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;"
+                                 :: "r"(dst0 + swz(r, piece)), "l"(rowp[j] + goff), "r"(nbytes) : "memory");
+                }
+                }
                 if (!kResidentW) {
                     const uint8_t *wsrc = reinterpret_cast<const uint8_t *>(wt + (size_t)kc * N_total * kChunkK + (size_t)n_off * kChunkK);
                     const uint32_t wdst = smem_u32(sB + st * kBBytes);
@@ -213,7 +235,6 @@ stm_cnn_gemm_kernel(const void *__restrict__ in, const __nv_bfloat16 *__restrict
         }
     } else if (warp < 4) {
         // ===================== producers, u8 NCHW input (conv1): registers, converted to bf16 =====================
-        const uint32_t a_row_off = (uint32_t)(tid >> 3) * 1024u + (uint32_t)(tid & 7) * 16u;
         uint32_t it = 0;
         for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
             const long long m = tile * kTileM + tid;
@@ -239,10 +260,10 @@ stm_cnn_gemm_kernel(const void *__restrict__ in, const __nv_bfloat16 *__restrict
                 if (kc + 1 < nchunks) load(kc + 1, nxt);
                 const uint32_t st = it % kStages, ph = (it / kStages) & 1;
                 mbar_wait(&empty[st], ph ^ 1);                      // slot free (first pass: returns at once)
-                uint8_t *arow = sA + st * kABytes + a_row_off;
+                uint8_t *abase = sA + st * kABytes;
                 #pragma unroll
                 for (int kg = 0; kg < 8; kg++)
-                    *reinterpret_cast<uint4 *>(arow + kg * 128) = u8x8_to_bf16x8(cur[kg].x, cur[kg].y);
+                    *reinterpret_cast<uint4 *>(abase + swz((uint32_t)tid, (uint32_t)kg)) = u8x8_to_bf16x8(cur[kg].x, cur[kg].y);
                 asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
                 mbar_arrive(&full[st]);
             }
@@ -263,9 +284,11 @@ stm_cnn_gemm_kernel(const void *__restrict__ in, const __nv_bfloat16 *__restrict
                     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
                     const uint32_t a0 = smem_u32(sA + st * kABytes);
                     const uint32_t b0 = smem_u32(sB + (kResidentW ? (size_t)kc : (size_t)st) * kBBytes);
+                    if (!(g.debug & 2)) {
                     #pragma unroll
                     for (int j = 0; j < kChunkK / 16; j++)
-                        umma(tmem_d, make_desc(a0 + j * 256), make_desc(b0 + j * 256), idesc, (kc | j) ? 1u : 0u);
+                        umma(tmem_d, make_desc(a0 + j * 32), make_desc(b0 + j * 32), idesc, (kc | j) ? 1u : 0u);
+                    }
                     umma_commit(&empty[st]);                        // frees the slot when these MMAs are done
                 }
                 umma_commit(&tfull[buf]);                           // accumulator complete
@@ -292,7 +315,7 @@ stm_cnn_gemm_kernel(const void *__restrict__ in, const __nv_bfloat16 *__restrict
                                "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
                              : "r"(taddr + (uint32_t)c0));
                 asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-                if (row_ok) {
+                if (row_ok && !(g.debug & 4)) {
                     float v[16];
                     #pragma unroll
                     for (int j = 0; j < 16; j++) {
@@ -328,8 +351,8 @@ stm_cnn_gemm_kernel(const void *__restrict__ in, const __nv_bfloat16 *__restrict
 }
 
 // fp32 torch-layout weights (n_real, K) -> bf16, K reordered (k = s*C + c <- column c*KHW + s), zero padded
-// to N rows, tiled per 64-wide K slice in the tensor core's canonical K-major layout:
-//   element (n, k): slice k/64, byte offset (n/8)*1024 + ((k%64)/8)*128 + (n%8)*16 + (k%8)*2
+// to N rows, tiled per 64-wide K slice in the 128-byte-swizzled K-major layout the kernel uses:
+//   element (n, k): slice k/64, byte offset n*128 + ((((k%64)/8) ^ (n%8)) * 16) + (k%8)*2
 __global__ void stm_tile_weights_kernel(const float *__restrict__ w, __nv_bfloat16 *__restrict__ dst, int n_real, int N,
                                         int K, int KHW, int C)
 {
@@ -339,7 +362,7 @@ __global__ void stm_tile_weights_kernel(const float *__restrict__ w, __nv_bfloat
     int s = k / C, c = k % C;
     float v = n < n_real ? w[(size_t)n * K + (size_t)c * KHW + s] : 0.f;
     int kc = k / 64, kk = k % 64;
-    size_t off = (size_t)kc * N * 64 + (size_t)(n / 8) * 512 + (kk / 8) * 64 + (n % 8) * 8 + (kk % 8);
+    size_t off = (size_t)kc * N * 64 + (size_t)n * 64 + (((kk / 8) ^ (n % 8)) * 8) + (kk % 8);
     dst[off] = __float2bfloat16_rn(v);
 }
 
@@ -357,7 +380,7 @@ int launch_layer(stm_ctx *ctx, const void *in, const __nv_bfloat16 *w, const flo
 {
     static bool attr_done = false;
     const int nchunks = g.K / kChunkK;
-    size_t smem = (size_t)kStages * kABytes + (size_t)(kResidentW ? nchunks : kStages) * N * kChunkK * 2;
+    size_t smem = (size_t)kStages * kABytes + (size_t)(kResidentW ? nchunks : kStages) * N * kChunkK * 2 + 1024;
     if (!attr_done) {
         cudaFuncSetAttribute(stm_cnn_gemm_kernel<N, kResidentW, kStages>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 2048);
         cudaFuncSetAttribute(stm_cnn_gemm_kernel<N, kResidentW, kStages>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
@@ -458,19 +481,21 @@ int stm_cnn_forward(stm_ctx *ctx, const uint8_t *obs, long long n, float *heads,
         s->cap_images = chunk;
     }
     const int A1 = s->A + 1;
+    const char *dbg_env = getenv("STM_CNN_DEBUG");
+    const int dbg = dbg_env ? atoi(dbg_env) : 0;
     for (long long i0 = 0; i0 < n; i0 += chunk) {
         long long c = n - i0 < chunk ? n - i0 : chunk;
         int rc;
-        LayerGeom g1 = { MODE_CONV1, 400, 20, 84, 84, 4, 0, 4, 256, 32, 1, 0, 1.0f / 255.0f };
+        LayerGeom g1 = { MODE_CONV1, 400, 20, 84, 84, 4, 0, 4, 256, 32, 1, 0, 1.0f / 255.0f, dbg };
         if ((rc = launch_layer<32, true, 4>(ctx, obs + (size_t)i0 * 4 * 84 * 84, s->w[0], s->b[0], s->act1, c * 400, g1, 0, 32, st))) return rc;
-        LayerGeom g2 = { MODE_NHWC, 81, 9, 20, 20, 32, 4 * 32, 2, 512, 64, 1, 0, 1.0f };
+        LayerGeom g2 = { MODE_NHWC, 81, 9, 20, 20, 32, 4 * 32, 2, 512, 64, 1, 0, 1.0f, dbg };
         if ((rc = launch_layer<64, true, 8>(ctx, s->act1, s->w[1], s->b[1], s->act2, c * 81, g2, 0, 64, st))) return rc;
-        LayerGeom g3 = { MODE_NHWC, 49, 7, 9, 9, 64, 3 * 64, 1, 576, 64, 1, 0, 1.0f };
+        LayerGeom g3 = { MODE_NHWC, 49, 7, 9, 9, 64, 3 * 64, 1, 576, 64, 1, 0, 1.0f, dbg };
         if ((rc = launch_layer<64, true, 8>(ctx, s->act2, s->w[2], s->b[2], s->act3, c * 49, g3, 0, 64, st))) return rc;
-        LayerGeom g4 = { MODE_NHWC, 1, 1, 1, 1, 3136, 3136, 1, 3136, 512, 1, 0, 1.0f };
+        LayerGeom g4 = { MODE_NHWC, 1, 1, 1, 1, 3136, 3136, 1, 3136, 512, 1, 0, 1.0f, dbg };
         for (int half = 0; half < 2; half++)
             if ((rc = launch_layer<256, false, 4>(ctx, s->act3, s->w[3], s->b[3], s->feat, c, g4, half * 256, 512, st))) return rc;
-        LayerGeom g5 = { MODE_NHWC, 1, 1, 1, 1, 512, 512, 1, 512, A1, 0, 1, 1.0f };
+        LayerGeom g5 = { MODE_NHWC, 1, 1, 1, 1, 512, 512, 1, 512, A1, 0, 1, 1.0f, dbg };
         if ((rc = launch_layer<32, true, 4>(ctx, s->feat, s->w[4], s->b[4], heads + (size_t)i0 * A1, c, g5, 0, 32, st))) return rc;
     }
     return STM_OK;
