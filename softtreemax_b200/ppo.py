@@ -1,0 +1,113 @@
+"""Minimal PPO driver for the SoftTreeMax policy — the caller on the other side of the hot path
+(SURVEY §8f rows 1-2).  The reference uses Stable-Baselines3 1.4.0's PPO (main.py:52-68,78), a
+third-party dependency that is not installable here; this restates its algorithm for the single-env
+case the tree path uses (n_envs = 1, main.py:47): rollout of n_steps with policy.forward, GAE(lambda),
+n_epochs x minibatches of clipped-surrogate + value + entropy loss through policy.evaluate_actions,
+Adam(eps=1e-5) with linearly decayed learning rate and clip range, gradient-norm clipping 0.5.
+"""
+import numpy as np
+import torch as th
+
+
+def get_linear_fn(start, end, end_fraction):
+    """SB3's schedule: value as a function of progress_remaining (1 -> 0)."""
+    def fn(progress_remaining):
+        if (1 - progress_remaining) > end_fraction:
+            return end
+        return start + (1 - progress_remaining) * (end - start) / end_fraction
+    return fn
+
+
+class PPO:
+    def __init__(self, policy, env, learning_rate=2.5e-4, n_steps=128, batch_size=32, n_epochs=3, gamma=0.99,
+                 gae_lambda=0.95, clip_range=0.1, ent_coef=0.01, vf_coef=1.0, max_grad_norm=0.5,
+                 policy_kwargs=None, verbose=0, seed=None):
+        self.env = env
+        self.lr = learning_rate if callable(learning_rate) else (lambda _: learning_rate)
+        self.clip = clip_range if callable(clip_range) else (lambda _: clip_range)
+        self.n_steps, self.batch_size, self.n_epochs = n_steps, batch_size, n_epochs
+        self.gamma, self.gae_lambda = gamma, gae_lambda
+        self.ent_coef, self.vf_coef, self.max_grad_norm = ent_coef, vf_coef, max_grad_norm
+        self.verbose = verbose
+        self.rng = np.random.RandomState(seed)
+        self.policy = policy(env.observation_space, env.action_space, self.lr, **(policy_kwargs or {}))
+        self.num_timesteps = 0
+        self.log = []
+
+    def _rollout(self, obs, episode_start):
+        n = self.n_steps
+        buf = dict(obs=np.zeros((n, 4, 84, 84), np.uint8), act=np.zeros(n, np.int64), rew=np.zeros(n, np.float32),
+                   start=np.zeros(n, np.float32), val=np.zeros(n, np.float32), logp=np.zeros(n, np.float32))
+        ep_rewards = []
+        for t in range(n):
+            with th.no_grad():
+                a, v, lp = self.policy.forward(th.from_numpy(obs).float()[None])
+            a = int(a)
+            buf["obs"][t], buf["act"][t], buf["start"][t] = obs, a, float(episode_start)
+            buf["val"][t], buf["logp"][t] = float(v.reshape(-1)[0]), float(lp.reshape(-1)[0])
+            obs, r, done, info = self.env.step(a)
+            buf["rew"][t] = float(r)
+            self._ep_ret += float(info.get("orig_reward", r))
+            self.num_timesteps += 1
+            episode_start = done
+            if done:
+                ep_rewards.append(self._ep_ret)
+                self._ep_ret = 0.0
+                obs = self.env.reset()
+        with th.no_grad():                                   # bootstrap with the depth-0 value of the last obs
+            feats = self.policy.extract_features(th.from_numpy(obs)[None].to(self.policy.device))
+            last_val = float(self.policy.value_net(feats).reshape(-1)[0])
+        adv = np.zeros(n, np.float32)
+        gae = 0.0
+        for t in reversed(range(n)):                         # GAE(lambda), SB3 RolloutBuffer.compute_returns_and_advantage
+            nonterminal = 1.0 - (float(episode_start) if t == n - 1 else buf["start"][t + 1])
+            next_val = last_val if t == n - 1 else buf["val"][t + 1]
+            delta = buf["rew"][t] + self.gamma * next_val * nonterminal - buf["val"][t]
+            gae = delta + self.gamma * self.gae_lambda * nonterminal * gae
+            adv[t] = gae
+        buf["adv"], buf["ret"] = adv, adv + buf["val"]
+        return buf, obs, episode_start, ep_rewards
+
+    def _train(self, buf, progress_remaining):
+        pol = self.policy
+        lr, clip = self.lr(progress_remaining), self.clip(progress_remaining)
+        for g in pol.optimizer.param_groups:
+            g["lr"] = lr
+        dev = pol.device
+        stats = []
+        for _ in range(self.n_epochs):
+            perm = self.rng.permutation(self.n_steps)
+            for s in range(0, self.n_steps, self.batch_size):
+                idx = perm[s:s + self.batch_size]
+                obs = th.from_numpy(buf["obs"][idx]).float()
+                act = th.from_numpy(buf["act"][idx]).to(dev)
+                adv = th.from_numpy(buf["adv"][idx]).to(dev)
+                adv = (adv - adv.mean()) / (adv.std() + 1e-8)
+                values, logp, entropy = pol.evaluate_actions(obs, act)
+                ratio = th.exp(logp - th.from_numpy(buf["logp"][idx]).to(dev))
+                pg = -th.min(adv * ratio, adv * th.clamp(ratio, 1 - clip, 1 + clip)).mean()
+                vl = th.nn.functional.mse_loss(th.from_numpy(buf["ret"][idx]).to(dev), values.reshape(-1))
+                ent = -entropy.mean()
+                loss = pg + self.ent_coef * ent + self.vf_coef * vl
+                pol.optimizer.zero_grad()
+                loss.backward()
+                th.nn.utils.clip_grad_norm_(pol.parameters(), self.max_grad_norm)
+                pol.optimizer.step()
+                stats.append((float(loss), float(pg), float(vl), float(-ent)))
+        return np.mean(stats, axis=0)
+
+    def learn(self, total_timesteps, callback=None):
+        obs = self.env.reset()
+        episode_start, self._ep_ret = True, 0.0
+        while self.num_timesteps < total_timesteps:
+            buf, obs, episode_start, ep = self._rollout(obs, episode_start)
+            st = self._train(buf, 1.0 - self.num_timesteps / total_timesteps)
+            rec = dict(timesteps=self.num_timesteps, loss=st[0], pg_loss=st[1], value_loss=st[2], entropy=st[3],
+                       episodes=len(ep), ep_reward_mean=float(np.mean(ep)) if ep else None,
+                       beta=float(self.policy.beta), alpha=float(self.policy.alpha))
+            self.log.append(rec)
+            if self.verbose:
+                print(rec, flush=True)
+            if callback is not None:
+                callback(self, rec)
+        return self

@@ -127,3 +127,24 @@ def test_device_roots_match_oracle_roots():
             assert np.array_equal(sk.cpu().numpy(), want_k), name
         finally:
             eng.close()
+
+
+def test_ppo_loop_runs_and_updates():
+    """Two PPO iterations (2 x 128 env steps, 3 epochs x 4 minibatches each) through the mirrored
+    policy: rollouts use K1-K5, the update uses K5's backward + torch autograd for the CNN."""
+    from softtreemax_b200.envs import CuleEnv
+    from softtreemax_b200.policy import ActorCriticCnnTSPolicy
+    from softtreemax_b200.ppo import PPO, get_linear_fn
+    env = CuleEnv(device="cuda:0", env_kwargs=ENV_KWARGS, clip_reward=True, fire_reset=True)
+    kw = dict(step_env=env, gamma=0.99, tree_depth=1, buffer_size=128, learn_alpha=False, learn_beta=True, max_width=-1,
+              use_leaves_v=False, is_cumulative_mode=False, regularization=0.001)
+    torch.manual_seed(0)
+    model = PPO(ActorCriticCnnTSPolicy, env, learning_rate=get_linear_fn(2.5e-4, 0, 1), clip_range=get_linear_fn(0.1, 0, 1),
+                policy_kwargs=kw, seed=0)
+    w0 = model.policy.action_net.weight.detach().clone()
+    b0 = float(model.policy.beta)
+    model.learn(256)
+    assert len(model.log) == 2 and all(np.isfinite(r["loss"]) for r in model.log)
+    assert not torch.equal(w0, model.policy.action_net.weight.detach())
+    assert float(model.policy.beta) != b0
+    assert len(model.policy.obs2leaves_dict) <= 128 + 1            # leaf cache is evicted (actor_critic_ts.py:99-103)
