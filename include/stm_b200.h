@@ -119,17 +119,22 @@ int stm_timing_read(stm_ctx *ctx, float *ms_by_kind, int *launches_by_kind);
  * Replaces policies/actor_critic_ts.py:60-95 and :147-188 and utils.py:52-57.
  *   head R x L x A f32, rewards R x L f32, depth0 R x A f32 or NULL (alpha-mix term treated as 0),
  *   values R x L f32 or NULL; logits R x A (out), raw R x A or NULL (z before the mix),
- *   vmax R or NULL (max_l val_coef*values + reward: the use_leaves_v root value, :62-63). */
+ *   vmax R or NULL (max_l val_coef*values + reward: the use_leaves_v root value, :62-63);
+ *   group R x L i32 or NULL: the root action of every leaf of a width-limited tree (the reference's
+ *   first_action, actor_critic_ts.py:70-79,163-171) — then count = members*A, actions without a
+ *   surviving leaf get -inf, and the reference's zero-filled scatter is reproduced (each non-member
+ *   slot adds exp(0) to the E-mode sum).  NULL = full-width tree, leaf l belongs to action l/(L/A). */
 int stm_logits_fwd(stm_ctx *ctx, const float *head, const float *rewards, const float *depth0,
-                   const float *values, int R, int L, int A, float val_coef, float beta, float alpha,
-                   float eps, int cumulative, float *logits, float *raw, float *vmax, void *stream);
+                   const float *values, const int *group, int R, int L, int A, float val_coef, float beta,
+                   float alpha, float eps, int cumulative, float *logits, float *raw, float *vmax,
+                   void *stream);
 /* Backward of stm_logits_fwd w.r.t. head, depth0, beta and alpha (what evaluate_actions needs from
  * autograd, actor_critic_ts.py:106-194).  dhead R x L x A, ddepth0 R x A or NULL, dbeta / dalpha: R
  * per-root partial sums (the caller adds them up). */
-int stm_logits_bwd(stm_ctx *ctx, const float *head, const float *rewards, const float *depth0, int R,
-                   int L, int A, float val_coef, float beta, float alpha, float eps, int cumulative,
-                   const float *dlogits, float *dhead, float *ddepth0, float *dbeta, float *dalpha,
-                   void *stream);
+int stm_logits_bwd(stm_ctx *ctx, const float *head, const float *rewards, const float *depth0,
+                   const int *group, int R, int L, int A, float val_coef, float beta, float alpha, float eps,
+                   int cumulative, const float *dlogits, float *dhead, float *ddepth0, float *dbeta,
+                   float *dalpha, void *stream);
 
 /* K4 — NatureCNN + heads.  stm_cnn_set_weights takes DEVICE pointers to fp32 parameters in the
  * layout SB3 1.4.0's ActorCriticCnnPolicy holds them (features_extractor.cnn.{0,2,4}, .linear.0,

@@ -16,16 +16,30 @@ import torch as th
 import torch.nn.functional as F
 
 
-def softtreemax_logits(head, rewards, A, val_coef, beta, alpha, eps, cumulative, depth0=None, values=None):
-    """head (R, L, A), rewards (R, L) -> (logits (R, A), raw (R, A), vmax (R,) or None)."""
+def softtreemax_logits(head, rewards, A, val_coef, beta, alpha, eps, cumulative, depth0=None, values=None,
+                       first_action=None):
+    """head (R, L, A), rewards (R, L) -> (logits (R, A), raw (R, A), vmax (R,) or None).
+    first_action (R, L) int: width-limited tree (actor_critic_ts.py:70-79), else full width (:68-69)."""
     R, L, _ = head.shape
     m = val_coef * head + rewards.unsqueeze(-1)                       # actor_critic_ts.py:66
-    per = beta * m.reshape(R, A, -1)                                  # :68  row a = leaves under root action a
-    cnt = per.shape[2]
+    if first_action is None:
+        per = beta * m.reshape(R, A, -1)                              # :68  row a = leaves under root action a
+        cnt = th.full((R, A), float(per.shape[2]))
+    else:
+        # :71-77 — scatter into a ZERO tensor (A, L, A); non-member slots stay 0 and take part in logsumexp
+        sub = th.zeros(R, A, L, A)
+        cnt = th.zeros(R, A)
+        for r in range(R):
+            fa = first_action[r].long()
+            sub[r, fa, th.arange(L), :] = m[r]
+            v, c = th.unique(fa, return_counts=True)
+            cnt[r, v] = c.float() * A
+        per = beta * sub.reshape(R, A, -1)
     if cumulative:
         raw = per.sum(dim=2) / cnt                                    # :81
     else:
-        raw = th.logsumexp(per, dim=2) - math.log(cnt)                # :84-85
+        raw = th.logsumexp(per, dim=2) - th.log(cnt)                  # :84-85
+    raw = th.where(cnt == 0, th.full_like(raw, -math.inf), raw)       # :86
     z = th.where(th.isnan(raw), th.zeros_like(raw), raw)              # :88-90
     d0 = depth0 if depth0 is not None else 0.0
     x = alpha * z + (1 - alpha) * d0                                  # :94

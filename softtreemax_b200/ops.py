@@ -12,7 +12,7 @@ def _p(t):
 
 class _SoftTreeMaxLogits(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, eng, head, rewards, depth0, beta, alpha, val_coef, eps, cumulative):
+    def forward(ctx, eng, head, rewards, depth0, beta, alpha, val_coef, eps, cumulative, group):
         R, L, A = head.shape
         head = head.contiguous().float()
         rewards = rewards.contiguous().float()
@@ -20,9 +20,10 @@ class _SoftTreeMaxLogits(torch.autograd.Function):
         logits = torch.empty((R, A), dtype=torch.float32, device=head.device)
         b = float(beta.detach()) if isinstance(beta, torch.Tensor) else float(beta)
         a = float(alpha.detach()) if isinstance(alpha, torch.Tensor) else float(alpha)
-        check(lib().stm_logits_fwd(eng._h, _p(head), _p(rewards), _p(d0), None, R, L, A, float(val_coef), b, a,
+        grp = group.contiguous().to(torch.int32) if group is not None else None
+        check(lib().stm_logits_fwd(eng._h, _p(head), _p(rewards), _p(d0), None, _p(grp), R, L, A, float(val_coef), b, a,
                                    float(eps), int(cumulative), _p(logits), None, None, eng._stream()), eng._h)
-        ctx.eng, ctx.scal = eng, (R, L, A, float(val_coef), b, a, float(eps), int(cumulative))
+        ctx.eng, ctx.scal, ctx.grp = eng, (R, L, A, float(val_coef), b, a, float(eps), int(cumulative)), grp
         ctx.save_for_backward(head, rewards, d0 if d0 is not None else torch.empty(0, device=head.device))
         ctx.has_d0 = d0 is not None
         ctx.beta_t = isinstance(beta, torch.Tensor)
@@ -40,19 +41,21 @@ class _SoftTreeMaxLogits(torch.autograd.Function):
         dd0 = torch.empty((R, A), dtype=torch.float32, device=head.device) if d0 is not None else None
         dbeta = torch.empty((R,), dtype=torch.float32, device=head.device)
         dalpha = torch.empty((R,), dtype=torch.float32, device=head.device)
-        check(lib().stm_logits_bwd(eng._h, _p(head), _p(rewards), _p(d0), R, L, A, val_coef, b, a, eps, cum,
+        check(lib().stm_logits_bwd(eng._h, _p(head), _p(rewards), _p(d0), _p(ctx.grp), R, L, A, val_coef, b, a, eps, cum,
                                    _p(dlogits), _p(dhead), _p(dd0), _p(dbeta), _p(dalpha), eng._stream()), eng._h)
         return (None, dhead, None, dd0, dbeta.sum() if ctx.beta_t else None,
-                dalpha.sum() if ctx.alpha_t else None, None, None, None)
+                dalpha.sum() if ctx.alpha_t else None, None, None, None, None)
 
 
-def softtreemax_logits(eng, head, rewards, val_coef, beta, alpha, eps, cumulative, depth0=None):
+def softtreemax_logits(eng, head, rewards, val_coef, beta, alpha, eps, cumulative, depth0=None, group=None):
     """head (R, L, A), rewards (R, L) -> regularised logits (R, A); differentiable in head, depth0,
-    beta and alpha (tensors).  policies/actor_critic_ts.py:60-95 / :147-188."""
-    return _SoftTreeMaxLogits.apply(eng, head, rewards, depth0, beta, alpha, val_coef, eps, cumulative)
+    beta and alpha (tensors).  group (R, L) int: root action of every leaf of a width-limited tree.
+    policies/actor_critic_ts.py:60-95 / :147-188."""
+    return _SoftTreeMaxLogits.apply(eng, head, rewards, depth0, beta, alpha, val_coef, eps, cumulative, group)
 
 
-def softtreemax_logits_full(eng, head, rewards, val_coef, beta, alpha, eps, cumulative, depth0=None, values=None):
+def softtreemax_logits_full(eng, head, rewards, val_coef, beta, alpha, eps, cumulative, depth0=None, values=None,
+                            group=None):
     """No-grad variant that also returns the un-mixed logits and the use_leaves_v root value."""
     R, L, A = head.shape
     head, rewards = head.contiguous().float(), rewards.contiguous().float()
@@ -61,7 +64,8 @@ def softtreemax_logits_full(eng, head, rewards, val_coef, beta, alpha, eps, cumu
     logits = torch.empty((R, A), dtype=torch.float32, device=head.device)
     raw = torch.empty_like(logits)
     vmax = torch.empty((R,), dtype=torch.float32, device=head.device) if v is not None else None
-    check(lib().stm_logits_fwd(eng._h, _p(head), _p(rewards), _p(d0), _p(v), R, L, A, float(val_coef), float(beta),
+    grp = group.contiguous().to(torch.int32) if group is not None else None
+    check(lib().stm_logits_fwd(eng._h, _p(head), _p(rewards), _p(d0), _p(v), _p(grp), R, L, A, float(val_coef), float(beta),
                                float(alpha), float(eps), int(cumulative), _p(logits), _p(raw), _p(vmax),
                                eng._stream()), eng._h)
     return logits, raw, vmax

@@ -83,7 +83,7 @@ class SoftTreeMaxPolicy(ActorCriticCnnPolicyDepth0):
     def __init__(self, observation_space, action_space, lr_schedule, tree_depth, gamma, step_env, buffer_size,
                  learn_alpha, learn_beta, max_width, use_leaves_v, is_cumulative_mode, regularization, **kwargs):
         super().__init__(observation_space, action_space, lr_schedule, **kwargs)
-        self.cule_bfs = CuleBFS(step_env, tree_depth, gamma, self.compute_value, max_width)         # :19
+        self.cule_bfs = CuleBFS(step_env, tree_depth, gamma, self.compute_value_kernel, max_width)  # :19
         self.eng = self.cule_bfs.eng
         self.time_step = 0
         self.obs2leaves_dict, self.timestep2obs_dict, self.obs2timestep_dict = {}, {}, {}            # :21-23
@@ -119,6 +119,13 @@ class SoftTreeMaxPolicy(ActorCriticCnnPolicyDepth0):
             return self.action_net(latent), None
         return latent, self.value_net(latent)
 
+    @th.no_grad()
+    def compute_value_kernel(self, leaves_obs, root_obs=None):
+        """compute_value(leaves_obs) for the tree's width pruning (cule_bfs.py:176), on K4."""
+        self._sync_kernel_weights()
+        head, _ = self.eng.cnn_forward(leaves_obs.contiguous())
+        return head, None
+
     def compute_value_with_root(self, leaves_obs, root_obs=None):                                    # :199-208
         if root_obs is None:
             return self.action_net(self.extract_features(leaves_obs)), None
@@ -149,7 +156,8 @@ class SoftTreeMaxPolicy(ActorCriticCnnPolicyDepth0):
         logits, _, vmax = ops.softtreemax_logits_full(                                               # K5
             self.eng, head_leaf.reshape(1, -1, A), rewards.reshape(1, -1), val_coef, float(self.beta), float(self.alpha),
             self.regularization, self.is_cumulative_mode, depth0=head_root if self.learn_alpha else None,
-            values=val_leaf.reshape(1, -1) if self.use_leaves_v else None)
+            values=val_leaf.reshape(1, -1) if self.use_leaves_v else None,
+            group=first_action.reshape(1, -1) if first_action is not None else None)                 # :70-79
         value_root = vmax.reshape(()) if self.use_leaves_v else val_root.reshape(1, 1)               # :62-65
         dist = self._distribution(logits)
         actions = logits.argmax(dim=1) if deterministic else dist.sample()
@@ -167,14 +175,15 @@ class SoftTreeMaxPolicy(ActorCriticCnnPolicyDepth0):
         obs = obs.to(self.device)
         B, A = obs.shape[0], self.action_space.n
         keys = self.hash_obs(obs).tolist()                                                           # one D2H, not B
-        leaves, rewards = [], []
+        leaves, rewards, groups = [], [], []
         for k in keys:
             if k not in self.obs2leaves_dict:
                 # the reference prints and re-expands with the WHOLE batch as root (:129-132), a latent bug
                 raise KeyError("observation not in the leaf cache: evaluate_actions must follow forward()")
-            l, r, _ = self.obs2leaves_dict[k]
+            l, r, fa = self.obs2leaves_dict[k]
             leaves.append(l)
             rewards.append(r)
+            groups.append(fa)
         L = leaves[0].shape[0]
         val_coef = self.cule_bfs.gamma ** self.cule_bfs.max_depth
         feats = self.extract_features(th.cat([obs.to(th.uint8)] + leaves))                           # :122,139
@@ -182,8 +191,9 @@ class SoftTreeMaxPolicy(ActorCriticCnnPolicyDepth0):
         head = self.action_net(feats[B:]).reshape(B, L, A)
         rew = th.stack(rewards)
         depth0 = self.action_net(feats[:B]) if self.learn_alpha else None
+        group = th.stack([g.reshape(-1) for g in groups]) if groups[0] is not None else None          # :163-171
         logits = ops.softtreemax_logits(self.eng, head, rew, val_coef, self.beta, self.alpha, self.regularization,
-                                        self.is_cumulative_mode, depth0)                              # K5 fwd + bwd
+                                        self.is_cumulative_mode, depth0, group)                       # K5 fwd + bwd
         dist = self._distribution(logits)
         log_prob = dist.log_prob(actions.to(self.device).reshape(-1))
         if self.use_leaves_v:

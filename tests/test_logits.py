@@ -16,7 +16,7 @@ ATOL = 2e-5
 
 def case_inputs(c):
     A, d = c["A"], c["d"]
-    L = A ** d
+    L = c.get("n", A ** d)
     if c["kind"] == "survey":
         l = np.arange(L)[:, None]
         a = np.arange(A)[None, :]
@@ -26,8 +26,16 @@ def case_inputs(c):
     else:
         head = torch.tensor(c["head"]).reshape(L, A)
         rew = torch.tensor(c["rewards"])
-        d0 = torch.tensor(c["depth0"]).reshape(1, A)
+        d0 = torch.tensor(c["depth0"]).reshape(1, A) if "depth0" in c else None
     return head, rew, d0
+
+
+def case_group(c):
+    return torch.tensor(c["first_action"], dtype=torch.int32)[None] if c["kind"] == "width" else None
+
+
+def want_raw(c):
+    return np.array([v if v is not None else -np.inf for v in c["raw"]], np.float32)
 
 
 @pytest.mark.parametrize("i", range(len(CASES)))
@@ -35,9 +43,11 @@ def test_restatement_matches_reference_vectors(i):
     from oracle import policy_ref
     c = CASES[i]
     head, rew, d0 = case_inputs(c)
+    if c["kind"] == "width":
+        d0 = None
     logits, raw, _ = policy_ref.softtreemax_logits(head[None], rew[None], c["A"], c["gamma"] ** c["d"], c["beta"],
-                                                   c["alpha"], c["eps"], c["cumulative"], d0)
-    assert np.allclose(raw[0].numpy(), c["raw"], atol=ATOL)
+                                                   c["alpha"], c["eps"], c["cumulative"], d0, first_action=case_group(c))
+    assert np.allclose(raw[0].numpy(), want_raw(c), atol=ATOL)
     assert np.allclose(logits[0].numpy(), c["reg"], atol=ATOL)
 
 
@@ -64,11 +74,23 @@ def test_kernel_matches_reference_vectors(eng, i):
     c = CASES[i]
     head, rew, d0 = case_inputs(c)
     dev = eng.device
+    grp = case_group(c)
+    if c["kind"] == "width":
+        d0 = None
     logits, raw, _ = ops.softtreemax_logits_full(eng, head[None].to(dev), rew[None].to(dev), c["gamma"] ** c["d"], c["beta"],
                                                 c["alpha"], c["eps"], c["cumulative"],
-                                                d0.to(dev) if d0 is not None else None)
-    assert np.allclose(raw[0].cpu().numpy(), c["raw"], atol=ATOL)
+                                                d0.to(dev) if d0 is not None else None,
+                                                group=grp.to(dev) if grp is not None else None)
+    assert np.allclose(raw[0].cpu().numpy(), want_raw(c), atol=ATOL)
     assert np.allclose(logits[0].cpu().numpy(), c["reg"], atol=ATOL)
+    if c["kind"] == "width":
+        h = head[None].to(dev).requires_grad_()
+        beta = torch.tensor(c["beta"], device=dev, requires_grad=True)
+        y = ops.softtreemax_logits(eng, h, rew[None].to(dev), c["gamma"] ** c["d"], beta, 1.0, c["eps"], c["cumulative"],
+                                   None, grp.to(dev))
+        (y * torch.tensor(c["dy"], device=dev).reshape(1, -1)).sum().backward()
+        assert np.allclose(h.grad.flatten().cpu().numpy(), c["dhead"], rtol=1e-4, atol=1e-6)
+        assert np.isclose(float(beta.grad), c["dbeta"], rtol=1e-4, atol=1e-6)
     if c["kind"] == "random":
         h = head[None].to(dev).requires_grad_()
         dd = d0.to(dev).requires_grad_()

@@ -39,8 +39,64 @@ def test_cule_bfs_interface_and_oracle_parity():
     want = g.bfs(blob[None], obs[None], 2)
     assert np.array_equal(leaves.cpu().numpy(), want[0][0])
     assert np.array_equal(rewards.cpu().numpy(), want[1][0])
-    with pytest.raises(NotImplementedError):
-        CuleBFS(env, 2, max_width=4)
+
+
+def test_width_limited_tree_matches_oracle_replay():
+    """max_width != -1 (cule_bfs.py:81-96,145-150,175-196): the survivor draw is random, so the GPU run's
+    survivor indices are replayed through the oracle; leaves, rewards and first_action must then match
+    bit for bit, and the policy's logits must match the restatement with first_action."""
+    from oracle import orc, policy_ref
+    env, pol = make_policy(depth=3, max_width=2)              # 2*A = 8 nodes per level at most
+    obs = env.reset()
+    for a in [1, 3, 3, 0, 2]:
+        obs, *_ = env.step(a)
+    bfs = pol.cule_bfs
+    A = env.action_space.n
+    obs_t = torch.from_numpy(obs).float()[None]
+    torch.manual_seed(1)
+    with torch.no_grad():
+        pol.action_net.weight.mul_(30.0)
+    leaves, rewards, first_action = bfs.bfs(obs_t, 3)
+    assert leaves.shape == (8, 4, 84, 84) and first_action.shape == (8, 1) and len(bfs.last_survivors) == 2
+    # oracle replay
+    g = orc.Game("synth_breakout")
+    st = env.env.blobs[0].cpu().numpy()[None].copy()
+    rw = np.zeros(1, np.float32); dn = np.zeros(1, np.uint8); lv = np.array([g.lives(st[0])], np.int32)
+    stacks = obs[None].copy()
+    fa = np.arange(A)[:, None]
+    pruned = 0
+    for depth in range(3):
+        n = st.shape[0] * A
+        st = np.repeat(st, A, axis=0); rw = np.repeat(rw, A); dn = np.repeat(dn, A); lv = np.repeat(lv, A)
+        if depth != 0:
+            fa = np.repeat(fa, A, axis=0)
+        new = np.zeros((n, 4, 84, 84), np.uint8)
+        for i in range(n):
+            o, *_ = g.agent_step(st[i], i % A, weight=float(np.float32(0.99) ** depth) if False else 0.99 ** depth,
+                                 done=dn[i:i + 1], reward=rw[i:i + 1], lives=lv[i:i + 1])
+            new[i, :3] = stacks[i // A, 1:]
+            new[i, 3] = o
+        stacks = new
+        if depth != 2 and n > 2:
+            top = np.array(bfs.last_survivors[pruned]); pruned += 1
+            fa, stacks, st, rw, dn, lv = fa[top], stacks[top], st[top], rw[top], dn[top], lv[top]
+    assert np.array_equal(leaves.cpu().numpy(), stacks)
+    assert np.array_equal(rewards.cpu().numpy(), np.sign(rw))
+    assert np.array_equal(first_action.cpu().numpy(), fa)
+    # policy logits with first_action
+    actions, value, log_prob = pol.forward(obs_t, deterministic=True)
+    key = int(pol.hash_obs(obs_t.to(pol.device))[0].item())
+    leaves2, rewards2, fa2 = pol.obs2leaves_dict[key]
+    params = {k: v.cpu() for k, v in pol.kernel_params().items()}
+    _, head, _ = policy_ref.nature_cnn_forward(params, leaves2.cpu())
+    logits, _, _ = policy_ref.softtreemax_logits(head[None], rewards2.cpu()[None], A, 0.99 ** 3, float(pol.beta), 1.0, 0.001,
+                                                 False, first_action=fa2.cpu().reshape(1, -1))
+    got = torch.distributions.Categorical(logits=logits).log_prob(actions.cpu())
+    assert abs(float(got) - float(log_prob)) <= 5e-2
+    # and the update path accepts the grouped leaves
+    v, lp, ent = pol.evaluate_actions(obs_t, actions)
+    (lp.sum() + v.sum()).backward()
+    assert torch.isfinite(pol.beta.grad)
 
 
 @pytest.mark.parametrize("kw", [dict(), dict(is_cumulative_mode=True), dict(learn_alpha=True), dict(use_leaves_v=True),
