@@ -153,7 +153,9 @@ static inline void build_decode_table(uint32_t *t)
 // touches, ...), so that lanes running LDA and LDX, or CLC and SED, stay converged.
 //   [2:0] am   0 none 1 imm 2 zp-family 3 abs-family 4 (zp,x) 5 (zp),y 6 (abs) 7 rel
 //   [4:3] idx  0 none 1 X 2 Y          [6:5] kind (bit0 reads memory, bit1 writes memory)
-//   [10:7] base cycles                 [12:11] length      [17:13] group      [31:18] data
+//   [10:7] base cycles                 [12:11] length      [17:13] group
+//   [18] page-cross penalty applies (indexed absolute READ)    [19] the reads are stack pulls
+//   [21:20] number of bus reads before execute (0, 1 operand, or 1..3 pulls)           [31:22] data
 enum Grp : uint32_t {
     G_NOP, G_LOAD, G_STORE, G_XFER, G_PUSH, G_PULL, G_LOGIC, G_ADC, G_SBC, G_CMP, G_BIT, G_SHIFT,
     G_INCDEC_MEM, G_INCDEC_REG, G_FLAG, G_JMP, G_JSR, G_RTS, G_RTI, G_BRK, G_BRANCH, G_RMW_ALU,
@@ -233,7 +235,11 @@ static inline uint32_t encode_hot(uint32_t e, uint32_t op)
     default: grp = G_NOP; break;
     }
     if (mode == M_ACC) kind = K_N;
-    return AM[mode] | (IX[mode] << 3) | (kind << 5) | (cyc << 7) | (LEN[mode] << 11) | (grp << 13) | (data << 18);
+    const uint32_t npull = grp == G_PULL ? 1u : (grp == G_RTS ? 2u : (grp == G_RTI ? 3u : 0u));
+    const uint32_t nrd = npull ? npull : (((kind & 1) && mode != M_IMM) ? 1u : 0u);
+    const uint32_t pen = (kind == K_R && (mode == M_ABX || mode == M_ABY)) ? 1u : 0u;
+    return AM[mode] | (IX[mode] << 3) | (kind << 5) | (cyc << 7) | (LEN[mode] << 11) | (grp << 13) | (pen << 18) |
+           ((npull ? 1u : 0u) << 19) | (nrd << 20) | (data << 22);
 }
 // the table the kernel uses
 static inline void build_hot_table(uint32_t *t)
@@ -891,7 +897,7 @@ struct Emu {
         } else {
             w = m.opinfo(peek(pc)); b1 = peek(pc + 1); b2 = peek(pc + 2);
         }
-        const uint32_t am = w & 7, kind = (w >> 5) & 3, grp = (w >> 13) & 31, data = w >> 18;
+        const uint32_t am = w & 7, kind = (w >> 5) & 3, grp = (w >> 13) & 31, data = w >> 22;
         uint32_t cyc = (w >> 7) & 15;
         uint32_t npc = (pc + ((w >> 11) & 3)) & 0xFFFF;
 
@@ -903,7 +909,7 @@ struct Emu {
                 uint32_t base = b1 | (am == 3 ? b2 << 8 : 0u);
                 uint32_t full = base + idx;
                 ea = full & (am == 3 ? 0xFFFFu : 0xFFu);
-                cyc += ((am == 3 && kind == K_R) ? 1u : 0u) & ((full ^ base) >> 8);
+                cyc += (w >> 18) & ((full ^ base) >> 8) & 1u;
             } else if (am == 4) { ea = peek16zp(b1 + x); }
             else if (am == 5) {
                 uint32_t base = peek16zp(b1);
@@ -922,35 +928,41 @@ struct Emu {
                 cyc += 1 + (((t ^ npc) & 0xFF00) ? 1u : 0u);
                 npc = t;
             }
+            pc = npc;                                          // nothing else to do for a branch: retire
+            hcyc += (int32_t)cyc;
+            timer -= (int32_t)cyc;
+            wsync = false;
+            return hcyc >= STM_CYC_PER_LINE;
         }
         wsync = false;
 
         // read phase: one memory operand, or 1..3 stack pulls
         uint32_t r0 = b1, r1 = 0, r2 = 0;
         {
-            uint32_t npull = grp == G_PULL ? 1u : (grp == G_RTS ? 2u : (grp == G_RTI ? 3u : 0u));
-            uint32_t nrd = npull ? npull : (((kind & 1) && am != 1) ? 1u : 0u);
-            for (uint32_t i = 0; i < nrd; i++) {
+            uint32_t nrd = (w >> 20) & 3u;
+            const bool pulls = (w >> 19) & 1u;
+            while (nrd--) {
                 uint32_t addr = ea;
-                if (npull) { sp = (sp + 1) & 0xFF; addr = 0x100 | sp; }
+                if (pulls) { sp = (sp + 1) & 0xFF; addr = 0x100 | sp; }
                 r2 = r1; r1 = r0;
                 r0 = bus_read(addr, cyc, w);
             }
         }
-        uint32_t v = (am == 0 && grp == G_SHIFT) ? a : r0;
+        const uint32_t v = r0;
 
         // execute: registers only; memory results are queued in w0..w2
         uint32_t nwr = 0, w0 = 0, w1 = 0, w2 = 0;
         bool wpush = false;
-        switch (grp) {
-        case G_LOAD:
+        // the two commonest groups are tested first; the rest go through the jump table
+        if (grp == G_LOAD) {
             if (data & 1) a = v;
             if (data & 2) x = v;
             if (data & 4) y = v;
-            zn = v; break;
-        case G_STORE:
+            zn = v;
+        } else if (grp == G_STORE) {
             w0 = ((data & 1) ? a : 0xFFu) & ((data & 2) ? x : 0xFFu) & ((data & 4) ? y : 0xFFu);
-            nwr = 1; break;
+            nwr = 1;
+        } else switch (grp) {
         case G_XFER: {
             uint32_t s = data & 3, d = (data >> 2) & 3;
             uint32_t val = s == 0 ? a : (s == 1 ? x : (s == 2 ? y : sp));
@@ -965,7 +977,7 @@ struct Emu {
         case G_CMP: cmp(data == 0 ? a : (data == 1 ? x : y), v); break;
         case G_BIT: p = (p & ~(uint32_t)FV) | (v & FV); zn = (v & a) | ((v & 0x80) << 1); break;
         case G_SHIFT: {
-            uint32_t r = shift(v, data);
+            uint32_t r = shift(am == 0 ? a : v, data);
             if (am == 0) a = r; else { w0 = r; nwr = 1; }
             break; }
         case G_INCDEC_MEM: w0 = (v + data) & 0xFF; zn = w0; nwr = 1; break;
