@@ -881,16 +881,17 @@ struct Emu {
     }
 
     // ---------------- one instruction ----------------
-    // Returns true when the instruction ran past the end of the scanline (or strobed WSYNC): the
-    // caller must then call finish_line().  Keeping the line wrap out of here lets the step kernel
-    // run all lanes of a warp to the end of their scanline and wrap — i.e. render — them together.
+    // Returns true when the caller must leave its instruction loop: the instruction ran past the end of
+    // the scanline or strobed WSYNC (call finish_line()), or it ended the frame.  Keeping the line wrap
+    // out of here lets the step kernel run all lanes of a warp to the end of their scanline and wrap —
+    // i.e. render — them together.
     STM_DEV bool exec_core()
     {
         // fetch + decode.  Cartridge code is predecoded (one 64-bit record per image byte: the hot
         // decode word of the opcode there and its two operand bytes), so the common case is one load.
         uint32_t w, b1, b2;
         uint32_t a13 = pc & 0x1FFF;
-        if ((a13 & 0x1000) && (a13 & 0xFFF) <= 0xFFD) {
+        if (a13 - 0x1000u <= 0xFFDu) {                      // in cartridge space with both operand bytes inside it
             uint32_t ops;
             m.fetch((bank << 12) | (a13 & gp.rom_mask), w, ops);
             b1 = ops & 0xFF; b2 = ops >> 8;
@@ -932,7 +933,7 @@ struct Emu {
             hcyc += (int32_t)cyc;
             timer -= (int32_t)cyc;
             wsync = false;
-            return hcyc >= STM_CYC_PER_LINE;
+            return hcyc >= STM_CYC_PER_LINE;                   // (a branch cannot end the frame)
         }
         wsync = false;
 
@@ -1024,7 +1025,7 @@ struct Emu {
         pc = npc;
         hcyc += (int32_t)cyc;
         timer -= (int32_t)cyc;
-        return hcyc >= STM_CYC_PER_LINE || wsync;
+        return hcyc >= STM_CYC_PER_LINE || wsync || (flags & STM_F_FRAME_DONE);
     }
     STM_DEV void finish_line()
     {
@@ -1032,7 +1033,7 @@ struct Emu {
         if (wsync && hcyc != 0) { timer -= STM_CYC_PER_LINE - hcyc; end_line(); hcyc = 0; }
         wsync = false;
     }
-    STM_DEV void exec_one() { if (exec_core()) finish_line(); }
+    STM_DEV void exec_one() { exec_core(); if (hcyc >= STM_CYC_PER_LINE || wsync) finish_line(); }
 
     // ---------------- one emulated frame ----------------
     // Rows the frame never reached are zero-filled, as the oracle does.
@@ -1062,8 +1063,9 @@ struct Emu {
                 if (key == kmin) ended = exec_core();
             }
 #else
-            while (!ended && !(flags & STM_F_FRAME_DONE)) ended = exec_core();
+            if (!over) while (!exec_core()) { }
 #endif
+            ended = hcyc >= STM_CYC_PER_LINE || wsync;
             if (!over) {
                 if (ended) finish_line();
                 over = (flags & STM_F_FRAME_DONE) != 0;

@@ -1,0 +1,71 @@
+"""Per-source-line instruction cost of the K2 step kernel from an `ncu --set full --import-source on`
+capture: joins ncu's per-SASS "Instructions Executed" with nvdisasm's line table of the shipped cubin.
+
+    python tools/k2_line_profile.py gpurun_out/prof.ncu-rep [top_n]
+Prints SASS instructions per emulated instruction (loop iteration), attributed to source lines.
+"""
+import collections
+import csv
+import io
+import os
+import re
+import subprocess
+import sys
+import tempfile
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def line_table():
+    so = os.path.join(ROOT, "softtreemax_b200", "libstm_b200.so")
+    with tempfile.TemporaryDirectory() as d:
+        subprocess.run(["cuobjdump", "-xelf", "all", so], cwd=d, capture_output=True)
+        cub = [f for f in os.listdir(d) if f.startswith("stm_kernels")][0]
+        txt = subprocess.run(["nvdisasm", "-g", "-c", os.path.join(d, cub)], capture_output=True, text=True).stdout
+    secs, cur, cf, cl = {}, None, None, None
+    for l in txt.splitlines():
+        m = re.match(r"\s*\.section\s+\.text\.(\S+?),", l)
+        if m:
+            cur = m.group(1)
+            secs[cur] = []
+            continue
+        m = re.match(r'\s*//## File "([^"]+)", line (\d+)', l)
+        if m:
+            cf, cl = os.path.basename(m.group(1)), int(m.group(2))
+            continue
+        m = re.match(r"\s*/\*([0-9a-f]{4,5})\*/\s+(.*?);", l)
+        if m and cur:
+            secs[cur].append((cf, cl))
+    return [v for k, v in secs.items() if "stm_step_kernel" in k][0]
+
+
+def main():
+    rep = sys.argv[1]
+    top = int(sys.argv[2]) if len(sys.argv) > 2 else 50
+    raw = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv", "--print-source", "sass"],
+                         capture_output=True, text=True).stdout
+    rows = list(csv.reader(io.StringIO(raw)))
+    k = [i for i, r in enumerate(rows) if r and r[0] == "Kernel Name"]
+    hdr = rows[k[0] + 1]
+    ie = hdr.index("Instructions Executed")
+    first = rows[k[0] + 2:(k[1] if len(k) > 1 else len(rows))]
+    table = line_table()
+    if len(table) != len(first):
+        sys.exit(f"SASS of the capture ({len(first)}) and of the library ({len(table)}) differ: rebuild / recapture")
+    counts = collections.Counter(int(r[ie]) for r in first)
+    n_iter = max(c for c, n in counts.items() if n >= 10 and c > 0)          # the loop-head count
+    agg = collections.Counter()
+    for r, (f, ln) in zip(first, table):
+        agg[(f, ln)] += int(r[ie])
+    tot = sum(agg.values())
+    src = {}
+    for f in ("emu_core.cuh", "stm_kernels.cu"):
+        src[f] = open(os.path.join(ROOT, "softtreemax_b200", "csrc", f)).read().splitlines()
+    print(f"SASS instructions per emulated instruction: {tot / n_iter:.1f}")
+    for (f, ln), c in agg.most_common(top):
+        text = src[f][ln - 1].strip()[:100] if f in src and ln - 1 < len(src[f]) else ""
+        print(f"{c / n_iter:7.2f}  {f}:{ln:<5d} {text}")
+
+
+if __name__ == "__main__":
+    main()
