@@ -544,6 +544,10 @@ STM_NOINLINE uint32_t tia_catchup(M m, uint32_t line, uint32_t rx, uint32_t xe, 
     return t.rx;
 }
 
+// native row `src` of the frame being drawn -> row `dst` (whole-line reuse, see Emu::end_line)
+template <class M>
+STM_NOINLINE void tia_copy_row(M m, uint32_t dst, uint32_t src) { m.copy_row(dst, src); }
+
 // ---- the per-env machine ---------------------------------------------------------------------------
 // M must provide:
 //   uint32_t ld8(off) / void st8(off, v) / ld16 / st16 / ld32 / st32     blob access (off = byte offset)
@@ -554,6 +558,7 @@ STM_NOINLINE uint32_t tia_catchup(M m, uint32_t line, uint32_t rx, uint32_t xe, 
 //   void px16(row, q, w0..w3) store 16 pixels of native row `row`, quad q (0..9): four packed words
 //   void px4(row, g, word)    store 4 pixels (colour indices), group g (0..39)
 //   void px1(row, x, v)       store 1 pixel
+//   void copy_row(dst, src)   copy the 160 pixels of native row src to row dst (same frame)
 //
 // One instruction = fetch -> decode -> address -> read phase -> execute (register-only switch over
 // ~25 groups) -> write phase -> retire.  Every memory access goes through ONE read site and ONE
@@ -593,7 +598,7 @@ struct Emu {
         m.st16(O_PC, pc); m.st8(O_A, a); m.st8(O_X, x); m.st8(O_Y, y); m.st8(O_SP, sp);
         m.st8(O_P, get_p());
         m.st8(O_BANK, bank); m.st16(O_LINE, line); m.st8(O_HCYC, (uint32_t)hcyc); m.st8(O_RX, rx);
-        m.st8(O_FLAGS, flags); m.st32(O_TIMER, (uint32_t)timer);
+        m.st8(O_FLAGS, flags & 0xFFu); m.st32(O_TIMER, (uint32_t)timer);
         m.st8(O_TFLAG, timer < 0 ? 0x80u : 0u);      // the underflow latch always equals (timer < 0) between instructions
     }
 
@@ -633,9 +638,33 @@ struct Emu {
         if (xe > rx) rx = tia_catchup<M>(m, line, rx, xe, flags, render);
     }
 
+    // Whole-line reuse.  Most scanlines of a frame are drawn under exactly the TIA state of the line
+    // above (a wall, a brick band, empty field).  `flags` carries two transient bits above its stored
+    // byte: F_CXCLEAN = a whole line has been processed under the current state (its collisions are
+    // latched; latching them again changes nothing), F_PIXCLEAN = additionally native row
+    // (flags >> 16) & 0xFF of this frame holds that line's pixels.  Every write that changes a register
+    // the renderer reads clears both (tia_dirty); a line wrapped while they are set is a 160-byte row
+    // copy (or nothing at all on rows/frames that are not drawn) instead of a render.
+    static constexpr uint32_t F_PIXCLEAN = 0x100u, F_CXCLEAN = 0x200u;
+    STM_DEV void tia_dirty() { flags &= ~(F_PIXCLEAN | F_CXCLEAN); }
     STM_DEV void end_line()
     {
-        catchup(STM_VIS_W);
+        if (rx == 0) {
+            int row = (int)line - STM_YSTART;
+            bool draw = render && row_sampled(row);
+            if (flags & (draw ? F_PIXCLEAN : F_CXCLEAN)) {
+                if (draw) tia_copy_row<M>(m, (uint32_t)row, (flags >> 16) & 0xFFu);
+            } else {
+                tia_catchup<M>(m, line, 0, STM_VIS_W, flags, render);
+                if (!(flags & STM_F_HMOVE_BLANK)) {
+                    flags |= F_CXCLEAN;
+                    if (draw) flags = (flags & 0xFF00FFFFu) | F_PIXCLEAN | ((uint32_t)row << 16);
+                }
+            }
+        } else {
+            catchup(STM_VIS_W);
+            tia_dirty();
+        }
         line++;
         rx = 0;
         flags &= ~(uint32_t)STM_F_HMOVE_BLANK;
@@ -692,35 +721,60 @@ struct Emu {
         if (reg > 0x2C) return;
         if (reg == 0x02) { wsync = true; return; }
         if (reg == 0x03 || (reg >= 0x15 && reg <= 0x1A)) return;
+        v &= 0xFFu;
+        // Plain registers: a write of the value already there changes nothing (no catch-up needed, the
+        // line stays reusable); HMxx / HMCLR are not read by the renderer at all.
+        if (reg >= 0x04 && reg <= 0x0F) {                                   // NUSIZ0..PF2 are laid out in register order
+            uint32_t o = O_NUSIZ0 + (reg - 4);
+            if (m.ld8(o) == v) return;
+            catchup(x_of(acc)); m.st8(o, v); tia_dirty(); return;
+        }
+        if (reg >= 0x1D && reg <= 0x1F) {                                   // ENAM0, ENAM1, ENABL
+            uint32_t o = O_ENAM0 + (reg - 0x1D);
+            if (m.ld8(o) == v) return;
+            catchup(x_of(acc)); m.st8(o, v); tia_dirty(); return;
+        }
+        if (reg >= 0x20 && reg <= 0x24) { m.st8(O_HMP0 + (reg - 0x20), v); return; }   // HMP0..HMBL
+        if (reg >= 0x25 && reg <= 0x27) {                                   // VDELP0, VDELP1, VDELBL follow them
+            uint32_t o = O_HMP0 + (reg - 0x20);
+            if (m.ld8(o) == v) return;
+            catchup(x_of(acc)); m.st8(o, v); tia_dirty(); return;
+        }
+        if (reg == 0x2B) { m.st8(O_HMP0, 0); m.st8(O_HMP1, 0); m.st8(O_HMM0, 0); m.st8(O_HMM1, 0); m.st8(O_HMBL, 0); return; }
+        if (reg == 0x1B) {
+            uint32_t g1 = m.ld8(O_GRP1);
+            if (m.ld8(O_GRP0) == v && m.ld8(O_GRP1_OLD) == g1) return;
+            catchup(x_of(acc)); m.st8(O_GRP0, v); m.st8(O_GRP1_OLD, g1); tia_dirty(); return;
+        }
+        if (reg == 0x1C) {
+            uint32_t g0 = m.ld8(O_GRP0), bl = m.ld8(O_ENABL);
+            if (m.ld8(O_GRP1) == v && m.ld8(O_GRP0_OLD) == g0 && m.ld8(O_ENABL_OLD) == bl) return;
+            catchup(x_of(acc)); m.st8(O_GRP1, v); m.st8(O_GRP0_OLD, g0); m.st8(O_ENABL_OLD, bl); tia_dirty(); return;
+        }
         catchup(x_of(acc));
-        if (reg >= 0x04 && reg <= 0x0F) { m.st8(O_NUSIZ0 + (reg - 4), v); return; }    // NUSIZ0..PF2 are laid out in register order
-        if (reg >= 0x1D && reg <= 0x1F) { m.st8(O_ENAM0 + (reg - 0x1D), v); return; }  // ENAM0, ENAM1, ENABL
-        if (reg >= 0x20 && reg <= 0x27) { m.st8(O_HMP0 + (reg - 0x20), v); return; }   // HMP0..VDELBL likewise
-        if (reg >= 0x10 && reg <= 0x14) { set_pos(reg - 0x10, reg < 0x12, acc); return; }   // RESP0 RESP1 RESM0 RESM1 RESBL = pos[0..4]
+        if (reg >= 0x10 && reg <= 0x14) { set_pos(reg - 0x10, reg < 0x12, acc); tia_dirty(); return; }   // RESP0 RESP1 RESM0 RESM1 RESBL = pos[0..4]
         switch (reg) {
         case 0x00:
             if ((v & 2) && !(m.ld8(O_VSYNC) & 2)) { flags |= STM_F_FRAME_DONE; end_line_no = line; line = 0; }
             m.st8(O_VSYNC, v); break;
         case 0x01:
             if (v & 0x80) m.st8(O_CHARGE, 0);
+            if (m.ld8(O_VBLANK) != v) tia_dirty();
             m.st8(O_VBLANK, v); update_latch(); break;
-        case 0x1B: m.st8(O_GRP0, v); m.st8(O_GRP1_OLD, m.ld8(O_GRP1)); break;
-        case 0x1C: m.st8(O_GRP1, v); m.st8(O_GRP0_OLD, m.ld8(O_GRP0)); m.st8(O_ENABL_OLD, m.ld8(O_ENABL)); break;
         case 0x28:
             if ((m.ld8(O_RESMP0) & 2) && !(v & 2)) m.st8(O_POS + STM_M0, (m.ld8(O_POS + STM_P0) + 4u) % 160u);
-            m.st8(O_RESMP0, v); break;
+            m.st8(O_RESMP0, v); tia_dirty(); break;
         case 0x29:
             if ((m.ld8(O_RESMP1) & 2) && !(v & 2)) m.st8(O_POS + STM_M1, (m.ld8(O_POS + STM_P1) + 4u) % 160u);
-            m.st8(O_RESMP1, v); break;
+            m.st8(O_RESMP1, v); tia_dirty(); break;
         case 0x2A:
             hmove_obj(STM_P0, m.ld8(O_HMP0)); hmove_obj(STM_P1, m.ld8(O_HMP1));
             hmove_obj(STM_M0, m.ld8(O_HMM0)); hmove_obj(STM_M1, m.ld8(O_HMM1));
             hmove_obj(STM_BL, m.ld8(O_HMBL));
             if (acc * 3 < STM_HBLANK_CLK) flags |= STM_F_HMOVE_BLANK;
+            tia_dirty();
             break;
-        case 0x2B:
-            m.st8(O_HMP0, 0); m.st8(O_HMP1, 0); m.st8(O_HMM0, 0); m.st8(O_HMM1, 0); m.st8(O_HMBL, 0); break;
-        case 0x2C: m.st16(O_CX, 0); break;
+        case 0x2C: m.st16(O_CX, 0); tia_dirty(); break;
         default: break;
         }
     }
@@ -1047,6 +1101,7 @@ struct Emu {
         render = want_pixels;
         set_action(ale_action);
         flags &= ~(uint32_t)STM_F_FRAME_DONE;
+        tia_dirty();                                           // a new native frame: no row to reuse yet
         bool over = false;
         do {
             // Run every lane to the end of its scanline.  (STM_MINPC: lowest-program-counter-first —

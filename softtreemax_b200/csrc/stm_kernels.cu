@@ -205,6 +205,19 @@ struct DevMem {
     { return scr + (size_t)((fsel * STM_VIS_H + row) * 10 + q) * (kTileEnvs * 4); }
     __device__ __forceinline__ void px16(uint32_t row, uint32_t q, uint32_t a, uint32_t b, uint32_t c, uint32_t d)
     { *reinterpret_cast<uint4 *>(quad(row, q)) = make_uint4(a, b, c, d); }
+    __device__ __forceinline__ void copy_row(uint32_t dst, uint32_t src)
+    {
+        const uint4 *s = reinterpret_cast<const uint4 *>(quad(src, 0));
+        uint4 *d = reinterpret_cast<uint4 *>(quad(dst, 0));
+        #pragma unroll
+        for (int h = 0; h < 2; h++) {                    // five loads in flight, then five stores
+            uint4 v[5];
+            #pragma unroll
+            for (int q = 0; q < 5; q++) v[q] = s[(size_t)(5 * h + q) * kTileEnvs];
+            #pragma unroll
+            for (int q = 0; q < 5; q++) d[(size_t)(5 * h + q) * kTileEnvs] = v[q];
+        }
+    }
     __device__ __forceinline__ void px4(uint32_t row, uint32_t g, uint32_t w) { quad(row, g >> 2)[g & 3] = w; }
     __device__ __forceinline__ void px1(uint32_t row, uint32_t x, uint32_t v)
     { reinterpret_cast<uint8_t *>(quad(row, x >> 4))[x & 15] = (uint8_t)v; }

@@ -48,23 +48,46 @@ def main():
     k = [i for i, r in enumerate(rows) if r and r[0] == "Kernel Name"]
     hdr = rows[k[0] + 1]
     ie = hdr.index("Instructions Executed")
+    isamp = [i for i, h in enumerate(hdr) if h.startswith("Warp Stall Sampling (All")]
+    isamp = isamp[0] if isamp else None
     first = rows[k[0] + 2:(k[1] if len(k) > 1 else len(rows))]
     table = line_table()
     if len(table) != len(first):
         sys.exit(f"SASS of the capture ({len(first)}) and of the library ({len(table)}) differ: rebuild / recapture")
     counts = collections.Counter(int(r[ie]) for r in first)
     n_iter = max(c for c, n in counts.items() if n >= 10 and c > 0)          # the loop-head count
-    agg = collections.Counter()
+    agg, samp = collections.Counter(), collections.Counter()
     for r, (f, ln) in zip(first, table):
         agg[(f, ln)] += int(r[ie])
+        if isamp is not None:
+            samp[(f, ln)] += int(r[isamp] or 0)
     tot = sum(agg.values())
+    stot = max(1, sum(samp.values()))
     src = {}
     for f in ("emu_core.cuh", "stm_kernels.cu"):
         src[f] = open(os.path.join(ROOT, "softtreemax_b200", "csrc", f)).read().splitlines()
     print(f"SASS instructions per emulated instruction: {tot / n_iter:.1f}")
     for (f, ln), c in agg.most_common(top):
         text = src[f][ln - 1].strip()[:100] if f in src and ln - 1 < len(src[f]) else ""
-        print(f"{c / n_iter:7.2f}  {f}:{ln:<5d} {text}")
+        print(f"{c / n_iter:7.2f} {100.0 * samp[(f, ln)] / stot:5.1f}%  {f}:{ln:<5d} {text}")
+    # coarse split by source region: the TIA renderer, the bus, the 6507 core, the kernel wrapper
+    emu = src["emu_core.cuh"]
+    marks = [(i + 1, l.strip()) for i, l in enumerate(emu) if re.match(r"\s*(STM_DEV|STM_FN|STM_NOINLINE|template|struct)\b", l)]
+    def region(f, ln):
+        if f != "emu_core.cuh":
+            return f
+        name = "?"
+        for m, t in marks:
+            if m <= ln:
+                name = t[:70]
+        return name
+    reg, regs = collections.Counter(), collections.Counter()
+    for k2, c in agg.items():
+        reg[region(*k2)] += c
+        regs[region(*k2)] += samp[k2]
+    print("-- by function (SASS/emulated instr, % of stall samples)")
+    for name, c in reg.most_common(25):
+        print(f"{c / n_iter:7.2f} {100.0 * regs[name] / stot:5.1f}%  {name}")
 
 
 if __name__ == "__main__":
