@@ -18,6 +18,8 @@
 // Reference call sites this replaces: policies/cule_bfs.py:154-158 (torchcule step + get_data).
 #pragma once
 #include <stdint.h>
+// hides a value's origin from the optimiser (no code is emitted)
+#define STM_OPAQUE(v) asm volatile("" : "+r"(v))
 #include "../../include/stm_state.h"
 
 #ifdef __CUDACC__
@@ -577,7 +579,10 @@ struct Emu {
     uint32_t bank;
     // warm state
     uint32_t line, rx, flags, end_line_no;
-    bool     render, wsync;
+    bool     render;
+    // instruction-loop break request, added to hcyc in the loop test: WSYNC strobed / frame over
+    int32_t  brk;
+    static constexpr int32_t BRK_WSYNC = 0x100, BRK_DONE = 0x200;
 
     STM_DEV Emu(M &mm, const GameParams &g) : m(mm), gp(g) {}
 
@@ -590,7 +595,7 @@ struct Emu {
         pc = m.ld16(O_PC); a = m.ld8(O_A); x = m.ld8(O_X); y = m.ld8(O_Y); sp = m.ld8(O_SP); set_p(m.ld8(O_P));
         bank = m.ld8(O_BANK); line = m.ld16(O_LINE); hcyc = (int32_t)m.ld8(O_HCYC); rx = m.ld8(O_RX);
         flags = m.ld8(O_FLAGS); timer = (int32_t)m.ld32(O_TIMER);
-        render = false; end_line_no = 0; wsync = false;
+        render = false; end_line_no = 0; brk = 0;
     }
     STM_DEV void store()
     {
@@ -669,7 +674,7 @@ struct Emu {
         rx = 0;
         flags &= ~(uint32_t)STM_F_HMOVE_BLANK;
         if (!(m.ld8(O_VBLANK) & 0x80)) { uint32_t c = m.ld8(O_CHARGE); if (c < 255) m.st8(O_CHARGE, c + 1); }
-        if (line >= STM_MAX_LINES) { flags |= STM_F_FRAME_DONE; end_line_no = STM_MAX_LINES; line = 0; }
+        if (line >= STM_MAX_LINES) { flags |= STM_F_FRAME_DONE; brk |= BRK_DONE; end_line_no = STM_MAX_LINES; line = 0; }
         if (timer < -(1 << 30)) timer += (1 << 30);
     }
     // cycle (within the line) at which the current instruction touches the bus; runs the line wrap
@@ -719,7 +724,7 @@ struct Emu {
     {
         reg &= 0x3F;
         if (reg > 0x2C) return;
-        if (reg == 0x02) { wsync = true; return; }
+        if (reg == 0x02) { brk |= BRK_WSYNC; return; }
         if (reg == 0x03 || (reg >= 0x15 && reg <= 0x1A)) return;
         v &= 0xFFu;
         // Plain registers: a write of the value already there changes nothing (no catch-up needed, the
@@ -755,7 +760,7 @@ struct Emu {
         if (reg >= 0x10 && reg <= 0x14) { set_pos(reg - 0x10, reg < 0x12, acc); tia_dirty(); return; }   // RESP0 RESP1 RESM0 RESM1 RESBL = pos[0..4]
         switch (reg) {
         case 0x00:
-            if ((v & 2) && !(m.ld8(O_VSYNC) & 2)) { flags |= STM_F_FRAME_DONE; end_line_no = line; line = 0; }
+            if ((v & 2) && !(m.ld8(O_VSYNC) & 2)) { flags |= STM_F_FRAME_DONE; brk |= BRK_DONE; end_line_no = line; line = 0; }
             m.st8(O_VSYNC, v); break;
         case 0x01:
             if (v & 0x80) m.st8(O_CHARGE, 0);
@@ -954,7 +959,7 @@ struct Emu {
         }
         const uint32_t am = w & 7, kind = (w >> 5) & 3, grp = (w >> 13) & 31, data = w >> 22;
         uint32_t cyc = (w >> 7) & 15;
-        uint32_t npc = (pc + ((w >> 11) & 3)) & 0xFFFF;
+        uint32_t npc = pc + ((w >> 11) & 3);                 // pc may run past 0xFFFF: every use masks it
 
         // effective address
         uint32_t ea;
@@ -986,21 +991,20 @@ struct Emu {
             pc = npc;                                          // nothing else to do for a branch: retire
             hcyc += (int32_t)cyc;
             timer -= (int32_t)cyc;
-            wsync = false;
             return hcyc >= STM_CYC_PER_LINE;                   // (a branch cannot end the frame)
         }
-        wsync = false;
 
         // read phase: one memory operand, or 1..3 stack pulls
         uint32_t r0 = b1, r1 = 0, r2 = 0;
-        {
+        if (w & (3u << 20)) {
             uint32_t nrd = (w >> 20) & 3u;
-            const bool pulls = (w >> 19) & 1u;
-            while (nrd--) {
-                uint32_t addr = ea;
-                if (pulls) { sp = (sp + 1) & 0xFF; addr = 0x100 | sp; }
-                r2 = r1; r1 = r0;
+            uint32_t addr = ea;
+            if (w & (1u << 19)) { sp = (sp + 1) & 0xFF; addr = 0x100 | sp; }
+            for (;;) {                                         // runs once except for RTS / RTI
                 r0 = bus_read(addr, cyc, w);
+                if (--nrd == 0) break;
+                r2 = r1; r1 = r0;
+                sp = (sp + 1) & 0xFF; addr = 0x100 | sp;
             }
         }
         const uint32_t v = r0;
@@ -1008,39 +1012,44 @@ struct Emu {
         // execute: registers only; memory results are queued in w0..w2
         uint32_t nwr = 0, w0 = 0, w1 = 0, w2 = 0;
         bool wpush = false;
-        // the two commonest groups are tested first; the rest go through the jump table
-        if (grp == G_LOAD) {
+        // The commonest groups are tested one by one (two instructions each, on a copy of the group
+        // number the compiler cannot see through — otherwise it folds the chain back into the jump
+        // table, whose indexed constant load + indirect branch cost more than the whole chain); the
+        // rest go through the jump table.
+        uint32_t gq = grp;
+        STM_OPAQUE(gq);
+        if (gq == G_STORE) {
+            w0 = ((data & 1) ? a : 0xFFu) & ((data & 2) ? x : 0xFFu) & ((data & 4) ? y : 0xFFu);
+            nwr = 1;
+        } else if (gq == G_LOAD) {
             if (data & 1) a = v;
             if (data & 2) x = v;
             if (data & 4) y = v;
             zn = v;
-        } else if (grp == G_STORE) {
-            w0 = ((data & 1) ? a : 0xFFu) & ((data & 2) ? x : 0xFFu) & ((data & 4) ? y : 0xFFu);
-            nwr = 1;
-        } else switch (grp) {
-        case G_XFER: {
+        } else if (gq == G_CMP) {
+            cmp(data == 0 ? a : (data == 1 ? x : y), v);
+        } else if (gq == G_INCDEC_REG) {
+            uint32_t d = data >> 2;
+            if (data & 1) { x = (x + d) & 0xFF; zn = x; } else { y = (y + d) & 0xFF; zn = y; }
+        } else if (gq == G_XFER) {
             uint32_t s = data & 3, d = (data >> 2) & 3;
             uint32_t val = s == 0 ? a : (s == 1 ? x : (s == 2 ? y : sp));
             if (d == 0) a = val; else if (d == 1) x = val; else if (d == 2) y = val; else sp = val;
             if (data & 16) zn = val;
-            break; }
+        } else if (gq == G_FLAG) {
+            p = (data & 256) ? (p | (data & 0xFF)) : (p & ~(data & 0xFF));
+        } else switch (grp) {
         case G_PUSH: w0 = data ? (get_p() | FB) : a; nwr = 1; wpush = true; break;
         case G_PULL: if (data) set_p(r0); else { a = r0; zn = r0; } break;
         case G_LOGIC: a = data == 0 ? (a & v) : (data == 1 ? (a | v) : (a ^ v)); zn = a; break;
         case G_ADC: adc(v); break;
         case G_SBC: sbc(v); break;
-        case G_CMP: cmp(data == 0 ? a : (data == 1 ? x : y), v); break;
         case G_BIT: p = (p & ~(uint32_t)FV) | (v & FV); zn = (v & a) | ((v & 0x80) << 1); break;
         case G_SHIFT: {
             uint32_t r = shift(am == 0 ? a : v, data);
             if (am == 0) a = r; else { w0 = r; nwr = 1; }
             break; }
         case G_INCDEC_MEM: w0 = (v + data) & 0xFF; zn = w0; nwr = 1; break;
-        case G_INCDEC_REG: {
-            uint32_t d = data >> 2;
-            if (data & 1) { x = (x + d) & 0xFF; zn = x; } else { y = (y + d) & 0xFF; zn = y; }
-            break; }
-        case G_FLAG: p = (data & 256) ? (p | (data & 0xFF)) : (p & ~(data & 0xFF)); break;
         case G_JMP: npc = ea; break;
         case G_JSR: { uint32_t ret = (pc + 2) & 0xFFFF; w0 = ret >> 8; w1 = ret & 0xFF; nwr = 2; wpush = true; npc = ea; break; }
         case G_RTS: npc = (((r0 << 8) | r1) + 1) & 0xFFFF; break;          // r1 = low byte (pulled first), r0 = high
@@ -1064,30 +1073,34 @@ struct Emu {
         case G_ANC: a &= v; zn = a; p = (p & ~(uint32_t)FC) | (a >> 7); break;
         case G_ALR: a = shift(a & v, 1); break;
         case G_SBX: { uint32_t t = (a & x) - v; p = (p & ~(uint32_t)FC) | (((t >> 8) & 1u) ^ 1u); x = t & 0xFF; zn = x; break; }
-        default: break;     // G_NOP, G_BRANCH (resolved above)
+        default: break;     // G_NOP; the groups resolved above
         }
 
         // write phase
-        for (uint32_t i = 0; i < nwr; i++) {
+        if (nwr) {
             uint32_t addr = ea;
             if (wpush) { addr = 0x100 | sp; sp = (sp - 1) & 0xFF; }
-            bus_write(addr, w0, cyc);
-            w0 = w1; w1 = w2;
+            for (;;) {                                         // runs once except for JSR / BRK
+                bus_write(addr, w0, cyc);
+                if (--nwr == 0) break;
+                w0 = w1; w1 = w2;
+                addr = 0x100 | sp; sp = (sp - 1) & 0xFF;
+            }
         }
 
         // retire
         pc = npc;
         hcyc += (int32_t)cyc;
         timer -= (int32_t)cyc;
-        return hcyc >= STM_CYC_PER_LINE || wsync || (flags & STM_F_FRAME_DONE);
+        return hcyc + brk >= STM_CYC_PER_LINE;
     }
     STM_DEV void finish_line()
     {
         if (hcyc >= STM_CYC_PER_LINE) { end_line(); hcyc -= STM_CYC_PER_LINE; }
-        if (wsync && hcyc != 0) { timer -= STM_CYC_PER_LINE - hcyc; end_line(); hcyc = 0; }
-        wsync = false;
+        if ((brk & BRK_WSYNC) && hcyc != 0) { timer -= STM_CYC_PER_LINE - hcyc; end_line(); hcyc = 0; }
+        brk &= ~BRK_WSYNC;
     }
-    STM_DEV void exec_one() { exec_core(); if (hcyc >= STM_CYC_PER_LINE || wsync) finish_line(); }
+    STM_DEV void exec_one() { exec_core(); if (hcyc >= STM_CYC_PER_LINE || (brk & BRK_WSYNC)) finish_line(); }
 
     // ---------------- one emulated frame ----------------
     // Rows the frame never reached are zero-filled, as the oracle does.
@@ -1101,6 +1114,7 @@ struct Emu {
         render = want_pixels;
         set_action(ale_action);
         flags &= ~(uint32_t)STM_F_FRAME_DONE;
+        brk &= ~BRK_DONE;
         tia_dirty();                                           // a new native frame: no row to reuse yet
         bool over = false;
         do {
@@ -1120,7 +1134,7 @@ struct Emu {
 #else
             if (!over) while (!exec_core()) { }
 #endif
-            ended = hcyc >= STM_CYC_PER_LINE || wsync;
+            ended = hcyc >= STM_CYC_PER_LINE || (brk & BRK_WSYNC);
             if (!over) {
                 if (ended) finish_line();
                 over = (flags & STM_F_FRAME_DONE) != 0;

@@ -17,6 +17,7 @@
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
+#include <cstdlib>
 #include <cmath>
 #include <new>
 #include "../../include/stm_b200.h"
@@ -204,7 +205,7 @@ struct DevMem {
     __device__ __forceinline__ uint32_t *quad(uint32_t row, uint32_t q) const
     { return scr + (size_t)((fsel * STM_VIS_H + row) * 10 + q) * (kTileEnvs * 4); }
     __device__ __forceinline__ void px16(uint32_t row, uint32_t q, uint32_t a, uint32_t b, uint32_t c, uint32_t d)
-    { *reinterpret_cast<uint4 *>(quad(row, q)) = make_uint4(a, b, c, d); }
+    { __stcg(reinterpret_cast<uint4 *>(quad(row, q)), make_uint4(a, b, c, d)); }
     __device__ __forceinline__ void copy_row(uint32_t dst, uint32_t src)
     {
         const uint4 *s = reinterpret_cast<const uint4 *>(quad(src, 0));
@@ -213,9 +214,9 @@ struct DevMem {
         for (int h = 0; h < 2; h++) {                    // five loads in flight, then five stores
             uint4 v[5];
             #pragma unroll
-            for (int q = 0; q < 5; q++) v[q] = s[(size_t)(5 * h + q) * kTileEnvs];
+            for (int q = 0; q < 5; q++) v[q] = __ldcg(s + (size_t)(5 * h + q) * kTileEnvs);   // L2 only: L1 is for the fetch path
             #pragma unroll
-            for (int q = 0; q < 5; q++) d[(size_t)(5 * h + q) * kTileEnvs] = v[q];
+            for (int q = 0; q < 5; q++) __stcg(d + (size_t)(5 * h + q) * kTileEnvs, v[q]);
         }
     }
     __device__ __forceinline__ void px4(uint32_t row, uint32_t g, uint32_t w) { quad(row, g >> 2)[g & 3] = w; }
@@ -586,9 +587,14 @@ int stm_ctx_create(stm_ctx **out, const stm_game_desc *desc, const uint8_t *rom,
         // the attribute is per kernel, not per ctx: always allow the largest cartridge (8 KB)
         size_t smem = (size_t)(64 * kStepThreads + 8192 / 4 + 256) * sizeof(uint32_t);
         CUDA_TRY(ctx, cudaFuncSetAttribute(stm_step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        // same L1/shared split as K4's kernels, so that CTAs of both can be resident on one SM when
-        // the policy pipeline runs tree expansion and the CNN on two streams
-        CUDA_TRY(ctx, cudaFuncSetAttribute(stm_step_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+        // Shared memory for the resident CTAs and no more: what is left of the 256 KB is L1, which holds
+        // the predecoded cartridge (8 B per image byte) every instruction fetch reads.
+        {
+            int pct = (int)((STM_STEP_MIN_CTAS * (smem + 1024) * 100 + 228 * 1024 - 1) / (228 * 1024));
+            if (const char *e = getenv("STM_STEP_CARVEOUT")) pct = atoi(e);
+            if (pct > 100) pct = 100;
+            CUDA_TRY(ctx, cudaFuncSetAttribute(stm_step_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, pct));
+        }
         return ensure_scratch(ctx, 4096);
     };
     rc = body();
