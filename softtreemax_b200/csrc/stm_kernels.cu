@@ -73,6 +73,9 @@ struct stm_ctx {
     uint8_t *h_in_state = nullptr, *h_in_stack = nullptr, *h_out_stack = nullptr;
     float *h_out_reward = nullptr; uint8_t *h_out_done = nullptr; int32_t *h_out_lives = nullptr;
     size_t h_roots = 0, h_leaves = 0;
+    // stm_bfs_host uploads the root stacks (28 KB per root) on its own stream while the first level steps
+    cudaStream_t up_stream = nullptr;
+    cudaEvent_t up_done = nullptr, up_go = nullptr;
     uint32_t reset_pc = 0;
     void *cnn = nullptr;             // K4 state (stm_cnn.cu): tiled weights + activation scratch
     long long launches = 0;
@@ -615,6 +618,9 @@ int stm_ctx_destroy(stm_ctx *ctx)
     }
     cudaFree(ctx->h_in_state); cudaFree(ctx->h_in_stack); cudaFree(ctx->h_out_stack);
     cudaFree(ctx->h_out_reward); cudaFree(ctx->h_out_done); cudaFree(ctx->h_out_lives);
+    if (ctx->up_done) cudaEventDestroy(ctx->up_done);
+    if (ctx->up_go) cudaEventDestroy(ctx->up_go);
+    if (ctx->up_stream) cudaStreamDestroy(ctx->up_stream);
     if (ctx->ev) { for (int i = 0; i < 2 * stm_ctx::kMaxTimed; i++) cudaEventDestroy(ctx->ev[i]); delete[] ctx->ev; }
     delete ctx;
     return STM_OK;
@@ -701,9 +707,12 @@ int stm_frames(stm_ctx *ctx, const uint8_t *parent_stacks, uint8_t *child_stacks
     return launch_frames(ctx, parent_stacks, child_stacks, n, fanout, (cudaStream_t)stream);
 }
 
-int stm_bfs(stm_ctx *ctx, const uint8_t *root_states, const uint8_t *root_stacks, int n_roots, int depth,
-            float gamma, int frameskip, int episodic_life, int clip_reward, uint8_t *leaf_stacks,
-            float *leaf_rewards, uint8_t *leaf_done, int32_t *leaf_lives, uint8_t *leaf_states, void *stream)
+// `stacks_ready` (optional): an event the stream must wait for before the first K3 launch reads
+// root_stacks — the emulation of the first level does not need the stacks, only the frames kernel does.
+static int bfs_impl(stm_ctx *ctx, const uint8_t *root_states, const uint8_t *root_stacks, int n_roots, int depth,
+                    float gamma, int frameskip, int episodic_life, int clip_reward, uint8_t *leaf_stacks,
+                    float *leaf_rewards, uint8_t *leaf_done, int32_t *leaf_lives, uint8_t *leaf_states, void *stream,
+                    cudaEvent_t stacks_ready)
 {
     if (!ctx || !root_states || !root_stacks || !leaf_stacks || !leaf_rewards || n_roots < 1 || depth < 1 || frameskip < 1)
         return fail(ctx, STM_ERR_ARG, "stm_bfs: bad argument");
@@ -751,6 +760,7 @@ int stm_bfs(stm_ctx *ctx, const uint8_t *root_states, const uint8_t *root_stacks
             int cn = (int)((n_dst - off) < step ? (n_dst - off) : step);
             if ((rc = launch_step(ctx, ctx->pool_state[nxt] + off * STM_STATE_BYTES, nullptr, cn, frameskip, episodic_life, weight,
                                   ctx->pool_reward[nxt] + off, ctx->pool_done[nxt] + off, ctx->pool_lives[nxt] + off, 1, st))) return rc;
+            if (stacks_ready) { CUDA_TRY(ctx, cudaStreamWaitEvent(st, stacks_ready, 0)); stacks_ready = nullptr; }
             // parent of env (off+i) is (off+i)/A = off/A + i/A because off % A == 0
             if ((rc = launch_frames(ctx, pstack + (off / A) * STM_STACK * STM_OBS_BYTES, cstack + off * STM_STACK * STM_OBS_BYTES, cn, A, st))) return rc;
         }
@@ -764,6 +774,14 @@ int stm_bfs(stm_ctx *ctx, const uint8_t *root_states, const uint8_t *root_stacks
     if (leaf_states) CUDA_TRY(ctx, cudaMemcpyAsync(leaf_states, ctx->pool_state[fin], L * STM_STATE_BYTES, cudaMemcpyDeviceToDevice, st));
     CUDA_TRY(ctx, cudaGetLastError());
     return STM_OK;
+}
+
+int stm_bfs(stm_ctx *ctx, const uint8_t *root_states, const uint8_t *root_stacks, int n_roots, int depth,
+            float gamma, int frameskip, int episodic_life, int clip_reward, uint8_t *leaf_stacks,
+            float *leaf_rewards, uint8_t *leaf_done, int32_t *leaf_lives, uint8_t *leaf_states, void *stream)
+{
+    return bfs_impl(ctx, root_states, root_stacks, n_roots, depth, gamma, frameskip, episodic_life, clip_reward,
+                    leaf_stacks, leaf_rewards, leaf_done, leaf_lives, leaf_states, stream, nullptr);
 }
 
 int stm_bfs_host(stm_ctx *ctx, const uint8_t *root_states, const uint8_t *root_stacks, int n_roots, int depth,
@@ -792,12 +810,22 @@ int stm_bfs_host(stm_ctx *ctx, const uint8_t *root_states, const uint8_t *root_s
         CUDA_TRY(ctx, cudaMalloc(&ctx->h_out_lives, L * sizeof(int32_t)));
         ctx->h_leaves = L;
     }
+    if (!ctx->up_stream) {
+        CUDA_TRY(ctx, cudaStreamCreateWithFlags(&ctx->up_stream, cudaStreamNonBlocking));
+        CUDA_TRY(ctx, cudaEventCreateWithFlags(&ctx->up_done, cudaEventDisableTiming));
+        CUDA_TRY(ctx, cudaEventCreateWithFlags(&ctx->up_go, cudaEventDisableTiming));
+    }
+    // The states (256 B per root) go first on the caller's stream; the stacks (28 KB per root, needed
+    // only by the first frames kernel) follow on the upload stream, under the first level's emulation.
+    CUDA_TRY(ctx, cudaEventRecord(ctx->up_go, st));                      // after whatever the caller queued before us
+    CUDA_TRY(ctx, cudaStreamWaitEvent(ctx->up_stream, ctx->up_go, 0));
     CUDA_TRY(ctx, cudaMemcpyAsync(ctx->h_in_state, root_states, (size_t)n_roots * STM_STATE_BYTES, cudaMemcpyHostToDevice, st));
-    CUDA_TRY(ctx, cudaMemcpyAsync(ctx->h_in_stack, root_stacks, (size_t)n_roots * SB, cudaMemcpyHostToDevice, st));
-    int rc = stm_bfs(ctx, ctx->h_in_state, ctx->h_in_stack, n_roots, depth, gamma, frameskip, episodic_life, clip_reward,
-                     leaf_stacks_on_device ? leaf_stacks : ctx->h_out_stack, ctx->h_out_reward, ctx->h_out_done,
-                     ctx->h_out_lives, nullptr, stream);
-    if (rc) return rc;
+    CUDA_TRY(ctx, cudaMemcpyAsync(ctx->h_in_stack, root_stacks, (size_t)n_roots * SB, cudaMemcpyHostToDevice, ctx->up_stream));
+    CUDA_TRY(ctx, cudaEventRecord(ctx->up_done, ctx->up_stream));
+    int rc = bfs_impl(ctx, ctx->h_in_state, ctx->h_in_stack, n_roots, depth, gamma, frameskip, episodic_life, clip_reward,
+                      leaf_stacks_on_device ? leaf_stacks : ctx->h_out_stack, ctx->h_out_reward, ctx->h_out_done,
+                      ctx->h_out_lives, nullptr, stream, ctx->up_done);
+    if (rc) { cudaStreamSynchronize(ctx->up_stream); return rc; }
     if (!leaf_stacks_on_device) CUDA_TRY(ctx, cudaMemcpyAsync(leaf_stacks, ctx->h_out_stack, L * SB, cudaMemcpyDeviceToHost, st));
     CUDA_TRY(ctx, cudaMemcpyAsync(leaf_rewards, ctx->h_out_reward, L * sizeof(float), cudaMemcpyDeviceToHost, st));
     if (leaf_done) CUDA_TRY(ctx, cudaMemcpyAsync(leaf_done, ctx->h_out_done, L, cudaMemcpyDeviceToHost, st));
