@@ -1016,27 +1016,26 @@ struct Emu {
         // number the compiler cannot see through — otherwise it folds the chain back into the jump
         // table, whose indexed constant load + indirect branch cost more than the whole chain); the
         // rest go through the jump table.
-        uint32_t gq = grp;
-        STM_OPAQUE(gq);
-        if (gq == G_STORE) {
+        auto is = [&](uint32_t g) { uint32_t t = grp; STM_OPAQUE(t); return t == g; };   // a fresh copy per test
+        if (is(G_STORE)) {
             w0 = ((data & 1) ? a : 0xFFu) & ((data & 2) ? x : 0xFFu) & ((data & 4) ? y : 0xFFu);
             nwr = 1;
-        } else if (gq == G_LOAD) {
+        } else if (is(G_LOAD)) {
             if (data & 1) a = v;
             if (data & 2) x = v;
             if (data & 4) y = v;
             zn = v;
-        } else if (gq == G_CMP) {
+        } else if (is(G_CMP)) {
             cmp(data == 0 ? a : (data == 1 ? x : y), v);
-        } else if (gq == G_INCDEC_REG) {
+        } else if (is(G_INCDEC_REG)) {
             uint32_t d = data >> 2;
             if (data & 1) { x = (x + d) & 0xFF; zn = x; } else { y = (y + d) & 0xFF; zn = y; }
-        } else if (gq == G_XFER) {
+        } else if (is(G_XFER)) {
             uint32_t s = data & 3, d = (data >> 2) & 3;
             uint32_t val = s == 0 ? a : (s == 1 ? x : (s == 2 ? y : sp));
             if (d == 0) a = val; else if (d == 1) x = val; else if (d == 2) y = val; else sp = val;
             if (data & 16) zn = val;
-        } else if (gq == G_FLAG) {
+        } else if (is(G_FLAG)) {
             p = (data & 256) ? (p | (data & 0xFF)) : (p & ~(data & 0xFF));
         } else switch (grp) {
         case G_PUSH: w0 = data ? (get_p() | FB) : a; nwr = 1; wpush = true; break;
