@@ -7,7 +7,7 @@ import ctypes as C
 import os
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libstm_b200.so")
+LIB_PATH = os.environ.get("STM_B200_LIB", os.path.join(HERE, "libstm_b200.so"))   # override: A/B builds of the same ABI
 
 STATE_BYTES = 256
 OBS = 84
