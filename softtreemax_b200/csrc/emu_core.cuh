@@ -493,8 +493,10 @@ struct TiaLine {
         bool comb = (flags & STM_F_HMOVE_BLANK) != 0;
         bool pfp = (ctrlpf & 4) != 0, score = (ctrlpf & 2) != 0 && !pfp;
         if (draw) {
-            c_p0 = (m.ld8(O_COLUP0) >> 1) * 0x01010101u; c_p1 = (m.ld8(O_COLUP1) >> 1) * 0x01010101u;
-            c_pf = (m.ld8(O_COLUPF) >> 1) * 0x01010101u; c_bk = (m.ld8(O_COLUBK) >> 1) * 0x01010101u;
+            // pixels are stored as GREY values (the palette look-up happens here, four times per line,
+            // not per pixel in the frame kernel); colour index 0 is grey 0, so blank rows stay zero
+            c_p0 = m.grey(m.ld8(O_COLUP0) >> 1) * 0x01010101u; c_p1 = m.grey(m.ld8(O_COLUP1) >> 1) * 0x01010101u;
+            c_pf = m.grey(m.ld8(O_COLUPF) >> 1) * 0x01010101u; c_bk = m.grey(m.ld8(O_COLUBK) >> 1) * 0x01010101u;
         }
         #pragma unroll 1
         for (int w = w0; w <= w1; w++) {
@@ -557,8 +559,9 @@ STM_NOINLINE void tia_copy_row(M m, uint32_t dst, uint32_t src) { m.copy_row(dst
 //   void     fetch(off, &w, &ops)   predecoded instruction at image offset off: w = hot decode word of
 //                                   the opcode there, ops = operand bytes b1 | b2 << 8 (build_predecode)
 //   uint32_t opinfo(op)                                                    hot decode word (build_hot_table)
-//   void px16(row, q, w0..w3) store 16 pixels of native row `row`, quad q (0..9): four packed words
-//   void px4(row, g, word)    store 4 pixels (colour indices), group g (0..39)
+//   uint32_t grey(idx)        NTSC colour index (COLUxx >> 1) -> 8-bit grey (include/stm_palette.h)
+//   void px16(row, q, w0..w3) store 16 pixels (grey values) of native row `row`, quad q (0..9): four packed words
+//   void px4(row, g, word)    store 4 pixels, group g (0..39)
 //   void px1(row, x, v)       store 1 pixel
 //   void copy_row(dst, src)   copy the 160 pixels of native row src to row dst (same frame)
 //

@@ -185,6 +185,8 @@ stm_clone_kernel(const uint4 *__restrict__ src, uint4 *__restrict__ dst,
 // lane t always hits bank t%32: conflict-free for every access pattern, RAM bytes included), the
 // cartridge image (4 or 8 KB) and the decode table.
 // ---------------------------------------------------------------------------------------------
+__constant__ uint8_t c_gray[128] = STM_GRAY_LUT_INIT;
+
 struct DevMem {
     uint8_t *blob;             // &sblob[tid] as bytes
     const uint32_t *rom;       // shared
@@ -204,6 +206,7 @@ struct DevMem {
     __device__ __forceinline__ void fetch(uint32_t off, uint32_t &w, uint32_t &ops) const
     { uint2 v = __ldg(pre + off); w = v.x; ops = v.y; }
     __device__ __forceinline__ uint32_t opinfo(uint32_t op) const { return lut[op]; }
+    __device__ __forceinline__ uint32_t grey(uint32_t i) const { return c_gray[i & 127]; }
     // scr points at this lane's uint4 slot of (frame 0, row 0, quad 0); quads are kTileEnvs uint4 apart
     __device__ __forceinline__ uint32_t *quad(uint32_t row, uint32_t q) const
     { return scr + (size_t)((fsel * STM_VIS_H + row) * 10 + q) * (kTileEnvs * 4); }
@@ -295,72 +298,74 @@ stm_step_kernel(const StepArgs a)
 }
 
 // ---------------------------------------------------------------------------------------------
-// K3 — observation kernel.  One CTA per (tile of 32 envs, output row oy).  The four native rows
-// the output row needs (2 source rows x 2 frames) are read coalesced (lane-minor) and transposed
-// into shared memory env-major with an odd pitch; then 21 threads per env each produce one packed
-// word (4 output pixels): grey LUT, 2x2 bilinear with integer weights, max over the two frames.
+// K3 — observation kernel.  One CTA per (tile of 32 envs, output row oy).  K2 stores GREY pixels,
+// so the 84x84 bilinear resize is pure integer arithmetic here, done separably:
+//   vertical   V[x] = wy0 * row_y0[x] + wy1 * row_y1[x]   (wy0 + wy1 = 4, V <= 1020), two pixels per
+//              32-bit multiply-add, straight from the coalesced (lane-minor) 16-byte global loads
+//              into shared memory as 16-bit values, env-major with an odd word pitch;
+//   horizontal out = ((42 - fx) * V[x0] + fx * V[x0 + 1] + 84) / 168, one rounding, as the oracle;
+// then the max over the two frames, four output pixels per packed word, 8 threads per env.
 // The same CTA moves row oy of the three older stack frames from the parent's stack.
 // HBM per leaf: reads 2*168*160 B of native frames (rows 2 mod 5 are never sampled) + 21 168 B of
 // parent stack, writes 28 224 B.
 // ---------------------------------------------------------------------------------------------
 constexpr int kFrameThreads = 256;
-constexpr int kPitch = 41;      // words per (source row, env) in shared memory; odd => conflict-free transpose
-
-__constant__ uint8_t c_gray[128] = STM_GRAY_LUT_INIT;
+constexpr int kVPitch = 83;     // words per (frame, env) row of V in shared memory: 81 used, odd => conflict-free
 
 __global__ void __launch_bounds__(kFrameThreads)
 stm_frames_kernel(const uint32_t *__restrict__ scratch, const uint8_t *__restrict__ stepped,
                   const uint8_t *__restrict__ parent, uint8_t *__restrict__ child,
                   int n, int fanout, int nframes)
 {
-    __shared__ uint32_t srows[4][kTileEnvs * kPitch];      // [frame*2 + {y0,y1}], GREY values (LUT applied while staging)
-    __shared__ uint8_t sgray[128];
+    __shared__ uint32_t sv[2][kTileEnvs * kVPitch];        // [frame][env][x / 2]: V[x] | V[x + 1] << 16
     __shared__ uint8_t sx0[STM_OBS_W], sfx[STM_OBS_W];     // source column and weight of every output column
     const int tile = blockIdx.x, oy = blockIdx.y, tid = threadIdx.x;
     const int env0 = tile * kTileEnvs;
     const int nenv = min(kTileEnvs, n - env0);
-    if (tid < 128) sgray[tid] = c_gray[tid];
     if (tid < STM_OBS_W) { int nx = 80 * tid + 19; sx0[tid] = (uint8_t)(nx / 42); sfx[tid] = (uint8_t)(nx % 42); }
-    __syncthreads();
     const int ny = 10 * oy + 3, y0 = ny >> 2, fy = ny & 3;
     const int y1 = min(y0 + 1, STM_VIS_H - 1);
+    const uint32_t wy0 = 4 - fy, wy1 = fy;
     const uint4 *tbase = reinterpret_cast<const uint4 *>(scratch + (size_t)tile * kTileWords);
-    auto grey4 = [&](uint32_t w) -> uint32_t {
-        return (uint32_t)sgray[w & 127] | ((uint32_t)sgray[(w >> 8) & 127] << 8) |
-               ((uint32_t)sgray[(w >> 16) & 127] << 16) | ((uint32_t)sgray[(w >> 24) & 127] << 24);
-    };
-    for (int i = tid; i < 4 * 10 * kTileEnvs; i += kFrameThreads) {
-        int lane = i & 31, q = (i >> 5) % 10, rs = i / (10 * 32);
-        int frame = rs >> 1, row = (rs & 1) ? y1 : y0;
-        uint4 v = make_uint4(0, 0, 0, 0);
-        if (frame >= 2 - nframes)        // with a single rendered frame only slot 1 holds data
-            v = tbase[((size_t)(frame * STM_VIS_H + row) * 10 + q) * kTileEnvs + lane];
-        uint32_t *d = &srows[rs][lane * kPitch + 4 * q];
-        if (frame >= 2 - nframes) { d[0] = grey4(v.x); d[1] = grey4(v.y); d[2] = grey4(v.z); d[3] = grey4(v.w); }
-        else { d[0] = 0; d[1] = 0; d[2] = 0; d[3] = 0; }
+    // vertical pass: item = (frame, quad, lane)
+    for (int i = tid; i < 2 * 10 * kTileEnvs; i += kFrameThreads) {
+        const int lane = i & 31, q = (i >> 5) % 10, frame = i / (10 * 32);
+        uint32_t *d = &sv[frame][lane * kVPitch + 8 * q];
+        if (frame >= 2 - nframes) {          // with a single rendered frame only slot 1 holds data
+            const uint4 a = __ldcs(tbase + ((size_t)(frame * STM_VIS_H + y0) * 10 + q) * kTileEnvs + lane);
+            const uint4 b = __ldcs(tbase + ((size_t)(frame * STM_VIS_H + y1) * 10 + q) * kTileEnvs + lane);
+            const uint32_t aw[4] = {a.x, a.y, a.z, a.w}, bw[4] = {b.x, b.y, b.z, b.w};
+            #pragma unroll
+            for (int k = 0; k < 4; k++) {
+                const uint32_t ve = wy0 * (aw[k] & 0x00FF00FFu) + wy1 * (bw[k] & 0x00FF00FFu);            // px 0, 2
+                const uint32_t vo = wy0 * ((aw[k] >> 8) & 0x00FF00FFu) + wy1 * ((bw[k] >> 8) & 0x00FF00FFu);   // px 1, 3
+                d[2 * k] = __byte_perm(ve, vo, 0x5410);
+                d[2 * k + 1] = __byte_perm(ve, vo, 0x7632);
+            }
+        } else {
+            #pragma unroll
+            for (int k = 0; k < 8; k++) d[k] = 0;
+        }
+        if (q == 9) d[8] = d[7] >> 16;       // V[160] = V[159]: the right tap of the last column clamps
     }
     __syncthreads();
-    // new frame -> child[env][3][oy][:]: 8 threads per env, each up to 3 packed words
+    // horizontal pass + max: 8 threads per env, each up to 3 packed words of the new frame
     {
         const int e = tid >> 3, sub = tid & 7;
         if (e < nenv) {
             const bool live = stepped[env0 + e] != 0;
-            const uint8_t *r00 = reinterpret_cast<const uint8_t *>(&srows[0][e * kPitch]);
-            const uint8_t *r01 = reinterpret_cast<const uint8_t *>(&srows[1][e * kPitch]);
-            const uint8_t *r10 = reinterpret_cast<const uint8_t *>(&srows[2][e * kPitch]);
-            const uint8_t *r11 = reinterpret_cast<const uint8_t *>(&srows[3][e * kPitch]);
+            const uint16_t *v0 = reinterpret_cast<const uint16_t *>(&sv[0][e * kVPitch]);
+            const uint16_t *v1 = reinterpret_cast<const uint16_t *>(&sv[1][e * kVPitch]);
             uint32_t *dst = reinterpret_cast<uint32_t *>(child + ((size_t)(env0 + e) * STM_STACK + 3) * STM_OBS_BYTES + oy * STM_OBS_W);
-            const int wy0 = 4 - fy, wy1 = fy;
             for (int wq = sub; wq < 21; wq += 8) {
                 uint32_t packed = 0;
                 if (live) {
                     #pragma unroll
                     for (int k = 0; k < 4; k++) {
                         const int ox = 4 * wq + k;
-                        const int x0 = sx0[ox], fx = sfx[ox], x1 = min(x0 + 1, STM_VIS_W - 1);
-                        const int w00 = wy0 * (42 - fx), w01 = wy0 * fx, w10 = wy1 * (42 - fx), w11 = wy1 * fx;
-                        const uint32_t va = (uint32_t)(w00 * r00[x0] + w01 * r00[x1] + w10 * r01[x0] + w11 * r01[x1] + 84) / 168u;
-                        const uint32_t vb = (uint32_t)(w00 * r10[x0] + w01 * r10[x1] + w10 * r11[x0] + w11 * r11[x1] + 84) / 168u;
+                        const uint32_t x0 = sx0[ox], fx = sfx[ox];
+                        const uint32_t va = ((42u - fx) * v0[x0] + fx * v0[x0 + 1] + 84u) / 168u;
+                        const uint32_t vb = ((42u - fx) * v1[x0] + fx * v1[x0 + 1] + 84u) / 168u;
                         packed |= max(va, vb) << (8 * k);
                     }
                 }

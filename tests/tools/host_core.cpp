@@ -3,6 +3,7 @@
 // this GPU-less container (tests/test_host_core.py).  Never loaded by the product package.
 #include <cstring>
 #include <cstdint>
+#include "../../include/stm_palette.h"
 #include "../../softtreemax_b200/csrc/emu_core.cuh"
 
 namespace {
@@ -23,6 +24,7 @@ struct HostMem {
         ops = rom[win | ((off + 1) & mask)] | (rom[win | ((off + 2) & mask)] << 8);
     }
     uint32_t opinfo(uint32_t op) const { return lut[op]; }
+    uint32_t grey(uint32_t i) const { static const uint8_t g[128] = STM_GRAY_LUT_INIT; return g[i & 127]; }
     void px4(uint32_t row, uint32_t g, uint32_t w) { if (fb) memcpy(fb + row * 160 + 4 * g, &w, 4); }
     void px16(uint32_t row, uint32_t q, uint32_t a, uint32_t b, uint32_t c, uint32_t d)
     { px4(row, 4 * q, a); px4(row, 4 * q + 1, b); px4(row, 4 * q + 2, c); px4(row, 4 * q + 3, d); }
