@@ -22,7 +22,9 @@ import time
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
-GAME = "synth_breakout"          # stands for BreakoutNoFrameskip-v4 (A = 4)
+GAME = "synth_breakout"          # default cartridge; --game overrides
+STANDS_FOR = {"synth_breakout": "BreakoutNoFrameskip-v4", "synth_pong": "PongNoFrameskip-v4",
+              "synth_pacman": "MsPacmanNoFrameskip-v4", "synth_torture": "opcode/TIA torture cartridge"}
 METRIC = "tree_leaf_states_per_sec"
 UNIT = "leaves/s"
 CYCLES_PER_NODE_STEP = 4 * 262 * 76          # emulated CPU cycles per node-step (NTSC nominal)
@@ -46,15 +48,21 @@ class ClockSampler(threading.Thread):
     def __init__(self, index):
         super().__init__(daemon=True)
         self.index, self.samples, self.reasons, self.max_mhz, self._halt = index, [], set(), None, threading.Event()
-
-    def run(self):
-        try:
+        self.nv = self.h = None
+        try:                                                        # NVML is brought up here, before the timed region
             import pynvml as nv
             nv.nvmlInit()
-            h = nv.nvmlDeviceGetHandleByIndex(self.index)
-            self.max_mhz = nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM)
-            names = {nv.nvmlClocksEventReasonHwSlowdown if hasattr(nv, "nvmlClocksEventReasonHwSlowdown") else 0x8: "hw_slowdown",
-                     0x40: "hw_thermal_slowdown", 0x20: "sw_thermal_slowdown", 0x4: "sw_power_cap"}
+            self.nv, self.h = nv, nv.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = nv.nvmlDeviceGetMaxClockInfo(self.h, nv.NVML_CLOCK_SM)
+        except Exception as e:                                      # NVML missing: report that, do not fail the run
+            self.reasons.add(f"nvml_unavailable:{type(e).__name__}")
+
+    def run(self):
+        nv, h = self.nv, self.h
+        if nv is None:
+            return
+        names = {0x8: "hw_slowdown", 0x40: "hw_thermal_slowdown", 0x20: "sw_thermal_slowdown", 0x4: "sw_power_cap"}
+        try:
             while not self._halt.is_set():
                 self.samples.append(nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM))
                 try:
@@ -64,9 +72,9 @@ class ClockSampler(threading.Thread):
                 for bit, name in names.items():
                     if r & bit:
                         self.reasons.add(name)
-                time.sleep(0.05)
-        except Exception as e:                                      # NVML missing: report that, do not fail the run
-            self.reasons.add(f"nvml_unavailable:{type(e).__name__}")
+                time.sleep(0.01)
+        except Exception as e:
+            self.reasons.add(f"nvml_error:{type(e).__name__}")
 
     def stop(self):
         self._halt.set()
@@ -76,10 +84,10 @@ class ClockSampler(threading.Thread):
                 "samples": len(s)}
 
 
-def cpu_oracle_rate(depth, seconds, threads):
+def cpu_oracle_rate(depth, seconds, threads, game=None):
     """leaves/s of the CPU oracle (oracle/, the timed CPU baseline) on a bounded sample."""
     from oracle import orc
-    g = orc.Game(GAME)
+    g = orc.Game(game or GAME)
     R = 64
     roots, stacks = orc.make_roots(g, R, seed=1234)
     g.bfs(roots[:8], stacks[:8], depth, nthreads=threads)           # warm-up
@@ -102,7 +110,7 @@ def run_reference(args, rank):
     threads = os.cpu_count() or 1
     vals = []
     for i in range(args.warmup + args.steps):
-        rate, leaves, dt = cpu_oracle_rate(args.depth, seconds=max(1.0, 20.0 / max(1, args.steps)), threads=threads)
+        rate, leaves, dt = cpu_oracle_rate(args.depth, seconds=max(1.0, 20.0 / max(1, args.steps)), threads=threads, game=args.game)
         if i >= args.warmup:
             vals.append((rate, leaves, dt))
     rate = sum(v[1] for v in vals) / sum(v[2] for v in vals)
@@ -118,11 +126,18 @@ def run_reference(args, rank):
     print(json.dumps(line), flush=True)
 
 
+def n_actions_of(game):
+    import json as _json
+    table = _json.load(open(os.path.join(ROOT, "softtreemax_b200", "roms", "games.json")))
+    return len(table[game]["actions"])
+
+
 def workload_config(args):
-    return {"workload": f"{GAME} (stands for BreakoutNoFrameskip-v4, A=4) tree_depth={args.depth} roots_per_gpu={args.roots} "
-                        f"frameskip=4 gamma=0.99 clip_reward episodic_life",
-            "roots_per_gpu": args.roots, "depth": args.depth, "leaves_per_gpu": args.roots * 4 ** args.depth,
-            "l2": "working set > L2: leaf stacks written per step = %.2f GB per GPU" % (args.roots * 4 ** args.depth * 28224 / 1e9),
+    A = n_actions_of(args.game)
+    return {"workload": f"{args.game} (stands for {STANDS_FOR.get(args.game, args.game)}, A={A}) tree_depth={args.depth} "
+                        f"roots_per_gpu={args.roots} frameskip=4 gamma=0.99 clip_reward episodic_life",
+            "roots_per_gpu": args.roots, "depth": args.depth, "leaves_per_gpu": args.roots * A ** args.depth,
+            "l2": "working set > L2: leaf stacks written per step = %.2f GB per GPU" % (args.roots * A ** args.depth * 28224 / 1e9),
             "parallelism": f"roots sharded over {args.gpus} GPU(s), no data-path collective"}
 
 
@@ -133,6 +148,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--roots", type=int, default=4096, help="root states per GPU")
     ap.add_argument("--depth", type=int, default=2)
+    ap.add_argument("--game", default=GAME, help="cartridge name (softtreemax_b200/roms/games.json)")
+    ap.add_argument("--no-policy", action="store_true", help="skip the bfs + CNN + logits arm (sweeps)")
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     ap.add_argument("--scratch-envs", type=int, default=262144, help="envs per K2/K3 pass (native-frame scratch: 67 KB each)")
@@ -160,9 +177,9 @@ def main():
     if world > 1:
         os.environ["NCCL_DEBUG"] = "WARN"            # keep NCCL's version banner off stdout: one JSON line only
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-    A, depth, R = 4, args.depth, args.roots
+    A, depth, R = n_actions_of(args.game), args.depth, args.roots
     L = R * A ** depth
-    eng = Engine(GAME, device=local, scratch_envs=min(L, args.scratch_envs))
+    eng = Engine(args.game, device=local, scratch_envs=min(L, args.scratch_envs))
     dev = eng.device
     # every rank owns its own shard of roots (different seeds => different states per rank)
     states, stacks = make_roots(eng, R, seed=1234 + rank)
@@ -212,108 +229,111 @@ def main():
     per_kernel = eng.timing_read()
     eng.timing(False)
 
-    # ---------------- policy arm: bfs + NatureCNN on leaves and roots (K4) + SoftTreeMax logits (K5) ----------
-    from softtreemax_b200 import ops
-    import math
-    gtor = torch.Generator().manual_seed(4)                  # reference default seed, utils.py:67
-    shapes = {"cnn.0": (32, 4, 8, 8), "cnn.2": (64, 32, 4, 4), "cnn.4": (64, 64, 3, 3), "linear.0": (512, 3136),
-              "action_net": (A, 512), "value_net": (1, 512)}
-    params = {}
-    for k, shp in shapes.items():                            # random-init weights of the architecture (orthogonal, SB3 gains)
-        w = torch.empty(shp)
-        torch.nn.init.orthogonal_(w, gain={"action_net": 0.01, "value_net": 1.0}.get(k, math.sqrt(2)), generator=gtor)
-        params[k + ".weight"], params[k + ".bias"] = w, torch.zeros(shp[0])
-    eng.cnn_set_weights(params)
-    val_coef = 0.99 ** depth
+    ms_policy = ms_policy_e2e = ms_pipe = c_ms = 0.0
+    hs_pin = hk_pin = None
+    if not args.no_policy:
+        # ---------------- policy arm: bfs + NatureCNN on leaves and roots (K4) + SoftTreeMax logits (K5) ----------
+        from softtreemax_b200 import ops
+        import math
+        gtor = torch.Generator().manual_seed(4)                  # reference default seed, utils.py:67
+        shapes = {"cnn.0": (32, 4, 8, 8), "cnn.2": (64, 32, 4, 4), "cnn.4": (64, 64, 3, 3), "linear.0": (512, 3136),
+                  "action_net": (A, 512), "value_net": (1, 512)}
+        params = {}
+        for k, shp in shapes.items():                            # random-init weights of the architecture (orthogonal, SB3 gains)
+            w = torch.empty(shp)
+            torch.nn.init.orthogonal_(w, gain={"action_net": 0.01, "value_net": 1.0}.get(k, math.sqrt(2)), generator=gtor)
+            params[k + ".weight"], params[k + ".bias"] = w, torch.zeros(shp[0])
+        eng.cnn_set_weights(params)
+        val_coef = 0.99 ** depth
 
-    def policy_step():
-        eng.bfs(states, stacks, depth, out=out)
-        head_leaf, _ = eng.cnn_forward(out["stacks"])
-        head_root, val_root = eng.cnn_forward(stacks)
-        logits, _, _ = ops.softtreemax_logits_full(eng, head_leaf.reshape(R, A ** depth, A), out["rewards"].reshape(R, -1),
-                                                  val_coef, 1.0, 1.0, 0.001, False)
-        return logits, val_root
+        def policy_step():
+            eng.bfs(states, stacks, depth, out=out)
+            head_leaf, _ = eng.cnn_forward(out["stacks"])
+            head_root, val_root = eng.cnn_forward(stacks)
+            logits, _, _ = ops.softtreemax_logits_full(eng, head_leaf.reshape(R, A ** depth, A), out["rewards"].reshape(R, -1),
+                                                      val_coef, 1.0, 1.0, 0.001, False)
+            return logits, val_root
 
-    for _ in range(2):
-        policy_step()
-    barrier()
-    p0, p1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    c_ms = 0.0
-    p0.record()
-    for _ in range(args.steps):
-        policy_step()
-    p1.record()
-    barrier()
-    ms_policy = p0.elapsed_time(p1)
-    # pipelined: tree expansion of batch i+1 (stream A) overlaps CNN + logits of batch i (stream B);
-    # two leaf buffers, events for the hand-offs.  K2 leaves issue slots and the tensor pipe idle,
-    # K4 leaves the ALUs idle: they co-run.
-    out2 = dict(stacks=torch.empty_like(out["stacks"]), rewards=torch.empty_like(out["rewards"]),
-                done=torch.empty_like(out["done"]), lives=torch.empty_like(out["lives"]), states=None)
-    bufs = [out, out2]
-    s_tree, s_net = torch.cuda.Stream(device=dev), torch.cuda.Stream(device=dev)
-    ready = [torch.cuda.Event(), torch.cuda.Event()]
-    free = [torch.cuda.Event(), torch.cuda.Event()]
+        for _ in range(2):
+            policy_step()
+        barrier()
+        p0, p1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        c_ms = 0.0
+        p0.record()
+        for _ in range(args.steps):
+            policy_step()
+        p1.record()
+        barrier()
+        ms_policy = p0.elapsed_time(p1)
+        # pipelined: tree expansion of batch i+1 (stream A) overlaps CNN + logits of batch i (stream B);
+        # two leaf buffers, events for the hand-offs.  K2 leaves issue slots and the tensor pipe idle,
+        # K4 leaves the ALUs idle: they co-run.
+        out2 = dict(stacks=torch.empty_like(out["stacks"]), rewards=torch.empty_like(out["rewards"]),
+                    done=torch.empty_like(out["done"]), lives=torch.empty_like(out["lives"]), states=None)
+        bufs = [out, out2]
+        s_tree, s_net = torch.cuda.Stream(device=dev), torch.cuda.Stream(device=dev)
+        ready = [torch.cuda.Event(), torch.cuda.Event()]
+        free = [torch.cuda.Event(), torch.cuda.Event()]
 
-    def pipelined(nsteps):
-        main = torch.cuda.current_stream()
-        s_tree.wait_stream(main)
-        s_net.wait_stream(main)
-        for i in range(nsteps):
-            b = i & 1
-            with torch.cuda.stream(s_tree):
-                if i >= 2:
-                    s_tree.wait_event(free[b])
-                eng.bfs(states, stacks, depth, out=bufs[b])
-                ready[b].record(s_tree)
-            with torch.cuda.stream(s_net):
-                s_net.wait_event(ready[b])
-                hl, _ = eng.cnn_forward(bufs[b]["stacks"])
-                eng.cnn_forward(stacks)
-                ops.softtreemax_logits_full(eng, hl.reshape(R, A ** depth, A), bufs[b]["rewards"].reshape(R, -1),
-                                            val_coef, 1.0, 1.0, 0.001, False)
-                free[b].record(s_net)
-        main.wait_stream(s_tree)
-        main.wait_stream(s_net)
+        def pipelined(nsteps):
+            main = torch.cuda.current_stream()
+            s_tree.wait_stream(main)
+            s_net.wait_stream(main)
+            for i in range(nsteps):
+                b = i & 1
+                with torch.cuda.stream(s_tree):
+                    if i >= 2:
+                        s_tree.wait_event(free[b])
+                    eng.bfs(states, stacks, depth, out=bufs[b])
+                    ready[b].record(s_tree)
+                with torch.cuda.stream(s_net):
+                    s_net.wait_event(ready[b])
+                    hl, _ = eng.cnn_forward(bufs[b]["stacks"])
+                    eng.cnn_forward(stacks)
+                    ops.softtreemax_logits_full(eng, hl.reshape(R, A ** depth, A), bufs[b]["rewards"].reshape(R, -1),
+                                                val_coef, 1.0, 1.0, 0.001, False)
+                    free[b].record(s_net)
+            main.wait_stream(s_tree)
+            main.wait_stream(s_net)
 
-    pipelined(2)
-    barrier()
-    r0, r1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    r0.record()
-    pipelined(args.steps)
-    r1.record()
-    barrier()
-    ms_pipe = r0.elapsed_time(r1)
-    # K4 alone, same inputs, for its tensor roofline
-    c0, c1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    c0.record()
-    for _ in range(args.steps):
-        eng.cnn_forward(out["stacks"])
-    c1.record()
-    torch.cuda.synchronize()
-    c_ms = c0.elapsed_time(c1)
-    # policy end to end: host roots in, host logits + values out
-    h_logits = torch.empty((R, A), dtype=torch.float32).pin_memory()
-    h_values = torch.empty((R,), dtype=torch.float32).pin_memory()
-    hs_pin, hk_pin = states.cpu().pin_memory(), stacks.cpu().pin_memory()
+        pipelined(2)
+        barrier()
+        r0, r1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        r0.record()
+        pipelined(args.steps)
+        r1.record()
+        barrier()
+        ms_pipe = r0.elapsed_time(r1)
+        # K4 alone, same inputs, for its tensor roofline
+        c0, c1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        c0.record()
+        for _ in range(args.steps):
+            eng.cnn_forward(out["stacks"])
+        c1.record()
+        torch.cuda.synchronize()
+        c_ms = c0.elapsed_time(c1)
+        # policy end to end: host roots in, host logits + values out
+        h_logits = torch.empty((R, A), dtype=torch.float32).pin_memory()
+        h_values = torch.empty((R,), dtype=torch.float32).pin_memory()
+        hs_pin, hk_pin = states.cpu().pin_memory(), stacks.cpu().pin_memory()
 
-    def policy_step_host():
-        states.copy_(hs_pin, non_blocking=True)
-        stacks.copy_(hk_pin, non_blocking=True)
-        lg, vr = policy_step()
-        h_logits.copy_(lg, non_blocking=True)
-        h_values.copy_(vr, non_blocking=True)
-        torch.cuda.current_stream().synchronize()
+        def policy_step_host():
+            states.copy_(hs_pin, non_blocking=True)
+            stacks.copy_(hk_pin, non_blocking=True)
+            lg, vr = policy_step()
+            h_logits.copy_(lg, non_blocking=True)
+            h_values.copy_(vr, non_blocking=True)
+            torch.cuda.current_stream().synchronize()
 
-    policy_step_host()
-    barrier()
-    q0, q1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    q0.record()
-    for _ in range(args.steps):
         policy_step_host()
-    q1.record()
-    barrier()
-    ms_policy_e2e = q0.elapsed_time(q1)
+        barrier()
+        q0, q1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        q0.record()
+        for _ in range(args.steps):
+            policy_step_host()
+        q1.record()
+        barrier()
+        ms_policy_e2e = q0.elapsed_time(q1)
 
     # ---------------- end-to-end arm: host roots in, host rewards/done/lives out ----------------
     h_states = states.cpu().pin_memory()
@@ -381,11 +401,12 @@ def main():
         }
         tf_peak = float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["bf16_tflops"]) \
             if os.path.exists(os.path.join(ROOT, "MEASURED_PEAKS.json")) else 1590.0
-        cnn_tflops = L * args.steps * (18685952 + 1024 * (A + 1)) / (c_ms / 1e3) / 1e12
-        kernels["K4_cnn"] = {"bound": "tensor", "achieved": cnn_tflops, "peak": tf_peak, "unit": "TFLOP/s",
-                             "frac": cnn_tflops / tf_peak, "ms_per_step": c_ms / args.steps,
-                             "images_per_step": L, "dtype": "bf16 x bf16 -> f32 (tcgen05)"}
-        policy = {"metric": "softtreemax_policy_evals_per_sec", "value": world * R * args.steps / (ms_policy / 1e3),
+        cnn_tflops = L * args.steps * (18685952 + 1024 * (A + 1)) / (c_ms / 1e3) / 1e12 if c_ms > 0 else 0.0
+        if not args.no_policy:
+            kernels["K4_cnn"] = {"bound": "tensor", "achieved": cnn_tflops, "peak": tf_peak, "unit": "TFLOP/s",
+                                 "frac": cnn_tflops / tf_peak, "ms_per_step": c_ms / args.steps,
+                                 "images_per_step": L, "dtype": "bf16 x bf16 -> f32 (tcgen05)"}
+        policy = None if args.no_policy else {"metric": "softtreemax_policy_evals_per_sec", "value": world * R * args.steps / (ms_policy / 1e3),
                   "unit": "evals/s", "ms_per_step": ms_policy / args.steps,
                   "leaves_per_sec_through_cnn": world * L * args.steps / (ms_policy / 1e3),
                   "pipelined": {"value": world * R * args.steps / (ms_pipe / 1e3), "unit": "evals/s",
@@ -395,7 +416,7 @@ def main():
                           "h2d_bytes_per_step": int(hs_pin.numel() + hk_pin.numel()), "d2h_bytes_per_step": int(R * (A + 1) * 4),
                           "api": "pinned host roots -> stm_bfs + stm_cnn_forward + stm_logits_fwd -> host logits, values"},
                   "what": "bfs + NatureCNN (K4) on R*A^d leaves and R roots + SoftTreeMax logits (K5); random-init SB3-style weights"}
-        cpu_rate, cpu_leaves, cpu_dt = cpu_oracle_rate(depth, args.cpu_seconds, os.cpu_count() or 1)
+        cpu_rate, cpu_leaves, cpu_dt = cpu_oracle_rate(depth, args.cpu_seconds, os.cpu_count() or 1, game=args.game)
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
                 "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
                 "dtype": "u8", "data": "synthetic", "config": workload_config(args),
