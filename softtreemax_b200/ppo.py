@@ -8,6 +8,8 @@ Adam(eps=1e-5) with linearly decayed learning rate and clip range, gradient-norm
 import numpy as np
 import torch as th
 
+from . import shard
+
 
 def get_linear_fn(start, end, end_fraction):
     """SB3's schedule: value as a function of progress_remaining (1 -> 0)."""
@@ -91,6 +93,7 @@ class PPO:
                 loss = pg + self.ent_coef * ent + self.vf_coef * vl
                 pol.optimizer.zero_grad()
                 loss.backward()
+                shard.allreduce_gradients(pol.parameters())      # data-parallel ranks (no-op on one process)
                 th.nn.utils.clip_grad_norm_(pol.parameters(), self.max_grad_norm)
                 pol.optimizer.step()
                 stats.append((float(loss), float(pg), float(vl), float(-ent)))

@@ -43,3 +43,35 @@ def max_over_ranks(values, device, group=None):
 def whole_job_rate(units_per_rank, world, ms):
     """value = units all ranks processed / the slowest rank's time (weak scaling)."""
     return world * units_per_rank / (ms / 1e3)
+
+
+def allreduce_gradients(parameters, group=None):
+    """Average the gradients of a data-parallel PPO minibatch over ranks (one fp32 sum over
+    the ~1.69 M-parameter gradient + beta/alpha per minibatch).  All gradients travel in ONE flat
+    bucket (6.7 MB: a single NCCL ring/NVLS launch), parameters without a gradient contribute zeros
+    so that every rank reduces the same layout."""
+    if not dist.is_initialized() or dist.get_world_size(group) == 1:
+        return
+    params = [p for p in parameters if p.requires_grad]
+    if not params:
+        return
+    flat = torch.cat([(p.grad if p.grad is not None else torch.zeros_like(p)).reshape(-1).float() for p in params])
+    dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=group)
+    flat /= dist.get_world_size(group)
+    off = 0
+    for p in params:
+        n = p.numel()
+        g = flat[off:off + n].reshape(p.shape).to(p.dtype)
+        if p.grad is None:
+            p.grad = g.clone()
+        else:
+            p.grad.copy_(g)
+        off += n
+
+
+def broadcast_parameters(parameters, src=0, group=None):
+    """Make every rank start from rank `src`'s weights (called once before training)."""
+    if not dist.is_initialized() or dist.get_world_size(group) == 1:
+        return
+    for p in parameters:
+        dist.broadcast(p.data, src=src, group=group)

@@ -40,3 +40,41 @@ def _worker(rank, world, port, n_roots, A):
 def test_gather_and_timing_over_gloo(world, n_roots):
     port = 29600 + world * 10 + n_roots
     mp.spawn(_worker, args=(world, port, n_roots, 5), nprocs=world, join=True)
+
+
+def _grad_worker(rank, world, port):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        torch.manual_seed(rank)                                  # different initial weights per rank
+        net = torch.nn.Sequential(torch.nn.Linear(6, 5), torch.nn.ReLU(), torch.nn.Linear(5, 3))
+        beta = torch.nn.Parameter(torch.tensor(1.0 + rank))
+        unused = torch.nn.Parameter(torch.zeros(4))              # never gets a gradient on rank 1
+        params = list(net.parameters()) + [beta, unused]
+        shard.broadcast_parameters(params)
+        ref = torch.nn.Sequential(torch.nn.Linear(6, 5), torch.nn.ReLU(), torch.nn.Linear(5, 3))
+        torch.manual_seed(0)
+        ref0 = torch.nn.Sequential(torch.nn.Linear(6, 5), torch.nn.ReLU(), torch.nn.Linear(5, 3))
+        for a, b in zip(net.parameters(), ref0.parameters()):
+            assert torch.equal(a, b), "broadcast must give every rank rank 0's weights"
+        assert float(beta) == 1.0
+        del ref
+        # every rank: its own minibatch; the averaged gradient must equal the full-batch mean gradient
+        g = torch.Generator().manual_seed(77)
+        x_all, y_all = torch.randn(world * 4, 6, generator=g), torch.randn(world * 4, 3, generator=g)
+        x, y = x_all[rank * 4:(rank + 1) * 4], y_all[rank * 4:(rank + 1) * 4]
+        loss = ((net(x) * beta - y) ** 2).mean() + (unused.sum() if rank == 0 else 0.0)
+        loss.backward()
+        shard.allreduce_gradients(params)
+        full = ((ref0(x_all) * 1.0 - y_all) ** 2).mean()
+        want = torch.autograd.grad(full, list(ref0.parameters()))
+        for p, w in zip(net.parameters(), want):
+            assert torch.allclose(p.grad, w, atol=1e-6), f"rank {rank}: averaged gradient"
+        assert torch.allclose(unused.grad, torch.full((4,), 1.0 / world))
+        dist.barrier()
+    finally:
+        dist.destroy_process_group()
+
+
+def test_gradient_allreduce_matches_full_batch_over_gloo():
+    mp.spawn(_grad_worker, args=(2, 29688), nprocs=2, join=True)
