@@ -28,6 +28,7 @@
 // for the life of the CTA; only fc (3.2 MB) streams its W slices through the ring.
 #include <cuda_runtime.h>
 #include <cuda_bf16.h>
+#include <cuda_fp16.h>
 #include <stdint.h>
 #include <new>
 #include <cstdlib>
@@ -57,6 +58,7 @@ struct LayerGeom {
     int relu;
     int out_f32;     // 1: fp32 output with row stride n_real; 0: bf16 output with row stride N
     float scale;     // multiplies the accumulator before the bias (1/255 for conv1)
+    int f16;         // 1: A and B operands are fp16 (conv1: u8 pixels are exact in fp16 and cheap to make), 0: bf16
     int debug;       // timing experiments only: bit0 producers skip loads, bit1 MMA thread skips the MMAs, bit2 epilogue skips stores
 };
 
@@ -92,10 +94,11 @@ __device__ __forceinline__ uint64_t make_desc(uint32_t saddr)
     return d;
 }
 __device__ __forceinline__ uint32_t swz(uint32_t row, uint32_t piece) { return row * 128u + ((piece ^ (row & 7u)) << 4); }
-// instruction descriptor, kind::f16: D = f32, A = B = bf16, both K-major, M = 128
-__device__ __forceinline__ uint32_t make_idesc(int N)
+// instruction descriptor, kind::f16: D = f32, A and B both bf16 (format 1) or both fp16 (format 0), K-major, M = 128
+__device__ __forceinline__ uint32_t make_idesc(int N, int f16)
 {
-    return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(kTileM >> 4) << 24);
+    const uint32_t fmt = f16 ? 0u : ((1u << 7) | (1u << 10));
+    return (1u << 4) | fmt | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(kTileM >> 4) << 24);
 }
 __device__ __forceinline__ void umma(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate)
 {
@@ -111,16 +114,20 @@ __device__ __forceinline__ void umma_commit(uint64_t *bar)
                  :: "r"(smem_u32(bar)) : "memory");
 }
 
-// pack 8 u8 (two words) into 8 bf16 (exact: 0..255 are representable)
-__device__ __forceinline__ uint4 u8x8_to_bf16x8(uint32_t lo, uint32_t hi)
+// 8 u8 (two words) -> 8 fp16, exact, on the integer / half2 pipes only (no I2F: the conversion unit runs at a
+// quarter of the ALU rate and was conv1's limiter): byte b under a 0x64 high byte is the fp16 number 1024 + b;
+// subtracting 1024 leaves b.
+__device__ __forceinline__ uint4 u8x8_to_f16x8(uint32_t lo, uint32_t hi)
 {
-    auto two = [](uint32_t a, uint32_t b) -> uint32_t {
-        __nv_bfloat162 v = __floats2bfloat162_rn((float)a, (float)b);
-        return *reinterpret_cast<uint32_t *>(&v);
+    const __half2 k1024 = __half2half2(__ushort_as_half((unsigned short)0x6400));
+    auto two = [&](uint32_t w, uint32_t sel) -> uint32_t {
+        uint32_t biased = __byte_perm(w, 0x64646464u, sel);
+        __half2 h = __hsub2(*reinterpret_cast<__half2 *>(&biased), k1024);
+        return *reinterpret_cast<uint32_t *>(&h);
     };
     uint4 r;
-    r.x = two(lo & 0xFF, (lo >> 8) & 0xFF);  r.y = two((lo >> 16) & 0xFF, lo >> 24);
-    r.z = two(hi & 0xFF, (hi >> 8) & 0xFF);  r.w = two((hi >> 16) & 0xFF, hi >> 24);
+    r.x = two(lo, 0x5140); r.y = two(lo, 0x7362);
+    r.z = two(hi, 0x5140); r.w = two(hi, 0x7362);
     return r;
 }
 
@@ -234,7 +241,7 @@ stm_cnn_gemm_kernel(const void *__restrict__ in, const __nv_bfloat16 *__restrict
             }
         }
     } else if (warp < 4) {
-        // ===================== producers, u8 NCHW input (conv1): registers, converted to bf16 =====================
+        // ===================== producers, u8 NCHW input (conv1): registers, converted to fp16 =====================
         uint32_t it = 0;
         for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
             const long long m = tile * kTileM + tid;
@@ -263,7 +270,7 @@ stm_cnn_gemm_kernel(const void *__restrict__ in, const __nv_bfloat16 *__restrict
                 uint8_t *abase = sA + st * kABytes;
                 #pragma unroll
                 for (int kg = 0; kg < 8; kg++)
-                    *reinterpret_cast<uint4 *>(abase + swz((uint32_t)tid, (uint32_t)kg)) = u8x8_to_bf16x8(cur[kg].x, cur[kg].y);
+                    *reinterpret_cast<uint4 *>(abase + swz((uint32_t)tid, (uint32_t)kg)) = u8x8_to_f16x8(cur[kg].x, cur[kg].y);
                 asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
                 mbar_arrive(&full[st]);
             }
@@ -271,7 +278,7 @@ stm_cnn_gemm_kernel(const void *__restrict__ in, const __nv_bfloat16 *__restrict
     } else if (warp == 8) {
         // ===================== MMA issuer =====================
         if ((tid & 31) == 0) {
-            const uint32_t idesc = make_idesc(N);
+            const uint32_t idesc = make_idesc(N, g.f16);
             uint32_t it = 0, t = 0;
             for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x, t++) {
                 const uint32_t buf = t & 1;
@@ -354,7 +361,7 @@ stm_cnn_gemm_kernel(const void *__restrict__ in, const __nv_bfloat16 *__restrict
 // to N rows, tiled per 64-wide K slice in the 128-byte-swizzled K-major layout the kernel uses:
 //   element (n, k): slice k/64, byte offset n*128 + ((((k%64)/8) ^ (n%8)) * 16) + (k%8)*2
 __global__ void stm_tile_weights_kernel(const float *__restrict__ w, __nv_bfloat16 *__restrict__ dst, int n_real, int N,
-                                        int K, int KHW, int C)
+                                        int K, int KHW, int C, int f16)
 {
     int idx = blockIdx.x * blockDim.x + threadIdx.x;
     if (idx >= N * K) return;
@@ -363,7 +370,8 @@ __global__ void stm_tile_weights_kernel(const float *__restrict__ w, __nv_bfloat
     float v = n < n_real ? w[(size_t)n * K + (size_t)c * KHW + s] : 0.f;
     int kc = k / 64, kk = k % 64;
     size_t off = (size_t)kc * N * 64 + (size_t)n * 64 + (((kk / 8) ^ (n % 8)) * 8) + (kk % 8);
-    dst[off] = __float2bfloat16_rn(v);
+    if (f16) reinterpret_cast<__half *>(dst)[off] = __float2half_rn(v);
+    else dst[off] = __float2bfloat16_rn(v);
 }
 
 struct CnnState {
@@ -440,7 +448,7 @@ int stm_cnn_set_weights(stm_ctx *ctx, const float *conv1_w, const float *conv1_b
             return stm_internal_fail(ctx, STM_ERR_NOMEM, "stm_cnn_set_weights: cudaMalloc");
         int total = spec[i].N * spec[i].K;
         stm_tile_weights_kernel<<<(total + 255) / 256, 256, 0, st>>>(spec[i].w, s->w[i], spec[i].n_real, spec[i].N,
-                                                                    spec[i].K, spec[i].KHW, spec[i].C);
+                                                                    spec[i].K, spec[i].KHW, spec[i].C, i == 0 ? 1 : 0);
         stm_internal_count_launch(ctx);
         cudaMemcpyAsync(s->b[i], spec[i].b, (size_t)spec[i].n_real * 4, cudaMemcpyDeviceToDevice, st);
     }
@@ -455,7 +463,7 @@ int stm_cnn_set_weights(stm_ctx *ctx, const float *conv1_w, const float *conv1_b
     cudaMemcpyAsync(tmp + (size_t)n_actions * 512, value_w, 512 * 4, cudaMemcpyDeviceToDevice, st);
     cudaMemcpyAsync(s->b[4], action_b, (size_t)n_actions * 4, cudaMemcpyDeviceToDevice, st);
     cudaMemcpyAsync(s->b[4] + n_actions, value_b, 4, cudaMemcpyDeviceToDevice, st);
-    stm_tile_weights_kernel<<<(32 * 512 + 255) / 256, 256, 0, st>>>(tmp, s->w[4], n_actions + 1, 32, 512, 1, 512);
+    stm_tile_weights_kernel<<<(32 * 512 + 255) / 256, 256, 0, st>>>(tmp, s->w[4], n_actions + 1, 32, 512, 1, 512, 0);
     stm_internal_count_launch(ctx);
     cudaStreamSynchronize(st);
     cudaFree(tmp);
@@ -486,16 +494,16 @@ int stm_cnn_forward(stm_ctx *ctx, const uint8_t *obs, long long n, float *heads,
     for (long long i0 = 0; i0 < n; i0 += chunk) {
         long long c = n - i0 < chunk ? n - i0 : chunk;
         int rc;
-        LayerGeom g1 = { MODE_CONV1, 400, 20, 84, 84, 4, 0, 4, 256, 32, 1, 0, 1.0f / 255.0f, dbg };
+        LayerGeom g1 = { MODE_CONV1, 400, 20, 84, 84, 4, 0, 4, 256, 32, 1, 0, 1.0f / 255.0f, 1, dbg };
         if ((rc = launch_layer<32, true, 4>(ctx, obs + (size_t)i0 * 4 * 84 * 84, s->w[0], s->b[0], s->act1, c * 400, g1, 0, 32, st))) return rc;
-        LayerGeom g2 = { MODE_NHWC, 81, 9, 20, 20, 32, 4 * 32, 2, 512, 64, 1, 0, 1.0f, dbg };
+        LayerGeom g2 = { MODE_NHWC, 81, 9, 20, 20, 32, 4 * 32, 2, 512, 64, 1, 0, 1.0f, 0, dbg };
         if ((rc = launch_layer<64, true, 8>(ctx, s->act1, s->w[1], s->b[1], s->act2, c * 81, g2, 0, 64, st))) return rc;
-        LayerGeom g3 = { MODE_NHWC, 49, 7, 9, 9, 64, 3 * 64, 1, 576, 64, 1, 0, 1.0f, dbg };
+        LayerGeom g3 = { MODE_NHWC, 49, 7, 9, 9, 64, 3 * 64, 1, 576, 64, 1, 0, 1.0f, 0, dbg };
         if ((rc = launch_layer<64, true, 8>(ctx, s->act2, s->w[2], s->b[2], s->act3, c * 49, g3, 0, 64, st))) return rc;
-        LayerGeom g4 = { MODE_NHWC, 1, 1, 1, 1, 3136, 3136, 1, 3136, 512, 1, 0, 1.0f, dbg };
+        LayerGeom g4 = { MODE_NHWC, 1, 1, 1, 1, 3136, 3136, 1, 3136, 512, 1, 0, 1.0f, 0, dbg };
         for (int half = 0; half < 2; half++)
             if ((rc = launch_layer<256, false, 4>(ctx, s->act3, s->w[3], s->b[3], s->feat, c, g4, half * 256, 512, st))) return rc;
-        LayerGeom g5 = { MODE_NHWC, 1, 1, 1, 1, 512, 512, 1, 512, A1, 0, 1, 1.0f, dbg };
+        LayerGeom g5 = { MODE_NHWC, 1, 1, 1, 1, 512, 512, 1, 512, A1, 0, 1, 1.0f, 0, dbg };
         if ((rc = launch_layer<32, true, 4>(ctx, s->feat, s->w[4], s->b[4], heads + (size_t)i0 * A1, c, g5, 0, 32, st))) return rc;
     }
     return STM_OK;
