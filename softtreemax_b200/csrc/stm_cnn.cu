@@ -58,8 +58,9 @@ struct LayerGeom {
     int relu;
     int out_f32;     // 1: fp32 output with row stride n_real; 0: bf16 output with row stride N
     float scale;     // multiplies the accumulator before the bias (1/255 for conv1)
+    int recip_ow;    // ceil(65536 / OW): pos / OW == (pos * recip_ow) >> 16 for every pos < P (checked by the host)
     int f16;         // 1: A and B operands are fp16 (conv1: u8 pixels are exact in fp16 and cheap to make), 0: bf16
-    int debug;       // timing experiments only: bit0 producers skip loads, bit1 MMA thread skips the MMAs, bit2 epilogue skips stores
+    int debug;       // timing experiments only: bit0 producers skip loads, bit1 MMA thread skips the MMAs, bit2 epilogue skips stores, bit3 conv1 only, bit4 conv1 producers skip convert+store, bit5 epilogue skips the TMEM loads
 };
 
 __device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -131,14 +132,16 @@ __device__ __forceinline__ uint4 u8x8_to_f16x8(uint32_t lo, uint32_t hi)
     return r;
 }
 
-constexpr int kProducerThreads = 128, kEpilogueThreads = 128;
-constexpr int kThreads2 = kProducerThreads + kEpilogueThreads + 32;      // + the MMA warp
+constexpr int kEpilogueThreads = 128;
+// threads of a CTA with kProdWarps producer warps: producers, 4 epilogue warps, the MMA warp.  The epilogue
+// warps must sit at warp indices = 0..3 mod 4 (a warp reads the TMEM lanes 32 * (warp % 4) ...), so kProdWarps % 4 == 0.
+__host__ __device__ constexpr int cta_threads(int prod_warps) { return prod_warps * 32 + kEpilogueThreads + 32; }
 
 __device__ __forceinline__ void mbar_arrive(uint64_t *bar)
 { asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" :: "r"(smem_u32(bar)) : "memory"); }
 
-template <int N, bool kResidentW, int kStages>
-__global__ void __launch_bounds__(kThreads2, 2)
+template <int N, bool kResidentW, int kStages, int kProdWarps>
+__global__ void __launch_bounds__(cta_threads(kProdWarps), 2)
 stm_cnn_gemm_kernel(const void *__restrict__ in, const __nv_bfloat16 *__restrict__ wt, const float *__restrict__ bias,
                     void *__restrict__ out, long long M_total, LayerGeom g, int n_off, int N_total)
 {
@@ -149,19 +152,21 @@ stm_cnn_gemm_kernel(const void *__restrict__ in, const __nv_bfloat16 *__restrict
     uint8_t *sB = smem + kStages * kABytes;               // resident: nchunks x kBBytes; streamed: kStages x kBBytes
     __shared__ __align__(8) uint64_t full[kStages], empty[kStages], tfull[2], tempty[2];
     __shared__ uint32_t tmem_base_s;
+    static_assert(kProdWarps % 4 == 0, "epilogue warps must start at a multiple of 4");
+    constexpr int kProducerThreads = kProdWarps * 32, kThreads2 = cta_threads(kProdWarps), kMmaWarp = kProdWarps + 4;
     const int tid = threadIdx.x, warp = tid >> 5;
     const int nchunks = g.K / kChunkK;
     const long long ntiles = (M_total + kTileM - 1) / kTileM;
     constexpr uint32_t kCols = (2 * N < 32) ? 32 : 2 * N;             // two accumulators
 
-    if (warp == 8) {
+    if (warp == kMmaWarp) {
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;"
                      :: "r"(smem_u32(&tmem_base_s)), "r"(kCols) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     }
     if (tid == 0) {
-        for (int i = 0; i < kStages; i++) { mbar_init(&full[i], kProducerThreads); mbar_init(&empty[i], 1); }
-        for (int i = 0; i < 2; i++) { mbar_init(&tfull[i], 1); mbar_init(&tempty[i], kEpilogueThreads); }
+        for (int i = 0; i < kStages; i++) { mbar_init(&full[i], kProducerThreads / 32); mbar_init(&empty[i], 1); }
+        for (int i = 0; i < 2; i++) { mbar_init(&tfull[i], 1); mbar_init(&tempty[i], kEpilogueThreads / 32); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (kResidentW) {
@@ -178,7 +183,7 @@ stm_cnn_gemm_kernel(const void *__restrict__ in, const __nv_bfloat16 *__restrict
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     const uint32_t tmem_base = tmem_base_s;
 
-    if (warp < 4 && g.mode != MODE_CONV1) {
+    if (warp < kProdWarps && g.mode != MODE_CONV1) {
         // ===================== producers, bf16 NHWC input: cp.async, kDepth slices in flight =====================
         // The stream of (tile, k-slice) work items is issued kDepth items ahead of the one being
         // published: 16-byte cp.async copies land straight in the ring (no registers), and an item is
@@ -186,39 +191,45 @@ stm_cnn_gemm_kernel(const void *__restrict__ in, const __nv_bfloat16 *__restrict
         constexpr int kDepth = kStages - 1;
         // eight consecutive lanes fetch the eight 16-byte pieces of one row's 128-byte K slice: every
         // warp-level copy touches four whole lines of global memory and four whole lines of shared memory
-        const uint32_t piece = (uint32_t)tid & 7u, row0 = (uint32_t)tid >> 3;          // rows row0 + 16 j
-        const long long my_tiles = blockIdx.x < ntiles ? (ntiles - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
-        const long long items = my_tiles * nchunks;
-        long long tile = blockIdx.x;
+        constexpr int kRowsPerPass = kProducerThreads / 8, kPasses = kTileM / kRowsPerPass;
+        const uint32_t piece = (uint32_t)tid & 7u, row0 = (uint32_t)tid >> 3;          // rows row0 + kRowsPerPass j
+        // All index arithmetic is 32-bit (M_total < 2^31 is checked by the host) and incremental: one division
+        // per tile, not two 64-bit ones per row — the address generation, not the copies, was the producers' cost.
+        const uint32_t Mt = (uint32_t)M_total, P = (uint32_t)g.P, OW = (uint32_t)g.OW, rOW = (uint32_t)g.recip_ow;
+        const int my_tiles = (long long)blockIdx.x < ntiles ? (int)((ntiles - blockIdx.x + gridDim.x - 1) / gridDim.x) : 0;
+        const int items = my_tiles * nchunks;
+        uint32_t tile = blockIdx.x;
         int kc = 0;
-        const uint8_t *rowp[8];
-        uint32_t okmask = 0;
-        for (long long i = 0; i < items + kDepth; i++) {
+        const uint8_t *rowp[kPasses];
+        uint32_t okmask = 0, st = 0, ph = 0, st_pub = 0;
+        for (int i = 0; i < items + kDepth; i++) {
             if (i < items) {
                 if (kc == 0) {
                     okmask = 0;
+                    uint32_t m = tile * kTileM + row0;
+                    uint32_t img = m / P, pos = m - img * P;
                     #pragma unroll
-                    for (int j = 0; j < 8; j++) {
-                        const long long m = tile * kTileM + row0 + 16 * j;
-                        const bool ok = m < M_total;
-                        const long long img = ok ? m / g.P : 0;
-                        const int pos = ok ? (int)(m % g.P) : 0;
-                        const int oy = pos / g.OW, ox = pos % g.OW;
-                        rowp[j] = reinterpret_cast<const uint8_t *>(reinterpret_cast<const __nv_bfloat16 *>(in)
-                                  + (((size_t)img * g.IH + oy * g.S) * g.IW + ox * g.S) * g.C) + piece * 16;
+                    for (int j = 0; j < kPasses; j++) {
+                        const bool ok = m < Mt;
+                        const uint32_t oy = (pos * rOW) >> 16, ox = pos - oy * OW;
+                        rowp[j] = reinterpret_cast<const uint8_t *>(in)
+                                  + ((size_t)img * (uint32_t)(g.IH * g.IW) + (oy * (uint32_t)g.IW + ox) * (uint32_t)g.S) * (uint32_t)(g.C * 2)
+                                  + piece * 16;
                         okmask |= (ok ? 1u : 0u) << j;
+                        m += kRowsPerPass;
+                        if (P == 1) img += kRowsPerPass;
+                        else { pos += kRowsPerPass; if (pos >= P) { pos -= P; img++; } }
                     }
                 }
-                const uint32_t st = (uint32_t)(i % kStages), ph = (uint32_t)((i / kStages) & 1);
                 mbar_wait(&empty[st], ph ^ 1);
                 const int k0 = kc * kChunkK;
                 const int kh = k0 / g.KWC, koff = k0 - kh * g.KWC;
-                const size_t goff = ((size_t)kh * g.IW * g.C + koff) * 2;
+                const uint32_t goff = (uint32_t)((kh * g.IW * g.C + koff) * 2);
                 const uint32_t dst0 = smem_u32(sA + st * kABytes);
                 if (!(g.debug & 1)) {
                 #pragma unroll
-                for (int j = 0; j < 8; j++) {
-                    const uint32_t r = row0 + 16 * j;
+                for (int j = 0; j < kPasses; j++) {
+                    const uint32_t r = row0 + kRowsPerPass * j;
                     const uint32_t nbytes = (okmask >> j) & 1u ? 16u : 0u;         // 0 => zero fill
                     asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;"
                                  :: "r"(dst0 + swz(r, piece)), "l"(rowp[j] + goff), "r"(nbytes) : "memory");
@@ -232,50 +243,86 @@ stm_cnn_gemm_kernel(const void *__restrict__ in, const __nv_bfloat16 *__restrict
                         asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" :: "r"(wdst + j * 16), "l"(wsrc + (size_t)j * 16) : "memory");
                 }
                 if (++kc == nchunks) { kc = 0; tile += gridDim.x; }
+                if (++st == kStages) { st = 0; ph ^= 1; }
             }
             asm volatile("cp.async.commit_group;" ::: "memory");              // (an empty group past the end keeps the count regular)
             if (i >= kDepth) {
                 asm volatile("cp.async.wait_group %0;" :: "n"(kDepth) : "memory");
                 asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-                mbar_arrive(&full[(i - kDepth) % kStages]);
+                __syncwarp();                                             // every lane's copies are fenced: one arrival per warp
+                if ((tid & 31) == 0) mbar_arrive(&full[st_pub]);
+                if (++st_pub == kStages) st_pub = 0;
             }
         }
-    } else if (warp < 4) {
-        // ===================== producers, u8 NCHW input (conv1): registers, converted to fp16 =====================
-        uint32_t it = 0;
-        for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
-            const long long m = tile * kTileM + tid;
-            const bool row_ok = m < M_total;
-            const long long img = row_ok ? m / g.P : 0;
-            const int pos = row_ok ? (int)(m % g.P) : 0;
-            const int oy = pos / g.OW, ox = pos % g.OW;
-            const uint8_t *src8 = reinterpret_cast<const uint8_t *>(in) + (size_t)img * g.C * g.IH * g.IW
-                                  + (size_t)(oy * g.S) * g.IW + ox * g.S;
-            uint2 cur[8], nxt[8];
-            auto load = [&](int kc, uint2 *r) {
-                const uint8_t *p8 = src8 + (size_t)kc * g.IH * g.IW;
-                #pragma unroll
-                for (int kg = 0; kg < 8; kg++) {
-                    const uint32_t *p = reinterpret_cast<const uint32_t *>(p8 + kg * g.IW);
-                    r[kg].x = row_ok ? __ldg(p) : 0u; r[kg].y = row_ok ? __ldg(p + 1) : 0u;
+    } else if (warp < kProdWarps) {
+        // ===================== producers, u8 NCHW input (conv1): cp.async staging, converted to fp16 =====================
+        // kSplit threads share a row of the tile: thread t owns row t % 128 and the patch rows
+        // [8 / kSplit * (t / 128), ...) of it, so one warp still covers 32 consecutive rows (coalesced gather)
+        // and the per-thread work shrinks with the number of producer warps (the gather is bound by the
+        // instruction latency of its producer warps, not by bytes).  The raw bytes of a thread's share of the
+        // patch in one channel are fetched as 4-byte cp.async copies into a PRIVATE slot of a small raw ring
+        // (word-major: copies and read-back are bank-conflict free); kRaw - 1 slices stay in flight per thread
+        // without holding registers.  A landed slice is read back, widened to fp16 and written to the swizzled
+        // operand ring.  No barrier guards the raw ring: nobody but its owner touches a thread's words.
+        constexpr int kRaw = 3, kSplit = kProducerThreads / kTileM, kMyRows = 8 / kSplit;     // patch rows per thread
+        static_assert(kProducerThreads % kTileM == 0 && 8 % kSplit == 0, "whole rows per producer thread");
+        uint32_t *raw = reinterpret_cast<uint32_t *>(sB + (size_t)nchunks * kBBytes);          // [kRaw][16][128]
+        const int row = tid % kTileM, kg0 = (tid / kTileM) * kMyRows;
+        const uint32_t Mt = (uint32_t)M_total, P = (uint32_t)g.P, OW = (uint32_t)g.OW, rOW = (uint32_t)g.recip_ow;
+        const int my_tiles = (long long)blockIdx.x < ntiles ? (int)((ntiles - blockIdx.x + gridDim.x - 1) / gridDim.x) : 0;
+        const int items = my_tiles * nchunks;
+        uint32_t tile = blockIdx.x;
+        int kc = 0;
+        const uint8_t *src8 = reinterpret_cast<const uint8_t *>(in);
+        uint32_t nbytes = 0, slot_w = 0, slot_r = 0, st = 0, ph = 0;
+        for (int i = 0; i < items + (kRaw - 1); i++) {
+            if (i < items) {
+                if (kc == 0) {
+                    const uint32_t m = tile * kTileM + row;
+                    const bool row_ok = m < Mt;
+                    const uint32_t img = row_ok ? m / P : 0u;
+                    const uint32_t pos = row_ok ? m - img * P : 0u;
+                    const uint32_t oy = (pos * rOW) >> 16, ox = pos - oy * OW;
+                    src8 = reinterpret_cast<const uint8_t *>(in) + (size_t)img * (uint32_t)(g.C * g.IH * g.IW)
+                           + (oy * (uint32_t)g.S + kg0) * (uint32_t)g.IW + ox * (uint32_t)g.S;
+                    nbytes = row_ok ? 4u : 0u;                          // 0 => zero fill
                 }
-            };
-            load(0, nxt);
-            for (int kc = 0; kc < nchunks; kc++, it++) {
+                const uint8_t *p8 = src8 + (uint32_t)(kc * g.IH * g.IW);
+                const uint32_t dst = smem_u32(raw + (size_t)slot_w * 16 * kTileM + (size_t)(2 * kg0) * kTileM + row);
+                if (!(g.debug & 1)) {
                 #pragma unroll
-                for (int kg = 0; kg < 8; kg++) cur[kg] = nxt[kg];
-                if (kc + 1 < nchunks) load(kc + 1, nxt);
-                const uint32_t st = it % kStages, ph = (it / kStages) & 1;
+                for (int kg = 0; kg < kMyRows; kg++) {
+                    asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;"
+                                 :: "r"(dst + (2 * kg) * kTileM * 4), "l"(p8 + kg * g.IW), "r"(nbytes) : "memory");
+                    asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;"
+                                 :: "r"(dst + (2 * kg + 1) * kTileM * 4), "l"(p8 + kg * g.IW + 4), "r"(nbytes) : "memory");
+                }
+                }
+                if (++kc == nchunks) { kc = 0; tile += gridDim.x; }
+                if (++slot_w == kRaw) slot_w = 0;
+            }
+            asm volatile("cp.async.commit_group;" ::: "memory");
+            if (i >= kRaw - 1) {
+                asm volatile("cp.async.wait_group %0;" :: "n"(kRaw - 1) : "memory");
+                const uint32_t *rs = raw + (size_t)slot_r * 16 * kTileM + (size_t)(2 * kg0) * kTileM + row;
+                uint32_t wv[2 * kMyRows];
+                #pragma unroll
+                for (int q = 0; q < 2 * kMyRows; q++) wv[q] = rs[q * kTileM];
                 mbar_wait(&empty[st], ph ^ 1);                      // slot free (first pass: returns at once)
                 uint8_t *abase = sA + st * kABytes;
+                if (!(g.debug & 16)) {
                 #pragma unroll
-                for (int kg = 0; kg < 8; kg++)
-                    *reinterpret_cast<uint4 *>(abase + swz((uint32_t)tid, (uint32_t)kg)) = u8x8_to_f16x8(cur[kg].x, cur[kg].y);
-                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-                mbar_arrive(&full[st]);
+                for (int kg = 0; kg < kMyRows; kg++)
+                    *reinterpret_cast<uint4 *>(abase + swz((uint32_t)row, (uint32_t)(kg0 + kg))) = u8x8_to_f16x8(wv[2 * kg], wv[2 * kg + 1]);
+                }
+                if (!(g.debug & 64)) asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                __syncwarp();
+                if ((tid & 31) == 0) mbar_arrive(&full[st]);
+                if (++slot_r == kRaw) slot_r = 0;
+                if (++st == kStages) { st = 0; ph ^= 1; }
             }
         }
-    } else if (warp == 8) {
+    } else if (warp == kMmaWarp) {
         // ===================== MMA issuer =====================
         if ((tid & 31) == 0) {
             const uint32_t idesc = make_idesc(N, g.f16);
@@ -296,8 +343,10 @@ stm_cnn_gemm_kernel(const void *__restrict__ in, const __nv_bfloat16 *__restrict
                     for (int j = 0; j < kChunkK / 16; j++)
                         umma(tmem_d, make_desc(a0 + j * 32), make_desc(b0 + j * 32), idesc, (kc | j) ? 1u : 0u);
                     }
+                    if (g.debug & 128) mbar_arrive(&empty[st]); else
                     umma_commit(&empty[st]);                        // frees the slot when these MMAs are done
                 }
+                if (g.debug & 128) mbar_arrive(&tfull[buf]); else
                 umma_commit(&tfull[buf]);                           // accumulator complete
             }
         }
@@ -315,6 +364,7 @@ stm_cnn_gemm_kernel(const void *__restrict__ in, const __nv_bfloat16 *__restrict
             const uint32_t taddr = tmem_base + buf * N + ((uint32_t)(ew * 32) << 16);
             #pragma unroll 1
             for (int c0 = 0; c0 < N; c0 += 16) {
+                if (g.debug & 32) break;
                 uint32_t r[16];
                 asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 "
                              "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
@@ -348,12 +398,13 @@ stm_cnn_gemm_kernel(const void *__restrict__ in, const __nv_bfloat16 *__restrict
                 }
             }
             asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-            mbar_arrive(&tempty[buf]);
+            __syncwarp();
+            if ((tid & 31) == 0) mbar_arrive(&tempty[buf]);
         }
     }
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
-    if (warp == 8)
+    if (warp == kMmaWarp)
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" :: "r"(tmem_base), "r"(kCols) : "memory");
 }
 
@@ -382,22 +433,26 @@ struct CnnState {
     long long cap_images = 0;
 };
 
-template <int N, bool kResidentW, int kStages>
+template <int N, bool kResidentW, int kStages, int kProdWarps>
 int launch_layer(stm_ctx *ctx, const void *in, const __nv_bfloat16 *w, const float *b, void *out, long long M,
                  const LayerGeom &g, int n_off, int N_total, cudaStream_t st)
 {
     static bool attr_done = false;
     const int nchunks = g.K / kChunkK;
-    size_t smem = (size_t)kStages * kABytes + (size_t)(kResidentW ? nchunks : kStages) * N * kChunkK * 2 + 1024;
+    size_t smem = (size_t)kStages * kABytes + (size_t)(kResidentW ? nchunks : kStages) * N * kChunkK * 2 + 1024
+                  + (g.mode == MODE_CONV1 ? 3 * 16 * 128 * 4 : 0);     // conv1's raw-byte ring (kRaw slots)
     if (!attr_done) {
-        cudaFuncSetAttribute(stm_cnn_gemm_kernel<N, kResidentW, kStages>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 2048);
-        cudaFuncSetAttribute(stm_cnn_gemm_kernel<N, kResidentW, kStages>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+        cudaFuncSetAttribute(stm_cnn_gemm_kernel<N, kResidentW, kStages, kProdWarps>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 2048);
+        cudaFuncSetAttribute(stm_cnn_gemm_kernel<N, kResidentW, kStages, kProdWarps>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
         attr_done = true;
     }
+    if (M >= (1LL << 31) - kTileM) return stm_internal_fail(ctx, STM_ERR_ARG, "stm_cnn: too many rows for one pass");
+    for (int pos = 0; pos < g.P; pos++)
+        if (((pos * g.recip_ow) >> 16) != pos / g.OW) return stm_internal_fail(ctx, STM_ERR_ARG, "stm_cnn: reciprocal of OW is not exact");
     long long tiles = (M + kTileM - 1) / kTileM;
-    int per_sm = smem <= 100 * 1024 ? 2 : 1;                         // persistent: fill every SM, CTAs loop over tiles
+    int per_sm = smem <= 110 * 1024 ? 2 : 1;                         // persistent: fill every SM, CTAs loop over tiles
     long long grid = tiles < 148LL * per_sm ? tiles : 148LL * per_sm;
-    stm_cnn_gemm_kernel<N, kResidentW, kStages><<<(unsigned)grid, kThreads2, smem, st>>>(in, w, b, out, M, g, n_off, N_total);
+    stm_cnn_gemm_kernel<N, kResidentW, kStages, kProdWarps><<<(unsigned)grid, cta_threads(kProdWarps), smem, st>>>(in, w, b, out, M, g, n_off, N_total);
     stm_internal_count_launch(ctx);
     cudaError_t e = cudaGetLastError();
     return e == cudaSuccess ? STM_OK : stm_internal_fail(ctx, STM_ERR_CUDA, cudaGetErrorString(e));
@@ -494,17 +549,18 @@ int stm_cnn_forward(stm_ctx *ctx, const uint8_t *obs, long long n, float *heads,
     for (long long i0 = 0; i0 < n; i0 += chunk) {
         long long c = n - i0 < chunk ? n - i0 : chunk;
         int rc;
-        LayerGeom g1 = { MODE_CONV1, 400, 20, 84, 84, 4, 0, 4, 256, 32, 1, 0, 1.0f / 255.0f, 1, dbg };
-        if ((rc = launch_layer<32, true, 4>(ctx, obs + (size_t)i0 * 4 * 84 * 84, s->w[0], s->b[0], s->act1, c * 400, g1, 0, 32, st))) return rc;
-        LayerGeom g2 = { MODE_NHWC, 81, 9, 20, 20, 32, 4 * 32, 2, 512, 64, 1, 0, 1.0f, 0, dbg };
-        if ((rc = launch_layer<64, true, 8>(ctx, s->act1, s->w[1], s->b[1], s->act2, c * 81, g2, 0, 64, st))) return rc;
-        LayerGeom g3 = { MODE_NHWC, 49, 7, 9, 9, 64, 3 * 64, 1, 576, 64, 1, 0, 1.0f, 0, dbg };
-        if ((rc = launch_layer<64, true, 8>(ctx, s->act2, s->w[2], s->b[2], s->act3, c * 49, g3, 0, 64, st))) return rc;
-        LayerGeom g4 = { MODE_NHWC, 1, 1, 1, 1, 3136, 3136, 1, 3136, 512, 1, 0, 1.0f, 0, dbg };
+        LayerGeom g1 = { MODE_CONV1, 400, 20, 84, 84, 4, 0, 4, 256, 32, 1, 0, 1.0f / 255.0f, (65536 + 20 - 1) / 20, 1, dbg };
+        if ((rc = launch_layer<32, true, 4, 8>(ctx, obs + (size_t)i0 * 4 * 84 * 84, s->w[0], s->b[0], s->act1, c * 400, g1, 0, 32, st))) return rc;
+        if (dbg & 8) continue;                                       // timing experiments: conv1 alone
+        LayerGeom g2 = { MODE_NHWC, 81, 9, 20, 20, 32, 4 * 32, 2, 512, 64, 1, 0, 1.0f, (65536 + 9 - 1) / 9, 0, dbg };
+        if ((rc = launch_layer<64, true, 8, 4>(ctx, s->act1, s->w[1], s->b[1], s->act2, c * 81, g2, 0, 64, st))) return rc;
+        LayerGeom g3 = { MODE_NHWC, 49, 7, 9, 9, 64, 3 * 64, 1, 576, 64, 1, 0, 1.0f, (65536 + 7 - 1) / 7, 0, dbg };
+        if ((rc = launch_layer<64, true, 8, 4>(ctx, s->act2, s->w[2], s->b[2], s->act3, c * 49, g3, 0, 64, st))) return rc;
+        LayerGeom g4 = { MODE_NHWC, 1, 1, 1, 1, 3136, 3136, 1, 3136, 512, 1, 0, 1.0f, 65536, 0, dbg };
         for (int half = 0; half < 2; half++)
-            if ((rc = launch_layer<256, false, 4>(ctx, s->act3, s->w[3], s->b[3], s->feat, c, g4, half * 256, 512, st))) return rc;
-        LayerGeom g5 = { MODE_NHWC, 1, 1, 1, 1, 512, 512, 1, 512, A1, 0, 1, 1.0f, 0, dbg };
-        if ((rc = launch_layer<32, true, 4>(ctx, s->feat, s->w[4], s->b[4], heads + (size_t)i0 * A1, c, g5, 0, 32, st))) return rc;
+            if ((rc = launch_layer<256, false, 4, 4>(ctx, s->act3, s->w[3], s->b[3], s->feat, c, g4, half * 256, 512, st))) return rc;
+        LayerGeom g5 = { MODE_NHWC, 1, 1, 1, 1, 512, 512, 1, 512, A1, 0, 1, 1.0f, 65536, 0, dbg };
+        if ((rc = launch_layer<32, true, 4, 4>(ctx, s->feat, s->w[4], s->b[4], heads + (size_t)i0 * A1, c, g5, 0, 32, st))) return rc;
     }
     return STM_OK;
 }
