@@ -92,3 +92,78 @@ class CuleEnv:
 
     def close(self):
         pass
+
+
+class CuleEnvMultiple:
+    """Mirror of environments/cule_env_multiple.py:13-80 — the depth-0 arm: `n_envs` root environments
+    stepped together (K2 + K3 with R roots and no tree), SB3 VecEnv conventions (batched numpy in/out,
+    one info dict per env).  The stack of the last `n_frame_stack` observations lives on the GPU
+    (`self.env.stacks`, shifted by K3) instead of in a deque of tensors (:27,40-42,49,69-74).
+
+    An env whose episode ended is restarted on the next `step` from the power-on state + one no-op
+    step, with a zeroed stack.  (The reference never resets an env here: it relies on torchcule's
+    own restart of finished envs, which is not visible in the reference's sources.)
+    """
+
+    def __init__(self, device, env_kwargs, n_frame_stack=4, noop_max=30, clip_reward=True, fire_reset=True, n_envs=1):
+        if n_frame_stack != 4:
+            raise NotImplementedError("n_frame_stack = 4 (what main.py uses)")
+        self.device, self.env_kwargs, self.num_envs = device, env_kwargs, n_envs
+        actions = AtariRom(env_kwargs["env_name"]).minimal_actions()
+        self.env = AtariEnv(num_envs=n_envs, device="cuda:0" if str(device) in ("cpu", "auto") else device, **env_kwargs)
+        self.env.reset(initial_steps=1, verbose=1)
+        self._fresh = (self.env.blobs.clone(), self.env.lives.clone())        # power-on + 1 no-op, for restarts
+        self.lives = 0
+        self.n_frame_stack, self.training = n_frame_stack, True
+        self.noop_max, self.clip_reward, self.fire_reset = noop_max, clip_reward, fire_reset
+        self.reward_range = (-math.inf, math.inf)
+        self.metadata = {"render.modes": ["human", "rgb_array"]}
+        self.observation_space = _Space(shape=(n_frame_stack, 84, 84))
+        self.action_space = _Space(n=len(actions))
+        self.rng = np.random.RandomState(0)
+        self._ended = torch.zeros(n_envs, dtype=torch.bool, device=self.env.device)
+
+    def _stack(self):
+        return self.env.stacks.cpu().numpy()                                              # :50,74
+
+    def reset(self):                                                                        # :44-50
+        noops = self.rng.randint(self.noop_max + 1)
+        self.env.reset(initial_steps=noops, verbose=1)
+        self.env.stacks[:, :3] = 0                              # _reset_buffer(): three zero frames under the first observation
+        self.last_frame = self.env.stacks[:, 3]
+        self.lives = self.env.lives.cpu().numpy()
+        self._ended.zero_()
+        return self._stack()
+
+    def step(self, action):                                                                 # :52-74
+        env = self.env
+        if bool(self._ended.any()):
+            idx = self._ended.nonzero().reshape(-1)
+            env.blobs[idx] = self._fresh[0][idx]
+            env.lives[idx] = self._fresh[1][idx]
+            env.stacks[idx] = 0
+        obs, reward, done, info = env.step(torch.as_tensor(np.asarray(action)))
+        self._ended = done.clone()
+        lives = info["ale.lives"].cpu().numpy()
+        orig, done_np = reward.cpu().numpy(), done.cpu().numpy()
+        infos = [{"ale.lives": int(lives[i]), "orig_reward": orig[i], "done": done_np[i]} for i in range(self.num_envs)]
+        if self.clip_reward:
+            reward = torch.sign(reward)
+        self.last_frame = obs[:, :, :, 0]
+        self.lives = lives
+        return self._stack(), reward.cpu().numpy(), done.float().cpu().numpy(), infos
+
+    def train(self):
+        self.training = True
+
+    def eval(self):
+        self.training = False
+
+    def seed(self, seed=None):
+        self.rng = np.random.RandomState(seed)
+
+    def render(self):
+        raise NotImplementedError
+
+    def close(self):
+        pass

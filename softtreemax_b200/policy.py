@@ -72,6 +72,38 @@ class ActorCriticCnnPolicyDepth0(nn.Module):
                 break
             self.gradients_history.setdefault(name, []).append(param.grad.data.detach().clone())
 
+    # what SB3's ActorCriticCnnPolicy gives the depth-0 policy (forward / evaluate_actions / predict), batched
+    def _logits_values(self, obs):
+        feats = self.extract_features(th.as_tensor(obs).to(self.device))
+        return self.action_net(feats), self.value_net(feats)
+
+    def forward(self, obs, deterministic=False):
+        logits, values = self._logits_values(obs)
+        dist = th.distributions.Categorical(logits=logits)
+        actions = logits.argmax(dim=1) if deterministic else dist.sample()
+        return actions, values, dist.log_prob(actions)
+
+    def evaluate_actions(self, obs, actions):
+        self.add_gradients_history()
+        logits, values = self._logits_values(obs)
+        dist = th.distributions.Categorical(logits=logits)
+        return values, dist.log_prob(th.as_tensor(actions).to(self.device).reshape(-1)), dist.entropy()
+
+    def predict(self, obs, state=None, mask=None, deterministic=False):
+        with th.no_grad():
+            return self.forward(th.as_tensor(obs), deterministic)[0].cpu().numpy(), None
+
+    def save(self, path):                                                 # SB3 BasePolicy.save: constructor data + weights
+        th.save({"state_dict": self.state_dict(),
+                 "data": dict(observation_space=self.observation_space, action_space=self.action_space)}, path)
+
+    @classmethod
+    def load(cls, path, device="cuda:0", **_):                            # main.py:91
+        saved = th.load(path, map_location=device, weights_only=False)
+        model = cls(**saved["data"], lr_schedule=lambda _: 0.0, device=device)
+        model.load_state_dict(saved["state_dict"])
+        return model
+
     def kernel_params(self):
         sd = self.state_dict()
         m = {"cnn.0": "features_extractor.cnn.0", "cnn.2": "features_extractor.cnn.2", "cnn.4": "features_extractor.cnn.4",

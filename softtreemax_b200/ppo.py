@@ -70,6 +70,41 @@ class PPO:
         buf["adv"], buf["ret"] = adv, adv + buf["val"]
         return buf, obs, episode_start, ep_rewards
 
+    def _rollout_vec(self, obs, episode_start):
+        """Rollout over a vectorised env (`env.num_envs` envs that restart themselves: CuleEnvMultiple, the depth-0
+        arm).  Same buffer keys as _rollout, flattened to (n_steps * n_envs, ...)."""
+        n, N = self.n_steps, self.env.num_envs
+        buf = dict(obs=np.zeros((n, N, 4, 84, 84), np.uint8), act=np.zeros((n, N), np.int64), rew=np.zeros((n, N), np.float32),
+                   start=np.zeros((n, N), np.float32), val=np.zeros((n, N), np.float32), logp=np.zeros((n, N), np.float32))
+        ep_rewards = []
+        for t in range(n):
+            with th.no_grad():
+                a, v, lp = self.policy.forward(th.from_numpy(obs))
+            a = a.cpu().numpy()
+            buf["obs"][t], buf["act"][t], buf["start"][t] = obs, a, episode_start
+            buf["val"][t], buf["logp"][t] = v.reshape(-1).cpu().numpy(), lp.reshape(-1).cpu().numpy()
+            obs, r, done, infos = self.env.step(a)
+            buf["rew"][t] = r
+            self._ep_ret = self._ep_ret + np.array([float(i.get("orig_reward", x)) for i, x in zip(infos, r)], np.float64)
+            self.num_timesteps += N
+            episode_start = np.asarray(done, np.float32)
+            for i in np.nonzero(episode_start)[0]:
+                ep_rewards.append(float(self._ep_ret[i]))
+                self._ep_ret[i] = 0.0
+        with th.no_grad():
+            last_val = self.policy.forward(th.from_numpy(obs))[1].reshape(-1).cpu().numpy()
+        adv = np.zeros((n, N), np.float32)
+        gae = np.zeros(N, np.float32)
+        for t in reversed(range(n)):
+            nonterminal = 1.0 - (episode_start if t == n - 1 else buf["start"][t + 1])
+            next_val = last_val if t == n - 1 else buf["val"][t + 1]
+            delta = buf["rew"][t] + self.gamma * next_val * nonterminal - buf["val"][t]
+            gae = delta + self.gamma * self.gae_lambda * nonterminal * gae
+            adv[t] = gae
+        buf["adv"], buf["ret"] = adv, adv + buf["val"]
+        buf = {k: v.reshape((n * N,) + v.shape[2:]) for k, v in buf.items()}
+        return buf, obs, episode_start, ep_rewards
+
     def _train(self, buf, progress_remaining):
         pol = self.policy
         lr, clip = self.lr(progress_remaining), self.clip(progress_remaining)
@@ -78,8 +113,9 @@ class PPO:
         dev = pol.device
         stats = []
         for _ in range(self.n_epochs):
-            perm = self.rng.permutation(self.n_steps)
-            for s in range(0, self.n_steps, self.batch_size):
+            total = len(buf["act"])
+            perm = self.rng.permutation(total)
+            for s in range(0, total, self.batch_size):
                 idx = perm[s:s + self.batch_size]
                 obs = th.from_numpy(buf["obs"][idx]).float()
                 act = th.from_numpy(buf["act"][idx]).to(dev)
@@ -96,21 +132,59 @@ class PPO:
                 shard.allreduce_gradients(pol.parameters())      # data-parallel ranks (no-op on one process)
                 th.nn.utils.clip_grad_norm_(pol.parameters(), self.max_grad_norm)
                 pol.optimizer.step()
-                stats.append((float(loss), float(pg), float(vl), float(-ent)))
+                stats.append((float(loss.detach()), float(pg.detach()), float(vl.detach()), float(-ent.detach())))
         return np.mean(stats, axis=0)
 
     def learn(self, total_timesteps, callback=None):
+        vec = hasattr(self.env, "num_envs")
         obs = self.env.reset()
-        episode_start, self._ep_ret = True, 0.0
+        if vec:
+            episode_start, self._ep_ret = np.ones(self.env.num_envs, np.float32), np.zeros(self.env.num_envs, np.float64)
+        else:
+            episode_start, self._ep_ret = True, 0.0
         while self.num_timesteps < total_timesteps:
-            buf, obs, episode_start, ep = self._rollout(obs, episode_start)
+            buf, obs, episode_start, ep = (self._rollout_vec if vec else self._rollout)(obs, episode_start)
             st = self._train(buf, 1.0 - self.num_timesteps / total_timesteps)
             rec = dict(timesteps=self.num_timesteps, loss=st[0], pg_loss=st[1], value_loss=st[2], entropy=st[3],
                        episodes=len(ep), ep_reward_mean=float(np.mean(ep)) if ep else None,
-                       beta=float(self.policy.beta), alpha=float(self.policy.alpha))
+                       beta=float(getattr(self.policy, "beta", 1.0)), alpha=float(getattr(self.policy, "alpha", 1.0)))
             self.log.append(rec)
             if self.verbose:
                 print(rec, flush=True)
             if callback is not None:
                 callback(self, rec)
         return self
+
+
+def evaluate_policy(model, env, n_eval_episodes=10, deterministic=False, return_episode_rewards=False):
+    """stable_baselines3.common.evaluation.evaluate_policy for the two env kinds of this package (main.py:94-95):
+    runs `n_eval_episodes` episodes with model.policy.predict and returns the un-clipped episode scores and
+    lengths (or their mean / std)."""
+    policy = model.policy if hasattr(model, "policy") else model
+    scores, lengths = [], []
+    if hasattr(env, "num_envs"):
+        N = env.num_envs
+        obs, ret, ln = env.reset(), np.zeros(N), np.zeros(N, np.int64)
+        while len(scores) < n_eval_episodes:
+            a, _ = policy.predict(obs, deterministic=deterministic)
+            obs, r, done, infos = env.step(a)
+            ret += np.array([float(i.get("orig_reward", x)) for i, x in zip(infos, r)])
+            ln += 1
+            for i in np.nonzero(done)[0]:
+                scores.append(float(ret[i]))
+                lengths.append(int(ln[i]))
+                ret[i], ln[i] = 0.0, 0
+    else:
+        for _ in range(n_eval_episodes):
+            obs, done, ret, ln = env.reset(), False, 0.0, 0
+            while not done:
+                a, _ = policy.predict(obs[None], deterministic=deterministic)
+                obs, r, done, info = env.step(int(np.asarray(a).reshape(-1)[0]))
+                ret += float(info.get("orig_reward", r))
+                ln += 1
+            scores.append(ret)
+            lengths.append(ln)
+    scores, lengths = scores[:n_eval_episodes], lengths[:n_eval_episodes]
+    if return_episode_rewards:
+        return scores, lengths
+    return float(np.mean(scores)), float(np.std(scores))

@@ -204,3 +204,71 @@ def test_ppo_loop_runs_and_updates():
     assert not torch.equal(w0, model.policy.action_net.weight.detach())
     assert float(model.policy.beta) != b0
     assert len(model.policy.obs2leaves_dict) <= 128 + 1            # leaf cache is evicted (actor_critic_ts.py:99-103)
+
+
+def test_cule_env_multiple_matches_oracle_and_restarts():
+    """Depth-0 arm (cule_env_multiple.py): N root envs stepped together through K2 + K3 == N oracle envs stepped
+    one by one, stacks included; a finished env restarts from power-on + one no-op with a zeroed stack."""
+    from oracle import orc
+    from softtreemax_b200.envs import CuleEnvMultiple
+    N = 37
+    env = CuleEnvMultiple(device="cuda:0", env_kwargs=ENV_KWARGS, clip_reward=True, n_envs=N)
+    env.seed(3)
+    noops = np.random.RandomState(3).randint(31)
+    stack = env.reset()
+    g = orc.Game("synth_breakout")
+    s0 = g.reset()
+    lives = np.array([g.lives(s0)], np.int32)
+    obs = None
+    for _ in range(max(1, noops)):
+        obs, _, _, _ = g.agent_step(s0, 0, lives=lives)
+    want = np.zeros((4, 84, 84), np.uint8)
+    want[3] = obs
+    assert stack.shape == (N, 4, 84, 84) and all(np.array_equal(stack[i], want) for i in range(N))
+    states = [s0.copy() for _ in range(N)]
+    stacks = [want.copy() for _ in range(N)]
+    lv = [lives.copy() for _ in range(N)]
+    fresh = g.reset()
+    fl = np.array([g.lives(fresh)], np.int32)
+    g.agent_step(fresh, 0, lives=fl)
+    ended = np.zeros(N, bool)
+    rng = np.random.default_rng(5)
+    saw_done = False
+    for t in range(260):
+        a = rng.integers(0, 4, N)
+        a[:5] = 0                                           # a few envs never serve: they lose all lives and restart
+        got_stack, got_r, got_d, infos = env.step(a)
+        for i in range(N):
+            if ended[i]:
+                states[i], lv[i], stacks[i] = fresh.copy(), fl.copy(), np.zeros((4, 84, 84), np.uint8)
+            o, r, d, l = g.agent_step(states[i], int(a[i]), lives=lv[i])
+            stacks[i] = np.concatenate([stacks[i][1:], o[None]])
+            ended[i] = bool(d)
+            assert np.array_equal(got_stack[i], stacks[i]), (t, i)
+            assert got_r[i] == np.sign(r) and infos[i]["orig_reward"] == r and bool(got_d[i]) == bool(d), (t, i)
+            assert infos[i]["ale.lives"] == l
+        saw_done |= bool(ended.any())
+    assert saw_done, "the trace must cover a restart"
+
+
+def test_depth0_ppo_on_cule_env_multiple(tmp_path):
+    from softtreemax_b200.envs import CuleEnvMultiple
+    from softtreemax_b200.policy import ActorCriticCnnPolicyDepth0
+    from softtreemax_b200.ppo import PPO
+    env = CuleEnvMultiple(device="cuda:0", env_kwargs=ENV_KWARGS, clip_reward=True, n_envs=16)
+    torch.manual_seed(0)
+    model = PPO(ActorCriticCnnPolicyDepth0, env, n_steps=16, batch_size=64, n_epochs=2, seed=0).learn(512)
+    assert model.num_timesteps == 512 and len(model.log) == 2 and all(np.isfinite(r["loss"]) for r in model.log)
+    # save / load round trip and the evaluation loop of main.py:87-99 (vectorised and single-env)
+    from softtreemax_b200.envs import CuleEnv
+    from softtreemax_b200.ppo import evaluate_policy
+    path = str(tmp_path / "depth0.pt")
+    model.policy.save(path)
+    pol = ActorCriticCnnPolicyDepth0.load(path)
+    for a, b in zip(pol.state_dict().values(), model.policy.state_dict().values()):
+        assert torch.equal(a, b)
+    scores, lengths = evaluate_policy(pol, env, n_eval_episodes=3, return_episode_rewards=True)
+    assert len(scores) == 3 and all(l > 0 for l in lengths)
+    single = CuleEnv(device="cuda:0", env_kwargs=ENV_KWARGS, clip_reward=True, fire_reset=True)
+    mean, std = evaluate_policy(pol, single, n_eval_episodes=2)
+    assert np.isfinite(mean) and np.isfinite(std)
