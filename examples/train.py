@@ -13,6 +13,7 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import numpy as np
 import torch
 
+from softtreemax_b200.callbacks import TrainingCallback
 from softtreemax_b200.envs import CuleEnv, CuleEnvMultiple
 from softtreemax_b200.policy import ActorCriticCnnPolicyDepth0, ActorCriticCnnTSPolicy
 from softtreemax_b200.ppo import PPO, evaluate_policy, get_linear_fn
@@ -38,6 +39,7 @@ def main():
     ap.add_argument("--n_envs", type=int, default=256, help="depth-0 arm only (CuleEnvMultiple)")
     ap.add_argument("--run_type", default="train", choices=["train", "evaluate"])
     ap.add_argument("--n_eval_episodes", type=int, default=10)
+    ap.add_argument("--log_jsonl", default=None, help="episode metrics (what the reference sends to wandb), one JSON per line")
     args = ap.parse_args()
     torch.manual_seed(args.seed)
     np.random.seed(args.seed)
@@ -64,7 +66,7 @@ def main():
                              is_cumulative_mode=bool(args.is_cumulative_mode), regularization=args.regularization)
         model = PPO(ActorCriticCnnTSPolicy, env, policy_kwargs=policy_kwargs, verbose=1, seed=args.seed, **ppo_params)
     if args.run_type == "train":
-        model.learn(args.total_timesteps)
+        model.learn(args.total_timesteps, callback=TrainingCallback(path=args.log_jsonl))      # callbacks.py:11-57
         if args.model_filename:
             model.policy.save(args.model_filename)
             print("Saved", args.model_filename)

@@ -35,6 +35,7 @@ class PPO:
         self.policy = policy(env.observation_space, env.action_space, self.lr, **(policy_kwargs or {}))
         self.num_timesteps = 0
         self.log = []
+        self._step_cb = None
 
     def _rollout(self, obs, episode_start):
         n = self.n_steps
@@ -48,6 +49,8 @@ class PPO:
             buf["obs"][t], buf["act"][t], buf["start"][t] = obs, a, float(episode_start)
             buf["val"][t], buf["logp"][t] = float(v.reshape(-1)[0]), float(lp.reshape(-1)[0])
             obs, r, done, info = self.env.step(a)
+            if self._step_cb is not None:
+                self._step_cb(self, [info], [done])
             buf["rew"][t] = float(r)
             self._ep_ret += float(info.get("orig_reward", r))
             self.num_timesteps += 1
@@ -84,6 +87,8 @@ class PPO:
             buf["obs"][t], buf["act"][t], buf["start"][t] = obs, a, episode_start
             buf["val"][t], buf["logp"][t] = v.reshape(-1).cpu().numpy(), lp.reshape(-1).cpu().numpy()
             obs, r, done, infos = self.env.step(a)
+            if self._step_cb is not None:
+                self._step_cb(self, infos, done)
             buf["rew"][t] = r
             self._ep_ret = self._ep_ret + np.array([float(i.get("orig_reward", x)) for i, x in zip(infos, r)], np.float64)
             self.num_timesteps += N
@@ -137,6 +142,7 @@ class PPO:
 
     def learn(self, total_timesteps, callback=None):
         vec = hasattr(self.env, "num_envs")
+        self._step_cb = getattr(callback, "on_step", None)       # per-env-step hook (callbacks.TrainingCallback)
         obs = self.env.reset()
         if vec:
             episode_start, self._ep_ret = np.ones(self.env.num_envs, np.float32), np.zeros(self.env.num_envs, np.float64)

@@ -73,3 +73,17 @@ def test_learn_loop_on_vec_env():
     assert ppo.num_timesteps == 32 and len(ppo.log) == 2 and all(np.isfinite(r["loss"]) for r in ppo.log)
     a, _ = ppo.policy.predict(np.zeros((3, 4, 84, 84), np.uint8), deterministic=True)
     assert a.shape == (3,)
+
+
+def test_training_callback_records_episode_metrics(tmp_path):
+    from softtreemax_b200.callbacks import TrainingCallback
+    torch.manual_seed(2)
+    cb = TrainingCallback(path=str(tmp_path / "train.jsonl"))
+    ppo = PPO(ActorCriticCnnPolicyDepth0, BanditVecEnv(2), n_steps=10, batch_size=10, n_epochs=1, seed=0,
+              policy_kwargs=dict(device="cpu")).learn(60, callback=cb)
+    assert len(cb.records) == 6                                     # env 0 finishes an episode every 5 steps, 30 steps
+    assert all(r["train/episodic_length"] == 5 for r in cb.records)
+    assert all(0.0 <= r["train/episodic_reward"] <= 5.0 for r in cb.records)
+    assert cb.records[-1]["train/policy_weights_grad_var"] > 0.0     # two or more updates have left gradient history
+    assert all(len(h) <= 100 for h in ppo.policy.gradients_history.values())
+    assert len(open(tmp_path / "train.jsonl").read().splitlines()) == 6
