@@ -172,6 +172,9 @@ int stm_step_frames_noalloc(stm_ctx *ctx, uint8_t *states, const uint8_t *action
 
 /* number of kernels this ctx has launched since creation (bench.py's gpu_launches) */
 long long stm_launch_count(const stm_ctx *ctx);
+/* (measurement only, no reference counterpart) index of the ahead-of-time translated step kernel this ctx uses,
+ * 0 = the interpreter.  Non-zero only in a library built with -DSTM_WITH_XLATE and a process run with STM_XLATE=1. */
+int stm_translated_core(const stm_ctx *ctx);
 
 #ifdef __cplusplus
 }

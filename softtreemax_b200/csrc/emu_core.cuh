@@ -39,9 +39,6 @@
 #define STM_WARP_ALL(mask, pred) (pred)
 #define STM_WARP_MIN(mask, v) (v)
 #endif
-#ifndef STM_MINPC
-#define STM_MINPC 0      /* 1: lowest-program-counter-first lane scheduling inside a scanline */
-#endif
 
 namespace stm {
 
@@ -267,6 +264,12 @@ static inline void build_predecode(const uint8_t *rom, uint32_t rom_size, uint32
         out[2 * off] = hot[rom[off]];
         out[2 * off + 1] = rom[o1] | ((uint32_t)rom[o2] << 8);
     }
+}
+
+// translated cartridges (csrc/gen/xl_*.cuh): write case number k+1 of offsets[k] into bits 16..31 of the operand word
+static inline void stamp_cases(uint32_t *pre, const uint16_t *offsets, uint32_t n)
+{
+    for (uint32_t k = 0; k < n; k++) pre[2 * offsets[k] + 1] |= (k + 1) << 16;
 }
 
 // ---- game constants handed to the kernel ---------------------------------------------------------
@@ -552,6 +555,32 @@ STM_NOINLINE uint32_t tia_catchup(M m, uint32_t line, uint32_t rx, uint32_t xe, 
     return t.rx;
 }
 
+// decimal-mode ADC: returns a | p << 8 | zn << 16 (p: C, I, D, V bits as in Emu::p)
+STM_NOINLINE uint32_t adc_decimal(uint32_t a, uint32_t v, uint32_t p)
+{
+    uint32_t cin = p & FC;
+    uint32_t al = (a & 0x0F) + (v & 0x0F) + cin;
+    if (al > 9) al += 6;
+    uint32_t ah = (a >> 4) + (v >> 4) + (al > 0x0F ? 1u : 0u);
+    uint32_t bin = (a + v + cin) & 0xFF;
+    p &= ~(uint32_t)(FV | FC);
+    uint32_t zn = (bin ? 1u : 0u) | ((ah & 8) << 5);           // Z from the binary sum, N from the high digit
+    if (~(a ^ v) & (a ^ (ah << 4)) & 0x80) p |= FV;
+    if (ah > 9) ah += 6;
+    if (ah > 15) p |= FC;
+    a = ((ah << 4) | (al & 0x0F)) & 0xFF;
+    return a | (p << 8) | (zn << 16);
+}
+// decimal-mode SBC: the accumulator result (flags are the binary ones)
+STM_NOINLINE uint32_t sbc_decimal(uint32_t a, uint32_t v, uint32_t bc)
+{
+    int al = (int)(a & 0x0F) - (int)(v & 0x0F) - (int)bc;
+    int ah = (int)(a >> 4) - (int)(v >> 4);
+    if (al & 0x10) { al -= 6; ah--; }
+    if (ah & 0x10) ah -= 6;
+    return (uint32_t)(((ah << 4) | (al & 0x0F)) & 0xFF);
+}
+
 // native row `src` of the frame being drawn -> row `dst` (whole-line reuse, see Emu::end_line)
 template <class M>
 STM_NOINLINE void tia_copy_row(M m, uint32_t dst, uint32_t src) { m.copy_row(dst, src); }
@@ -573,6 +602,18 @@ STM_NOINLINE void tia_copy_row(M m, uint32_t dst, uint32_t src) { m.copy_row(dst
 // ~25 groups) -> write phase -> retire.  Every memory access goes through ONE read site and ONE
 // write site, so the TIA/RIOT slow paths (and the big catch-up renderer behind them) exist once in
 // the kernel instead of once per opcode; stack pulls/pushes are sequenced through the same sites.
+// The instruction loop of one scanline, as a policy of Emu::run_frame.  InterpCore interprets: fetch,
+// decode, dispatch per instruction.  (Lowest-program-counter-first lane scheduling was measured neutral
+// for the interpreter on B200; the translated cores use it, see tools/xlate_rom.cpp.)
+struct InterpCore {
+    template <class E>
+    static STM_DEV void run_line(E &e, uint32_t lanes, bool over)
+    {
+        (void)lanes;
+        if (!over) while (!e.exec_core()) { }
+    }
+};
+
 template <class M>
 struct Emu {
     M &m;
@@ -686,10 +727,13 @@ struct Emu {
     }
     // cycle (within the line) at which the current instruction touches the bus; runs the line wrap
     // first when that cycle lies beyond the end of the line
+    // kNoWrap: the caller has already checked that the access stays inside the line (translated cores send
+    // the rare straddling instruction to the interpreter, so the line wrap is not inlined into every case)
+    template <bool kNoWrap = false>
     STM_DEV uint32_t access_cycle(uint32_t cyc)
     {
         int32_t acc = hcyc + (int32_t)cyc - 1;
-        if (STM_UNLIKELY(acc >= STM_CYC_PER_LINE)) { end_line(); hcyc -= STM_CYC_PER_LINE; acc -= STM_CYC_PER_LINE; }
+        if (!kNoWrap && STM_UNLIKELY(acc >= STM_CYC_PER_LINE)) { end_line(); hcyc -= STM_CYC_PER_LINE; acc -= STM_CYC_PER_LINE; }
         return (uint32_t)acc;
     }
     STM_DEV uint32_t x_of(uint32_t acc) { int v = (int)acc * 3 - STM_HBLANK_CLK; return v < 0 ? 0u : (uint32_t)v; }
@@ -870,21 +914,35 @@ struct Emu {
     }
     STM_DEV uint32_t peek16zp(uint32_t z) { return peek(z & 0xFF) | (peek((z + 1) & 0xFF) << 8); }
     // the single read site / write site of the machine
-    STM_DEV uint32_t bus_read(uint32_t addr, uint32_t cyc, uint32_t opword)
+    // what a translated instruction knows at compile time about the address it touches
+    enum AddrCls : uint32_t { A_ANY, A_ROM, A_ZP };
+    template <bool kNoWrap = false>
+    STM_DEV uint32_t bus_read(uint32_t addr, uint32_t cyc, uint32_t opword, uint32_t cls = A_ANY)
     {
         addr &= 0x1FFF;
+        if (cls == A_ROM) return rom_at(addr);                          // cartridge space, no hotspot in range
+        if (cls == A_ZP) {                                              // zero page: RIOT RAM or a TIA read register
+            if (addr & 0x80) return m.ld8(addr & 0x7F);
+            return tia_read(addr, access_cycle<kNoWrap>(cyc));
+        }
         if ((addr & 0x1280) == 0x80) return m.ld8(addr & 0x7F);          // RAM: the common case
         if (addr & 0x1000) { hotspot(addr); return rom_at(addr); }
-        uint32_t acc = access_cycle(cyc);
+        uint32_t acc = access_cycle<kNoWrap>(cyc);
         if (!(addr & 0x80)) return tia_read(addr, acc);
         return riot_read(addr, cyc, opword);
     }
-    STM_DEV void bus_write(uint32_t addr, uint32_t v, uint32_t cyc)
+    template <bool kNoWrap = false>
+    STM_DEV void bus_write(uint32_t addr, uint32_t v, uint32_t cyc, uint32_t cls = A_ANY)
     {
         addr &= 0x1FFF;
+        if (cls == A_ZP) {
+            if (addr & 0x80) { m.st8(addr & 0x7F, v); return; }
+            tia_write(addr, v, access_cycle<kNoWrap>(cyc));
+            return;
+        }
         if ((addr & 0x1280) == 0x80) { m.st8(addr & 0x7F, v); return; }
         if (STM_UNLIKELY(addr & 0x1000)) { hotspot(addr); return; }
-        uint32_t acc = access_cycle(cyc);
+        uint32_t acc = access_cycle<kNoWrap>(cyc);
         if (!(addr & 0x80)) { tia_write(addr, v, acc); return; }
         riot_write(addr, v, cyc);
     }
@@ -892,19 +950,11 @@ struct Emu {
     // ---------------- ALU helpers (register only) ----------------
     STM_DEV void adc(uint32_t v)
     {
-        uint32_t cin = p & FC;
         if (STM_UNLIKELY(p & FD)) {
-            uint32_t al = (a & 0x0F) + (v & 0x0F) + cin;
-            if (al > 9) al += 6;
-            uint32_t ah = (a >> 4) + (v >> 4) + (al > 0x0F ? 1u : 0u);
-            uint32_t bin = (a + v + cin) & 0xFF;
-            p &= ~(uint32_t)(FV | FC);
-            zn = (bin ? 1u : 0u) | ((ah & 8) << 5);           // Z from the binary sum, N from the high digit
-            if (~(a ^ v) & (a ^ (ah << 4)) & 0x80) p |= FV;
-            if (ah > 9) ah += 6;
-            if (ah > 15) p |= FC;
-            a = ((ah << 4) | (al & 0x0F)) & 0xFF;
+            uint32_t r = adc_decimal(a, v, p);                 // out of line: one copy in a translated kernel
+            a = r & 0xFF; p = (r >> 8) & 0xFF; zn = r >> 16;
         } else {
+            uint32_t cin = p & FC;
             uint32_t s = a + v + cin;
             p = (p & ~(uint32_t)(FV | FC)) | (s >> 8) | (((~(a ^ v) & (a ^ s)) >> 1) & FV);
             a = s & 0xFF;
@@ -916,16 +966,11 @@ struct Emu {
         uint32_t bc = (p & FC) ^ 1u;
         uint32_t s = a - v - bc;
         uint32_t res = s & 0xFF;
-        bool dec = (p & FD) != 0;
+        const bool dec = (p & FD) != 0;
+        const uint32_t a0 = a;
         p = (p & ~(uint32_t)(FV | FC)) | (((s >> 8) & 1u) ^ 1u) | ((((a ^ v) & (a ^ s)) >> 1) & FV);
         zn = res;
-        if (STM_UNLIKELY(dec)) {
-            int al = (int)(a & 0x0F) - (int)(v & 0x0F) - (int)bc;
-            int ah = (int)(a >> 4) - (int)(v >> 4);
-            if (al & 0x10) { al -= 6; ah--; }
-            if (ah & 0x10) ah -= 6;
-            res = (uint32_t)(((ah << 4) | (al & 0x0F)) & 0xFF);
-        }
+        if (STM_UNLIKELY(dec)) res = sbc_decimal(a0, v, bc);
         a = res;
     }
     STM_DEV void cmp(uint32_t r, uint32_t v)
@@ -960,10 +1005,18 @@ struct Emu {
         if (STM_LIKELY(a13 - 0x1000u <= 0xFFDu)) {                      // in cartridge space with both operand bytes inside it
             uint32_t ops;
             m.fetch((bank << 12) | (a13 & gp.rom_mask), w, ops);
-            b1 = ops & 0xFF; b2 = ops >> 8;
+            b1 = ops & 0xFF; b2 = (ops >> 8) & 0xFF;            // (bits 16..31: case number of a translated core)
         } else {
             w = m.opinfo(peek(pc)); b1 = peek(pc + 1); b2 = peek(pc + 2);
         }
+        return exec_body<false>(w, b1, b2);
+    }
+    // Everything after the fetch.  kConst = the caller passes compile-time constants (a translated
+    // cartridge, csrc/gen/xl_*.cuh): decode, addressing and dispatch then fold away at compile time and
+    // what is left is the few instructions this one 6502 instruction needs.
+    template <bool kConst>
+    STM_DEV bool exec_body(const uint32_t w, uint32_t b1, uint32_t b2)
+    {
         const uint32_t am = w & 7, kind = (w >> 5) & 3, grp = (w >> 13) & 31, data = w >> 22;
         uint32_t cyc = (w >> 7) & 15;
         uint32_t npc = pc + ((w >> 11) & 3);                 // pc may run past 0xFFFF: every use masks it
@@ -1001,6 +1054,19 @@ struct Emu {
             return hcyc >= STM_CYC_PER_LINE;                   // (a branch cannot end the frame)
         }
 
+        // A translated instruction (kConst) knows its base address: an indexed access whose whole 256-byte
+        // range lies in cartridge space (no hotspot) is a ROM read, a zero-page one is RAM-or-TIA; the other
+        // address spaces' code is then never instantiated for it.  Stack pulls / pushes go the general way.
+        uint32_t acls = A_ANY;
+        if (kConst && !((w >> 19) & 1u) && grp != G_PUSH && grp != G_JSR && grp != G_BRK) {
+            if (am == 2) acls = A_ZP;
+            else if (am == 3 && (w & 0x18)) {
+                const uint32_t base16 = b1 | (b2 << 8), lo = base16 & 0x1FFF, hi = lo + 0xFF;
+                const bool f8 = gp.bank_scheme == STM_BANK_F8;
+                if ((lo & 0x1000) && hi <= 0x1FFF && !(f8 && hi >= 0x1FF8 && lo <= 0x1FF9) && kind == K_R) acls = A_ROM;
+            }
+        }
+
         // read phase: one memory operand, or 1..3 stack pulls
         uint32_t r0 = b1, r1 = 0, r2 = 0;
         if (w & (3u << 20)) {
@@ -1008,7 +1074,7 @@ struct Emu {
             uint32_t addr = ea;
             if (STM_UNLIKELY(w & (1u << 19))) { sp = (sp + 1) & 0xFF; addr = 0x100 | sp; }
             for (;;) {                                         // runs once except for RTS / RTI
-                r0 = bus_read(addr, cyc, w);
+                r0 = bus_read<kConst>(addr, cyc, w, acls);
                 if (STM_LIKELY(--nrd == 0)) break;
                 r2 = r1; r1 = r0;
                 sp = (sp + 1) & 0xFF; addr = 0x100 | sp;
@@ -1023,7 +1089,7 @@ struct Emu {
         // number the compiler cannot see through — otherwise it folds the chain back into the jump
         // table, whose indexed constant load + indirect branch cost more than the whole chain); the
         // rest go through the jump table.
-        auto is = [&](uint32_t g) { uint32_t t = grp; STM_OPAQUE(t); return t == g; };   // a fresh copy per test
+        auto is = [&](uint32_t g) { uint32_t t = grp; if (!kConst) STM_OPAQUE(t); return t == g; };   // a fresh copy per test
         if (is(G_STORE)) {
             w0 = ((data & 1) ? a : 0xFFu) & ((data & 2) ? x : 0xFFu) & ((data & 4) ? y : 0xFFu);
             nwr = 1;
@@ -1087,7 +1153,7 @@ struct Emu {
             uint32_t addr = ea;
             if (STM_UNLIKELY(wpush)) { addr = 0x100 | sp; sp = (sp - 1) & 0xFF; }
             for (;;) {                                         // runs once except for JSR / BRK
-                bus_write(addr, w0, cyc);
+                bus_write<kConst>(addr, w0, cyc, acls);
                 if (STM_LIKELY(--nwr == 0)) break;
                 w0 = w1; w1 = w2;
                 addr = 0x100 | sp; sp = (sp - 1) & 0xFF;
@@ -1114,6 +1180,7 @@ struct Emu {
     // call run_frame the same number of times.  Scanline lock-step: each lane runs instructions until
     // its scanline ends, then the warp reconverges and wraps the line (the whole-line catch-up render)
     // with all lanes active; lanes whose frame is over idle until the slowest lane's frame is over.
+    template <class Core = InterpCore>
     STM_DEV void run_frame(uint32_t ale_action, bool want_pixels, uint32_t lanes = 0xFFFFFFFFu)
     {
         (void)lanes;
@@ -1124,22 +1191,10 @@ struct Emu {
         tia_dirty();                                           // a new native frame: no row to reuse yet
         bool over = false;
         do {
-            // Run every lane to the end of its scanline.  (STM_MINPC: lowest-program-counter-first —
-            // in each round only the lanes whose (bank, pc) is the warp minimum execute, so lanes
-            // that took different sides of a branch fall back into step when their paths merge.
-            // Measured on B200: no gain over plain per-lane progress for these cartridges, so off.)
-            bool ended = over;
-#if STM_MINPC
-            for (;;) {
-                bool want = !ended && !(flags & STM_F_FRAME_DONE);
-                uint32_t key = want ? ((bank << 16) | pc) : 0xFFFFFFFFu;
-                uint32_t kmin = STM_WARP_MIN(lanes, key);
-                if (kmin == 0xFFFFFFFFu) break;
-                if (key == kmin) ended = exec_core();
-            }
-#else
-            if (!over) while (!exec_core()) { }
-#endif
+            // Run every lane to the end of its scanline: Core::run_line (the interpreter loop below, or a
+            // translated cartridge).
+            Core::run_line(*this, lanes, over);
+            bool ended;
             ended = hcyc >= STM_CYC_PER_LINE || (brk & BRK_WSYNC);
             if (!over) {
                 if (ended) finish_line();

@@ -23,6 +23,7 @@
 #include "../../include/stm_b200.h"
 #include "../../include/stm_palette.h"
 #include "emu_core.cuh"
+#include "gen/xl_index.cuh"
 
 namespace {
 
@@ -60,6 +61,7 @@ struct stm_ctx {
     uint32_t *d_scratch = nullptr;   // native frames
     uint8_t  *d_stepped = nullptr;   // per scratch env: 1 if the env was emulated by the last stm_step
     int scratch_envs = 0;
+    int xl = 0;                      // 0: interpreter; k > 0: the k-th translated cartridge of STM_XL_LIST
     int last_render_frames = 0;      // how many native frames the last stm_step(render) produced (1 or 2)
     // intermediate-level pools for stm_bfs (ping-pong)
     uint8_t *pool_state[2] = {nullptr, nullptr};
@@ -237,6 +239,8 @@ struct StepArgs {
     GameParams gp;
 };
 
+// Core = stm::InterpCore (any cartridge) or a translated cartridge stm::Xl_<name> (csrc/gen/)
+template <class Core>
 __global__ void __launch_bounds__(kStepThreads, STM_STEP_MIN_CTAS)
 stm_step_kernel(const StepArgs a)
 {
@@ -281,7 +285,7 @@ stm_step_kernel(const StepArgs a)
         bool want = a.render && f >= a.frameskip - 2;
         // the newest frame always goes to slot 1, the one before it to slot 0
         m.fsel = (f == a.frameskip - 1) ? 1u : 0u;
-        e.run_frame(ale, want, lanes);
+        e.template run_frame<Core>(ale, want, lanes);
         int r = e.get_data(a.episodic_life != 0, done, lives);
         rew = __fadd_rn(rew, __fmul_rn(a.weight, (float)r));
     }
@@ -457,6 +461,24 @@ int ensure_scratch(stm_ctx *ctx, int n_envs)
     return STM_OK;
 }
 
+// the step kernel for this ctx's cartridge: its translated core if the library has one, else the interpreter
+void launch_step_kernel(const stm_ctx *ctx, int blocks, size_t smem, cudaStream_t st, const StepArgs &a)
+{
+    int k = 0; (void)k;
+#define STM_LAUNCH(name) if (ctx->xl == ++k) { stm_step_kernel<stm::Xl_##name><<<blocks, kStepThreads, smem, st>>>(a); return; }
+    STM_XL_LIST(STM_LAUNCH)
+#undef STM_LAUNCH
+    stm_step_kernel<stm::InterpCore><<<blocks, kStepThreads, smem, st>>>(a);
+}
+
+template <class Core>
+cudaError_t set_step_attrs(size_t smem, int pct)
+{
+    cudaError_t e = cudaFuncSetAttribute(stm_step_kernel<Core>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    return cudaFuncSetAttribute(stm_step_kernel<Core>, cudaFuncAttributePreferredSharedMemoryCarveout, pct);
+}
+
 int launch_step(stm_ctx *ctx, uint8_t *states, const uint8_t *actions, int n, int frameskip,
                 int episodic_life, float weight, float *rewards, uint8_t *done, int32_t *lives,
                 int render, cudaStream_t st)
@@ -470,7 +492,7 @@ int launch_step(stm_ctx *ctx, uint8_t *states, const uint8_t *actions, int n, in
     a.rom_words = ctx->rom_words; a.weight = weight; a.gp = ctx->gp;
     size_t smem = (size_t)(64 * kStepThreads + ctx->rom_words + 256) * sizeof(uint32_t);
     int blocks = (n + kStepThreads - 1) / kStepThreads;
-    { Timed t(ctx, st, T_STEP); stm_step_kernel<<<blocks, kStepThreads, smem, st>>>(a); }
+    { Timed t(ctx, st, T_STEP); launch_step_kernel(ctx, blocks, smem, st, a); }
     ctx->launches++;
     if (render) ctx->last_render_frames = frameskip >= 2 ? 2 : 1;
     CUDA_TRY(ctx, cudaGetLastError());
@@ -545,6 +567,7 @@ const char *stm_last_error(const stm_ctx *ctx) { return ctx ? ctx->err : g_creat
 size_t stm_state_bytes(const stm_ctx *) { return STM_STATE_BYTES; }
 int stm_num_actions(const stm_ctx *ctx) { return ctx ? ctx->desc.n_actions : 0; }
 long long stm_launch_count(const stm_ctx *ctx) { return ctx ? ctx->launches : 0; }
+int stm_translated_core(const stm_ctx *ctx) { return ctx ? ctx->xl : 0; }
 int stm_max_step_envs(const stm_ctx *ctx) { return ctx ? ctx->scratch_envs : 0; }
 
 int stm_ctx_create(stm_ctx **out, const stm_game_desc *desc, const uint8_t *rom, int device)
@@ -587,6 +610,22 @@ int stm_ctx_create(stm_ctx **out, const stm_game_desc *desc, const uint8_t *rom,
             uint32_t *pre = new (std::nothrow) uint32_t[2 * desc->rom_size];
             if (!pre) return fail(ctx, STM_ERR_NOMEM, "stm_ctx_create: out of host memory");
             build_predecode(rom, desc->rom_size, gp.rom_mask, pre);
+            // A translated core for this very image?  OFF unless STM_XLATE=1: on B200 the translated kernels
+            // execute half the instructions of the interpreter and still lose to it, because their code
+            // (one block of SASS per cartridge instruction, 300 KB) misses the instruction caches where the
+            // interpreter's 10 KB loop hits; they stay in the library as a measured experiment.
+            {
+                const char *on = getenv("STM_XLATE");
+                const char *no = (on && atoi(on)) ? "0" : "1";
+                const uint32_t h = stm::rom_hash(rom, desc->rom_size);
+                int k = 0; (void)k; (void)h; (void)no;
+#define STM_MATCH(name) \
+                ++k; \
+                if (!(no && atoi(no)) && h == stm::Xl_##name::kRomHash && desc->rom_size == stm::Xl_##name::kRomSize) { \
+                    ctx->xl = k; stm::stamp_cases(pre, stm::Xl_##name::offsets(), stm::Xl_##name::kCases); }
+                STM_XL_LIST(STM_MATCH)
+#undef STM_MATCH
+            }
             cudaError_t e1 = cudaMalloc(&ctx->d_pre, 8ull * desc->rom_size);
             if (e1 == cudaSuccess) e1 = cudaMemcpy(ctx->d_pre, pre, 8ull * desc->rom_size, cudaMemcpyHostToDevice);
             delete[] pre;
@@ -594,14 +633,17 @@ int stm_ctx_create(stm_ctx **out, const stm_game_desc *desc, const uint8_t *rom,
         }
         // the attribute is per kernel, not per ctx: always allow the largest cartridge (8 KB)
         size_t smem = (size_t)(64 * kStepThreads + 8192 / 4 + 256) * sizeof(uint32_t);
-        CUDA_TRY(ctx, cudaFuncSetAttribute(stm_step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         // Shared memory for the resident CTAs and no more: what is left of the 256 KB is L1, which holds
         // the predecoded cartridge (8 B per image byte) every instruction fetch reads.
+        int pct = (int)((STM_STEP_MIN_CTAS * (smem + 1024) * 100 + 228 * 1024 - 1) / (228 * 1024));
+        if (const char *e = getenv("STM_STEP_CARVEOUT")) pct = atoi(e);
+        if (pct > 100) pct = 100;
+        CUDA_TRY(ctx, set_step_attrs<stm::InterpCore>(smem, pct));
         {
-            int pct = (int)((STM_STEP_MIN_CTAS * (smem + 1024) * 100 + 228 * 1024 - 1) / (228 * 1024));
-            if (const char *e = getenv("STM_STEP_CARVEOUT")) pct = atoi(e);
-            if (pct > 100) pct = 100;
-            CUDA_TRY(ctx, cudaFuncSetAttribute(stm_step_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, pct));
+            int k = 0; (void)k;
+#define STM_ATTR(name) if (ctx->xl == ++k) CUDA_TRY(ctx, set_step_attrs<stm::Xl_##name>(smem, pct));
+            STM_XL_LIST(STM_ATTR)
+#undef STM_ATTR
         }
         return ensure_scratch(ctx, 4096);
     };
@@ -911,7 +953,7 @@ extern "C" int stm_step_frames_noalloc(stm_ctx *ctx, uint8_t *states, const uint
     a.n = n; a.frameskip = frameskip; a.episodic_life = episodic_life; a.render = 1;
     a.rom_words = ctx->rom_words; a.weight = weight; a.gp = ctx->gp;
     const size_t smem = (size_t)(64 * kStepThreads + ctx->rom_words + 256) * sizeof(uint32_t);
-    stm_step_kernel<<<(n + kStepThreads - 1) / kStepThreads, kStepThreads, smem, st>>>(a);
+    launch_step_kernel(ctx, (n + kStepThreads - 1) / kStepThreads, smem, st, a);
     ctx->launches++;
     CUDA_TRY(ctx, cudaGetLastError());
     dim3 grid((n + kTileEnvs - 1) / kTileEnvs, STM_OBS_H);

@@ -54,6 +54,11 @@ class Engine:
         return lib().stm_launch_count(self._h)
 
     @property
+    def translated_core(self):
+        """0 = the interpreter kernel; k > 0 = the k-th translated cartridge (STM_WITH_XLATE build + STM_XLATE=1)."""
+        return lib().stm_translated_core(self._h)
+
+    @property
     def max_step_envs(self):
         return lib().stm_max_step_envs(self._h)
 

@@ -159,6 +159,31 @@ def test_bfs_matches_oracle(orc, engines, name, R, depth):
     assert np.array_equal(got["states"].cpu().numpy(), want[4].reshape(L, 256))
 
 
+@pytest.mark.parametrize("name,R,depth", [("synth_breakout", 40, 2), ("synth_pong", 9, 2), ("synth_pacman", 5, 2), ("synth_torture", 7, 2)])
+def test_translated_cartridge_kernels_match_oracle(orc, name, R, depth, monkeypatch):
+    """The ahead-of-time translated step kernels (tools/xlate_rom.cpp -> csrc/gen/xl_*.cuh, selected by image hash
+    when STM_XLATE=1; off by default because they measure slower than the interpreter) are bit-exact too."""
+    from softtreemax_b200.engine import Engine
+    monkeypatch.setenv("STM_XLATE", "1")
+    g = orc.Game(name)
+    eng = Engine(name)
+    if eng.translated_core == 0:
+        eng.close()
+        pytest.skip("library built without -DSTM_WITH_XLATE (the default)")
+    try:
+        roots, stacks = orc.make_roots(g, R, seed=21, base_steps=50, spread=60)
+        want = g.bfs(roots, stacks, depth, gamma=0.99, clip_reward=False)
+        got = eng.bfs(dev(roots, eng), dev(stacks, eng), depth, gamma=0.99, clip_reward=False, want_states=True)
+        torch.cuda.synchronize()
+        L = R * g.n_actions ** depth
+        assert np.array_equal(got["stacks"].cpu().numpy(), want[0].reshape(L, 4, 84, 84))
+        assert np.array_equal(got["rewards"].cpu().numpy(), want[1].reshape(L))
+        assert np.array_equal(got["done"].cpu().numpy(), want[2].reshape(L))
+        assert np.array_equal(got["states"].cpu().numpy(), want[4].reshape(L, 256))
+    finally:
+        eng.close()
+
+
 def test_bfs_unclipped_rewards_and_chunking(orc, engines):
     """clip_reward=False returns the raw discounted sums; a scratch smaller than a level forces the
     level to be processed in several K2/K3 chunks — results must not change."""

@@ -37,10 +37,12 @@ def _bind(H, orc):
     H.hc_frame.argtypes = [C.POINTER(orc.GameDesc), C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_int,
                            C.c_float, C.c_void_p, C.c_void_p, C.c_void_p]
     H.hc_exec_one.argtypes = [C.POINTER(orc.GameDesc), C.c_void_p, C.c_void_p]
+    H.hc_frame_xl.argtypes = H.hc_frame.argtypes
+    H.hc_frame_xl.restype = C.c_int
     return H
 
 
-def run_pair(orc, H, game, nframes, seed, render_every=1):
+def run_pair(orc, H, game, nframes, seed, render_every=1, translated=False):
     rng = np.random.default_rng(seed)
     so = game.reset()
     sh = so.copy()
@@ -54,8 +56,9 @@ def run_pair(orc, H, game, nframes, seed, render_every=1):
         rend = (f % render_every) == 0
         game.frame(so, a, fbo if rend else None)
         orc.lib().orc_get_data(game.h, _p(so), 1, C.c_float(0.97), _p(do), _p(ro), _p(lo))
-        H.hc_frame(C.byref(game.desc), _p(rom), _p(sh), a, _p(fbh) if rend else None, 1, C.c_float(0.97),
-                   _p(dh), _p(rh), _p(lh))
+        rc = (H.hc_frame_xl if translated else H.hc_frame)(C.byref(game.desc), _p(rom), _p(sh), a, _p(fbh) if rend else None, 1,
+                                                           C.c_float(0.97), _p(dh), _p(rh), _p(lh))
+        assert not translated or rc == 1, "no translated core for this cartridge"
         assert np.array_equal(so, sh), f"state differs at frame {f}: offsets {np.nonzero(so != sh)[0][:16]}"
         if rend:
             # rows with row % 5 == 2 are never sampled by the 84x84 resize; the CUDA core does not draw them
@@ -68,6 +71,12 @@ def run_pair(orc, H, game, nframes, seed, render_every=1):
 @pytest.mark.parametrize("name", ["synth_breakout", "synth_pong", "synth_pacman", "synth_torture"])
 def test_games_match_oracle(orc, host_core, name):
     run_pair(orc, _bind(host_core, orc), orc.Game(name), 240, seed=3)
+
+
+@pytest.mark.parametrize("name", ["synth_breakout", "synth_pong", "synth_pacman", "synth_torture"])
+def test_translated_cartridges_match_oracle(orc, host_core, name):
+    """The ahead-of-time translated cores (tools/xlate_rom.cpp -> csrc/gen/xl_*.cuh) against the oracle."""
+    run_pair(orc, _bind(host_core, orc), orc.Game(name), 400, seed=11, translated=True)
 
 
 @pytest.mark.parametrize("seed", range(12))

@@ -2,9 +2,12 @@
 // plain-array memory policy so that the CUDA emulator core can be diffed against the oracle in
 // this GPU-less container (tests/test_host_core.py).  Never loaded by the product package.
 #include <cstring>
+#include <vector>
 #include <cstdint>
 #include "../../include/stm_palette.h"
 #include "../../softtreemax_b200/csrc/emu_core.cuh"
+#define STM_WITH_XLATE 1
+#include "../../softtreemax_b200/csrc/gen/xl_index.cuh"
 
 namespace {
 struct HostMem {
@@ -17,11 +20,12 @@ struct HostMem {
     void st32(uint32_t o, uint32_t v) { memcpy(blob + o, &v, 4); }
     uint32_t rom8(uint32_t i) const { return rom[i]; }
     uint32_t mask;
+    const uint16_t *xl = nullptr;          // case number per image offset (translated cores), or null
     void fetch(uint32_t off, uint32_t &w, uint32_t &ops) const
     {
         uint32_t win = off & ~mask;
         w = lut[rom[off]];
-        ops = rom[win | ((off + 1) & mask)] | (rom[win | ((off + 2) & mask)] << 8);
+        ops = rom[win | ((off + 1) & mask)] | (rom[win | ((off + 2) & mask)] << 8) | (xl ? (uint32_t)xl[off] << 16 : 0u);
     }
     uint32_t opinfo(uint32_t op) const { return lut[op]; }
     uint32_t grey(uint32_t i) const { static const uint8_t g[128] = STM_GRAY_LUT_INIT; return g[i & 127]; }
@@ -50,22 +54,59 @@ void hc_fill_params(stm::GameParams *gp, const stm_game_desc *d)
 
 void hc_decode_table(uint32_t *out) { stm::build_decode_table(out); }
 
+}  // extern "C"
+
+extern "C" void hc_fill_params(stm::GameParams *gp, const stm_game_desc *d);
+
+// per translated core: image offset -> case number (what stm_ctx_create stamps into the predecoded cartridge)
+template <class Core> static const uint16_t *case_table(uint32_t rom_size)
+{
+    static std::vector<uint16_t> t;
+    if (t.empty()) {
+        t.assign(rom_size, 0);
+        for (uint32_t k = 0; k < Core::kCases; k++) t[Core::offsets()[k]] = (uint16_t)(k + 1);
+    }
+    return t.data();
+}
+template <> const uint16_t *case_table<stm::InterpCore>(uint32_t) { return nullptr; }
+
 // one emulated frame + get_data, like the oracle's orc_frame + orc_get_data
-void hc_frame(const stm_game_desc *d, const uint8_t *rom, uint8_t *blob, int ale_action, uint8_t *fb,
-              int episodic_life, float weight, uint8_t *done, float *reward, int32_t *lives)
+template <class Core>
+static void frame_with(const stm_game_desc *d, const uint8_t *rom, uint8_t *blob, int ale_action, uint8_t *fb,
+                       int episodic_life, float weight, uint8_t *done, float *reward, int32_t *lives)
 {
     if (!g_lut_ok) { stm::build_hot_table(g_lut); g_lut_ok = true; }
     stm::GameParams gp; hc_fill_params(&gp, d);
     HostMem m{blob, rom, g_lut, fb, gp.rom_mask};
+    m.xl = case_table<Core>(d->rom_size);
     stm::Emu<HostMem> e(m, gp);
     e.load();
-    e.run_frame((uint32_t)ale_action, fb != nullptr);
+    e.template run_frame<Core>((uint32_t)ale_action, fb != nullptr);
     uint32_t dn = *done; int lv = *lives;
     int r = e.get_data(episodic_life != 0, dn, lv);
     volatile float wr = weight * (float)r;
     *reward = *reward + wr;
     *done = (uint8_t)dn; *lives = lv;
     e.store();
+}
+
+extern "C" {
+
+void hc_frame(const stm_game_desc *d, const uint8_t *rom, uint8_t *blob, int ale_action, uint8_t *fb,
+              int episodic_life, float weight, uint8_t *done, float *reward, int32_t *lives)
+{ frame_with<stm::InterpCore>(d, rom, blob, ale_action, fb, episodic_life, weight, done, reward, lives); }
+
+// the same through the translated core of this cartridge (csrc/gen/xl_*.cuh); returns 0 if there is none
+int hc_frame_xl(const stm_game_desc *d, const uint8_t *rom, uint8_t *blob, int ale_action, uint8_t *fb,
+                int episodic_life, float weight, uint8_t *done, float *reward, int32_t *lives)
+{
+    const uint32_t h = stm::rom_hash(rom, d->rom_size);
+#define STM_TRY(name) \
+    if (h == stm::Xl_##name::kRomHash && d->rom_size == stm::Xl_##name::kRomSize) { \
+        frame_with<stm::Xl_##name>(d, rom, blob, ale_action, fb, episodic_life, weight, done, reward, lives); return 1; }
+    STM_XL_LIST(STM_TRY)
+#undef STM_TRY
+    return 0;
 }
 
 void hc_exec_one(const stm_game_desc *d, const uint8_t *rom, uint8_t *blob)

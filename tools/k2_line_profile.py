@@ -16,7 +16,7 @@ import tempfile
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
-def line_table():
+def line_table(want_len=None):
     so = os.path.join(ROOT, "softtreemax_b200", "libstm_b200.so")
     with tempfile.TemporaryDirectory() as d:
         subprocess.run(["cuobjdump", "-xelf", "all", so], cwd=d, capture_output=True)
@@ -36,7 +36,12 @@ def line_table():
         m = re.match(r"\s*/\*([0-9a-f]{4,5})\*/\s+(.*?);", l)
         if m and cur:
             secs[cur].append((cf, cl))
-    return [v for k, v in secs.items() if "stm_step_kernel" in k][0]
+    cands = [v for k, v in secs.items() if "stm_step_kernel" in k]
+    if want_len is not None:                       # several instantiations (interpreter, translated cartridges): match by size
+        for v in cands:
+            if len(v) == want_len:
+                return v
+    return cands[0]
 
 
 def main():
@@ -51,7 +56,7 @@ def main():
     isamp = [i for i, h in enumerate(hdr) if h.startswith("Warp Stall Sampling (All")]
     isamp = isamp[0] if isamp else None
     first = rows[k[0] + 2:(k[1] if len(k) > 1 else len(rows))]
-    table = line_table()
+    table = line_table(len(first))
     if len(table) != len(first):
         sys.exit(f"SASS of the capture ({len(first)}) and of the library ({len(table)}) differ: rebuild / recapture")
     counts = collections.Counter(int(r[ie]) for r in first)
@@ -66,6 +71,9 @@ def main():
     src = {}
     for f in ("emu_core.cuh", "stm_kernels.cu"):
         src[f] = open(os.path.join(ROOT, "softtreemax_b200", "csrc", f)).read().splitlines()
+    gen = os.path.join(ROOT, "softtreemax_b200", "csrc", "gen")
+    for f in os.listdir(gen) if os.path.isdir(gen) else []:
+        src[f] = open(os.path.join(gen, f)).read().splitlines()
     print(f"SASS instructions per emulated instruction: {tot / n_iter:.1f}")
     for (f, ln), c in agg.most_common(top):
         text = src[f][ln - 1].strip()[:100] if f in src and ln - 1 < len(src[f]) else ""
