@@ -255,72 +255,58 @@ stm_cnn_gemm_kernel(const void *__restrict__ in, const __nv_bfloat16 *__restrict
             }
         }
     } else if (warp < kProdWarps) {
-        // ===================== producers, u8 NCHW input (conv1): cp.async staging, converted to fp16 =====================
+        // ===================== producers, u8 NCHW input (conv1): registers, converted to fp16 =====================
         // kSplit threads share a row of the tile: thread t owns row t % 128 and the patch rows
-        // [8 / kSplit * (t / 128), ...) of it, so one warp still covers 32 consecutive rows (coalesced gather)
-        // and the per-thread work shrinks with the number of producer warps (the gather is bound by the
-        // instruction latency of its producer warps, not by bytes).  The raw bytes of a thread's share of the
-        // patch in one channel are fetched as 4-byte cp.async copies into a PRIVATE slot of a small raw ring
-        // (word-major: copies and read-back are bank-conflict free); kRaw - 1 slices stay in flight per thread
-        // without holding registers.  A landed slice is read back, widened to fp16 and written to the swizzled
-        // operand ring.  No barrier guards the raw ring: nobody but its owner touches a thread's words.
-        constexpr int kRaw = 3, kSplit = kProducerThreads / kTileM, kMyRows = 8 / kSplit;     // patch rows per thread
+        // [8 / kSplit * (t / 128), ...) of it, so one warp covers 32 consecutive rows (coalesced 4-byte loads).
+        // The loads of work item i+1 (the next channel, or the first channel of the next tile) are issued before
+        // item i is widened to fp16 and stored, so their latency hides under the conversion.  (A cp.async raw-byte
+        // ring with two items in flight per thread measured 8 % slower: more instructions, same latency.)
+        constexpr int kSplit = kProducerThreads / kTileM, kMyRows = 8 / kSplit;                 // patch rows per thread
         static_assert(kProducerThreads % kTileM == 0 && 8 % kSplit == 0, "whole rows per producer thread");
-        uint32_t *raw = reinterpret_cast<uint32_t *>(sB + (size_t)nchunks * kBBytes);          // [kRaw][16][128]
         const int row = tid % kTileM, kg0 = (tid / kTileM) * kMyRows;
         const uint32_t Mt = (uint32_t)M_total, P = (uint32_t)g.P, OW = (uint32_t)g.OW, rOW = (uint32_t)g.recip_ow;
         const int my_tiles = (long long)blockIdx.x < ntiles ? (int)((ntiles - blockIdx.x + gridDim.x - 1) / gridDim.x) : 0;
         const int items = my_tiles * nchunks;
-        uint32_t tile = blockIdx.x;
+        uint32_t tile = blockIdx.x, st = 0, ph = 0;
         int kc = 0;
         const uint8_t *src8 = reinterpret_cast<const uint8_t *>(in);
-        uint32_t nbytes = 0, slot_w = 0, slot_r = 0, st = 0, ph = 0;
-        for (int i = 0; i < items + (kRaw - 1); i++) {
-            if (i < items) {
-                if (kc == 0) {
-                    const uint32_t m = tile * kTileM + row;
-                    const bool row_ok = m < Mt;
-                    const uint32_t img = row_ok ? m / P : 0u;
-                    const uint32_t pos = row_ok ? m - img * P : 0u;
-                    const uint32_t oy = (pos * rOW) >> 16, ox = pos - oy * OW;
-                    src8 = reinterpret_cast<const uint8_t *>(in) + (size_t)img * (uint32_t)(g.C * g.IH * g.IW)
-                           + (oy * (uint32_t)g.S + kg0) * (uint32_t)g.IW + ox * (uint32_t)g.S;
-                    nbytes = row_ok ? 4u : 0u;                          // 0 => zero fill
-                }
-                const uint8_t *p8 = src8 + (uint32_t)(kc * g.IH * g.IW);
-                const uint32_t dst = smem_u32(raw + (size_t)slot_w * 16 * kTileM + (size_t)(2 * kg0) * kTileM + row);
-                if (!(g.debug & 1)) {
-                #pragma unroll
-                for (int kg = 0; kg < kMyRows; kg++) {
-                    asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;"
-                                 :: "r"(dst + (2 * kg) * kTileM * 4), "l"(p8 + kg * g.IW), "r"(nbytes) : "memory");
-                    asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;"
-                                 :: "r"(dst + (2 * kg + 1) * kTileM * 4), "l"(p8 + kg * g.IW + 4), "r"(nbytes) : "memory");
-                }
-                }
-                if (++kc == nchunks) { kc = 0; tile += gridDim.x; }
-                if (++slot_w == kRaw) slot_w = 0;
+        bool row_ok = false;
+        uint2 cur[kMyRows], nxt[kMyRows];
+        auto load_next = [&](uint2 *r) {
+            if (kc == 0) {
+                const uint32_t m = tile * kTileM + row;
+                row_ok = m < Mt;
+                const uint32_t img = row_ok ? m / P : 0u;
+                const uint32_t pos = row_ok ? m - img * P : 0u;
+                const uint32_t oy = (pos * rOW) >> 16, ox = pos - oy * OW;
+                src8 = reinterpret_cast<const uint8_t *>(in) + (size_t)img * (uint32_t)(g.C * g.IH * g.IW)
+                       + (oy * (uint32_t)g.S + kg0) * (uint32_t)g.IW + ox * (uint32_t)g.S;
             }
-            asm volatile("cp.async.commit_group;" ::: "memory");
-            if (i >= kRaw - 1) {
-                asm volatile("cp.async.wait_group %0;" :: "n"(kRaw - 1) : "memory");
-                const uint32_t *rs = raw + (size_t)slot_r * 16 * kTileM + (size_t)(2 * kg0) * kTileM + row;
-                uint32_t wv[2 * kMyRows];
-                #pragma unroll
-                for (int q = 0; q < 2 * kMyRows; q++) wv[q] = rs[q * kTileM];
-                mbar_wait(&empty[st], ph ^ 1);                      // slot free (first pass: returns at once)
-                uint8_t *abase = sA + st * kABytes;
-                if (!(g.debug & 16)) {
-                #pragma unroll
-                for (int kg = 0; kg < kMyRows; kg++)
-                    *reinterpret_cast<uint4 *>(abase + swz((uint32_t)row, (uint32_t)(kg0 + kg))) = u8x8_to_f16x8(wv[2 * kg], wv[2 * kg + 1]);
-                }
-                if (!(g.debug & 64)) asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-                __syncwarp();
-                if ((tid & 31) == 0) mbar_arrive(&full[st]);
-                if (++slot_r == kRaw) slot_r = 0;
-                if (++st == kStages) { st = 0; ph ^= 1; }
+            const uint8_t *p8 = src8 + (uint32_t)(kc * g.IH * g.IW);
+            #pragma unroll
+            for (int kg = 0; kg < kMyRows; kg++) {
+                const uint32_t *p = reinterpret_cast<const uint32_t *>(p8 + kg * g.IW);
+                const bool ld = row_ok && !(g.debug & 1);
+                r[kg].x = ld ? __ldg(p) : 0u; r[kg].y = ld ? __ldg(p + 1) : 0u;
             }
+            if (++kc == nchunks) { kc = 0; tile += gridDim.x; }
+        };
+        if (items > 0) load_next(nxt);
+        for (int i = 0; i < items; i++) {
+            #pragma unroll
+            for (int kg = 0; kg < kMyRows; kg++) cur[kg] = nxt[kg];
+            if (i + 1 < items) load_next(nxt);
+            mbar_wait(&empty[st], ph ^ 1);                          // slot free (first pass: returns at once)
+            uint8_t *abase = sA + st * kABytes;
+            if (!(g.debug & 16)) {
+            #pragma unroll
+            for (int kg = 0; kg < kMyRows; kg++)
+                *reinterpret_cast<uint4 *>(abase + swz((uint32_t)row, (uint32_t)(kg0 + kg))) = u8x8_to_f16x8(cur[kg].x, cur[kg].y);
+            }
+            if (!(g.debug & 64)) asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+            __syncwarp();
+            if ((tid & 31) == 0) mbar_arrive(&full[st]);
+            if (++st == kStages) { st = 0; ph ^= 1; }
         }
     } else if (warp == kMmaWarp) {
         // ===================== MMA issuer =====================
@@ -439,8 +425,7 @@ int launch_layer(stm_ctx *ctx, const void *in, const __nv_bfloat16 *w, const flo
 {
     static bool attr_done = false;
     const int nchunks = g.K / kChunkK;
-    size_t smem = (size_t)kStages * kABytes + (size_t)(kResidentW ? nchunks : kStages) * N * kChunkK * 2 + 1024
-                  + (g.mode == MODE_CONV1 ? 3 * 16 * 128 * 4 : 0);     // conv1's raw-byte ring (kRaw slots)
+    size_t smem = (size_t)kStages * kABytes + (size_t)(kResidentW ? nchunks : kStages) * N * kChunkK * 2 + 1024;
     if (!attr_done) {
         cudaFuncSetAttribute(stm_cnn_gemm_kernel<N, kResidentW, kStages, kProdWarps>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 2048);
         cudaFuncSetAttribute(stm_cnn_gemm_kernel<N, kResidentW, kStages, kProdWarps>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
