@@ -94,6 +94,18 @@ int stm_bfs(stm_ctx *ctx, const uint8_t *root_states, const uint8_t *root_stacks
             uint8_t *leaf_stacks, float *leaf_rewards, uint8_t *leaf_done, int32_t *leaf_lives,
             uint8_t *leaf_states, void *stream);
 
+/* Continue a tree from interior nodes: `n_nodes` nodes of level `level0` (their emulator states, observation
+ * stacks, accumulated UNCLIPPED discounted rewards, done flags and lives, e.g. a slice of what stm_bfs returned
+ * with clip_reward = 0) are expanded `depth_more` further levels exactly as stm_bfs would have expanded them:
+ * child order, frozen done nodes, reward weight gamma^(level0 + k), sign() of the total at the end when clip_reward.
+ * The reference has no counterpart (it always expands the whole tree on one device, cule_bfs.py:129-173); this is
+ * the leaf-block partition of one tree over several GPUs: every rank expands the first levels, keeps its
+ * contiguous block of level-`level0` nodes and resumes from there (softtreemax_b200/shard.py). */
+int stm_bfs_resume(stm_ctx *ctx, const uint8_t *node_states, const uint8_t *node_stacks, const float *node_rewards,
+                   const uint8_t *node_done, const int32_t *node_lives, int n_nodes, int level0, int depth_more,
+                   float gamma, int frameskip, int episodic_life, int clip_reward, uint8_t *leaf_stacks,
+                   float *leaf_rewards, uint8_t *leaf_done, int32_t *leaf_lives, uint8_t *leaf_states, void *stream);
+
 /* Same, with HOST buffers (pinned or pageable) for the roots and for rewards/done/lives: copies
  * the roots host->device, runs stm_bfs, copies the results device->host and synchronises
  * `stream` before returning.  This is the call a non-CUDA host program makes, and it mirrors the

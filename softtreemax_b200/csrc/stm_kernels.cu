@@ -759,7 +759,8 @@ int stm_frames(stm_ctx *ctx, const uint8_t *parent_stacks, uint8_t *child_stacks
 static int bfs_impl(stm_ctx *ctx, const uint8_t *root_states, const uint8_t *root_stacks, int n_roots, int depth,
                     float gamma, int frameskip, int episodic_life, int clip_reward, uint8_t *leaf_stacks,
                     float *leaf_rewards, uint8_t *leaf_done, int32_t *leaf_lives, uint8_t *leaf_states, void *stream,
-                    cudaEvent_t stacks_ready)
+                    cudaEvent_t stacks_ready, const float *node_rewards = nullptr, const uint8_t *node_done = nullptr,
+                    const int32_t *node_lives = nullptr, int level0 = 0)
 {
     if (!ctx || !root_states || !root_stacks || !leaf_stacks || !leaf_rewards || n_roots < 1 || depth < 1 || frameskip < 1)
         return fail(ctx, STM_ERR_ARG, "stm_bfs: bad argument");
@@ -788,16 +789,22 @@ static int bfs_impl(stm_ctx *ctx, const uint8_t *root_states, const uint8_t *roo
 
     // level 0 = the roots
     CUDA_TRY(ctx, cudaMemcpyAsync(ctx->pool_state[0], root_states, n_level[0] * STM_STATE_BYTES, cudaMemcpyDeviceToDevice, st));
-    stm_root_init_kernel<<<(n_roots + 127) / 128, 128, 0, st>>>(ctx->pool_state[0], ctx->pool_reward[0], ctx->pool_done[0],
-                                                               ctx->pool_lives[0], n_roots, ctx->gp);
-    ctx->launches++;
+    if (node_rewards) {                                   // resuming from interior nodes: their accumulated state comes in
+        CUDA_TRY(ctx, cudaMemcpyAsync(ctx->pool_reward[0], node_rewards, n_level[0] * sizeof(float), cudaMemcpyDeviceToDevice, st));
+        CUDA_TRY(ctx, cudaMemcpyAsync(ctx->pool_done[0], node_done, n_level[0], cudaMemcpyDeviceToDevice, st));
+        CUDA_TRY(ctx, cudaMemcpyAsync(ctx->pool_lives[0], node_lives, n_level[0] * sizeof(int32_t), cudaMemcpyDeviceToDevice, st));
+    } else {
+        stm_root_init_kernel<<<(n_roots + 127) / 128, 128, 0, st>>>(ctx->pool_state[0], ctx->pool_reward[0], ctx->pool_done[0],
+                                                                   ctx->pool_lives[0], n_roots, ctx->gp);
+        ctx->launches++;
+    }
     for (int k = 0; k < depth; k++) {
         int cur = k & 1, nxt = cur ^ 1;
         size_t n_src = n_level[k], n_dst = n_level[k + 1];
         if ((rc = launch_clone(ctx, ctx->pool_state[cur], ctx->pool_reward[cur], ctx->pool_done[cur], ctx->pool_lives[cur],
                                ctx->pool_state[nxt], ctx->pool_reward[nxt], ctx->pool_done[nxt], ctx->pool_lives[nxt],
                                (int)n_src, A, st))) return rc;
-        float weight = (float)pow((double)gamma, (double)k);
+        float weight = (float)pow((double)gamma, (double)(level0 + k));
         const uint8_t *pstack = k == 0 ? root_stacks : ctx->pool_stack[cur];
         uint8_t *cstack = k == depth - 1 ? leaf_stacks : ctx->pool_stack[nxt];
         // chunks are multiples of the tile size and of A, so "action = env % A" holds inside a chunk
@@ -829,6 +836,18 @@ int stm_bfs(stm_ctx *ctx, const uint8_t *root_states, const uint8_t *root_stacks
 {
     return bfs_impl(ctx, root_states, root_stacks, n_roots, depth, gamma, frameskip, episodic_life, clip_reward,
                     leaf_stacks, leaf_rewards, leaf_done, leaf_lives, leaf_states, stream, nullptr);
+}
+
+int stm_bfs_resume(stm_ctx *ctx, const uint8_t *node_states, const uint8_t *node_stacks, const float *node_rewards,
+                   const uint8_t *node_done, const int32_t *node_lives, int n_nodes, int level0, int depth_more,
+                   float gamma, int frameskip, int episodic_life, int clip_reward, uint8_t *leaf_stacks,
+                   float *leaf_rewards, uint8_t *leaf_done, int32_t *leaf_lives, uint8_t *leaf_states, void *stream)
+{
+    if (!node_rewards || !node_done || !node_lives || level0 < 0)
+        return fail(ctx, STM_ERR_ARG, "stm_bfs_resume: bad argument");
+    return bfs_impl(ctx, node_states, node_stacks, n_nodes, depth_more, gamma, frameskip, episodic_life, clip_reward,
+                    leaf_stacks, leaf_rewards, leaf_done, leaf_lives, leaf_states, stream, nullptr,
+                    node_rewards, node_done, node_lives, level0);
 }
 
 int stm_bfs_host(stm_ctx *ctx, const uint8_t *root_states, const uint8_t *root_stacks, int n_roots, int depth,

@@ -118,6 +118,25 @@ class Engine:
               self._h)
         return out
 
+    def bfs_resume(self, node_states, node_stacks, node_rewards, node_done, node_lives, level0, depth_more, gamma=0.99,
+                   frameskip=4, episodic_life=True, clip_reward=True, want_states=False):
+        """Continue a tree from `n` interior nodes of level `level0` (stm_bfs_resume): the leaf-block partition of
+        one tree over several GPUs (shard.py).  node_rewards are the UNCLIPPED accumulated rewards."""
+        n = node_states.shape[0]
+        L = n * self.n_actions ** depth_more
+        d = self.device
+        out = dict(stacks=torch.empty((L, 4, 84, 84), dtype=torch.uint8, device=d),
+                   rewards=torch.empty((L,), dtype=torch.float32, device=d),
+                   done=torch.empty((L,), dtype=torch.uint8, device=d),
+                   lives=torch.empty((L,), dtype=torch.int32, device=d),
+                   states=torch.empty((L, STATE_BYTES), dtype=torch.uint8, device=d) if want_states else None)
+        check(lib().stm_bfs_resume(self._h, _ptr(node_states), _ptr(node_stacks), _ptr(node_rewards), _ptr(node_done),
+                                   _ptr(node_lives), n, int(level0), int(depth_more), float(gamma), frameskip,
+                                   int(episodic_life), int(clip_reward), _ptr(out["stacks"]), _ptr(out["rewards"]),
+                                   _ptr(out["done"]), _ptr(out["lives"]), _ptr(out.get("states")), self._stream()),
+              self._h)
+        return out
+
     def bfs_host(self, root_states, root_stacks, depth, gamma=0.99, frameskip=4, episodic_life=True,
                  clip_reward=True, out=None, stacks_on_device=False):
         """Host-buffer entry point: roots come from host memory (numpy arrays or pinned CPU tensors),

@@ -281,3 +281,29 @@ def test_reset_states_match_oracle(orc, engines):
         torch.cuda.synchronize()
         want = orc.Game(name).reset()
         assert np.array_equal(st.cpu().numpy(), np.repeat(want[None], 3, 0))
+
+
+@pytest.mark.parametrize("name,depth,worlds", [("synth_breakout", 3, (1, 2, 3, 5, 8, 20)), ("synth_pong", 2, (2, 4, 7)),
+                                               ("synth_pacman", 2, (2, 9, 12))])
+def test_leaf_blocks_of_one_tree_equal_the_whole_tree(orc, engines, name, depth, worlds):
+    """Leaf-block partition (shard.expand_leaf_block / stm_bfs_resume): the blocks of all ranks, concatenated,
+    are the tree stm_bfs expands in one piece — stacks, rewards (clipped and raw), done, lives — also when the
+    blocks resume below nodes that are already done (frozen)."""
+    from softtreemax_b200 import shard
+    g = orc.Game(name)
+    eng = engines(name)
+    roots, stacks = orc.make_roots(g, 6, seed=33, base_steps=30, spread=400)      # long traces: some roots near game over
+    for r in range(6):
+        rs, rk = dev(roots[r:r + 1], eng), dev(stacks[r:r + 1], eng)
+        for clip in (True, False):
+            want = eng.bfs(rs, rk, depth, clip_reward=clip)
+            A = eng.n_actions
+            for world in worlds:
+                parts = [shard.expand_leaf_block(eng, rs[0], rk[0], depth, rank, world, clip_reward=clip) for rank in range(world)]
+                assert parts[0]["leaf_lo"] == 0 and parts[-1]["leaf_hi"] == A ** depth
+                assert all(parts[i]["leaf_hi"] == parts[i + 1]["leaf_lo"] for i in range(world - 1))
+                for key in ("stacks", "rewards", "done", "lives"):
+                    got = torch.cat([p[key] for p in parts])
+                    assert torch.equal(got, want[key]), (name, r, clip, world, key)
+                fa = torch.cat([p["first_action"] for p in parts])
+                assert torch.equal(fa.cpu(), torch.arange(A ** depth) // (A ** (depth - 1)))

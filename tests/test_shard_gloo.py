@@ -78,3 +78,40 @@ def _grad_worker(rank, world, port):
 
 def test_gradient_allreduce_matches_full_batch_over_gloo():
     mp.spawn(_grad_worker, args=(2, 29688), nprocs=2, join=True)
+
+
+def _leaf_worker(rank, world, port, A, depth, cumulative):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from oracle import policy_ref
+        g = torch.Generator().manual_seed(5)
+        L = A ** depth
+        head = 3 * torch.randn(L, A, generator=g)
+        rew = torch.randint(-2, 3, (L,), generator=g).float()
+        val_coef, beta = 0.99 ** depth, 1.7
+        _, want, _ = policy_ref.softtreemax_logits(head[None], rew[None], A, val_coef, beta, 1.0, 0.001, cumulative)
+        # this rank's block of the level-k nodes -> its contiguous block of leaves
+        k = shard.split_level(A, depth, world)
+        lo, cnt = shard.shard_range(A ** k, rank, world)
+        per = A ** (depth - k)
+        sl = slice(lo * per, (lo + cnt) * per)
+        fa = torch.arange(L)[sl] // (A ** (depth - 1))
+        stat, count = shard.partial_action_stats(head[sl], rew[sl], fa, A, val_coef, beta, cumulative)
+        raw = shard.combine_action_stats(stat, count, cumulative)
+        assert torch.allclose(raw, want[0], atol=2e-5), (rank, raw, want[0])
+        dist.barrier()
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world,A,depth,cumulative", [(2, 6, 3, False), (3, 4, 2, False), (2, 4, 3, True), (3, 9, 2, False)])
+def test_leaf_block_partial_logits_over_gloo(world, A, depth, cumulative):
+    """One tree split over ranks by leaf blocks: the all-gathered per-first-action partials reproduce the
+    full-tree raw logits of the restatement (actor_critic_ts.py:66-86)."""
+    mp.spawn(_leaf_worker, args=(world, 29700 + world * 7 + A + depth, A, depth, cumulative), nprocs=world, join=True)
+
+
+def test_split_level():
+    assert shard.split_level(6, 3, 1) == 0 and shard.split_level(6, 3, 2) == 1 and shard.split_level(6, 3, 8) == 2
+    assert shard.split_level(4, 2, 64) == 2            # more ranks than leaves: capped, some ranks own nothing
