@@ -27,7 +27,11 @@ def resolve(env_name):
 
 
 def load(name):
-    """-> (GameDesc, rom bytes, descriptor dict)"""
+    """-> (GameDesc, rom bytes, descriptor dict).  `name`: a bundled cartridge / an env_name alias, or a
+    (descriptor dict, rom bytes) pair for a user-supplied image (same keys as roms/games.json)."""
+    if isinstance(name, tuple):
+        g, rom = name
+        return make_desc(g, len(rom)), bytes(rom), g
     games = json.load(open(os.path.join(ROM_DIR, "games.json")))
     g = games[resolve(name)]
     rom = open(os.path.join(ROM_DIR, g["file"]), "rb").read()

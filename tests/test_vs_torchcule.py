@@ -1,0 +1,56 @@
+"""Conditional upgrade of the parity claim: compare the CUDA emulator with the reference's own
+emulator, CuLE (`torchcule`, NVLabs/cule branch `bfs`), on a real cartridge.
+
+Neither torchcule nor any Atari ROM exists in this image (no network), so this file SKIPS here and on the GPU box;
+until someone runs it where both exist, parity with the reference's emulator stays "unpinned" (DESIGN.md §2).
+To run it: install torchcule, export STM_ROM_DIR=<directory holding breakout.bin> and run
+`python -m pytest tests/test_vs_torchcule.py -m gpu`.
+"""
+import os
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+torchcule = pytest.importorskip("torchcule", reason="the reference's emulator (NVLabs/cule, branch bfs) is not installed")
+ROM_DIR = os.environ.get("STM_ROM_DIR")
+if not ROM_DIR or not os.path.exists(os.path.join(ROM_DIR, "breakout.bin")):
+    pytest.skip("STM_ROM_DIR/breakout.bin not provided", allow_module_level=True)
+
+# ALE's decoding of Breakout (ale/games/supported/Breakout.cpp): score = BCD in RAM 77 (tens, ones) and the low
+# nibble of RAM 76 (hundreds); lives in RAM 57; the episode ends when the lives reach zero; paddle controller.
+BREAKOUT = dict(file="breakout.bin", bank_scheme=0, controller=1, actions=[0, 1, 3, 4], score_addr=[255, 76, 77],
+                score2_addr=[255, 255, 255], lives_addr=57, lives_shift=0, lives_mask=255, term_addr=57, term_mask=255,
+                term_value=0)
+
+
+def test_ram_rewards_done_match_cule_on_breakout():
+    import torch
+    from torchcule.atari import Env as CuleEnv
+    from softtreemax_b200.engine import Engine
+    rom = open(os.path.join(ROM_DIR, "breakout.bin"), "rb").read()
+    eng = Engine((BREAKOUT, rom))
+    N, steps = 8, 300
+    ref = CuleEnv("BreakoutNoFrameskip-v4", N, color_mode="gray", repeat_prob=0.0, device="cpu", rescale=True,
+                  episodic_life=True, frameskip=4)
+    ref.reset(initial_steps=1, verbose=False)
+    blobs, rewards, done, lives = eng.reset_states(N)
+    stacks = torch.zeros((N, 4, 84, 84), dtype=torch.uint8, device=eng.device)
+    noop = torch.zeros(N, dtype=torch.uint8, device=eng.device)
+    eng.step(blobs, rewards, done, lives, actions=noop, frameskip=4, episodic_life=True, weight=1.0, render=True)
+    stacks = eng.frames(stacks, N, fanout=1)
+    rng = np.random.default_rng(0)
+    for t in range(steps):
+        a = rng.integers(0, 4, N)
+        obs, r, d, info = ref.step(torch.as_tensor(a, dtype=torch.uint8))
+        rewards.zero_()
+        done.zero_()
+        eng.step(blobs, rewards, done, lives, actions=torch.as_tensor(a, dtype=torch.uint8, device=eng.device), frameskip=4,
+                 episodic_life=True, weight=1.0, render=True)
+        stacks = eng.frames(stacks, N, fanout=1)
+        assert np.array_equal(blobs[:, :128].cpu().numpy(), ref.ram[:, :128].cpu().numpy()), f"RIOT RAM differs at step {t}"
+        assert np.array_equal(rewards.cpu().numpy(), r.cpu().numpy().astype(np.float32)), f"rewards differ at step {t}"
+        assert np.array_equal(done.cpu().numpy().astype(bool), d.cpu().numpy().astype(bool)), f"done differs at step {t}"
+        assert np.array_equal(stacks[:, 3].cpu().numpy(), obs[..., 0].cpu().numpy()), f"84x84 frame differs at step {t}"
+    eng.close()
