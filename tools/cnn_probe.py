@@ -1,3 +1,12 @@
+"""Time K4 (stm_cnn_forward) alone on 32 768 random observation stacks.
+
+STM_CNN_DEBUG (a bit mask read by stm_cnn_forward, timing experiments only — results are wrong when set) switches
+stages of the kernel off to see what the rest costs: 1 producers skip the global loads, 2 the MMA thread skips the
+MMAs, 4 the epilogue skips the stores, 8 run conv1 only, 16 conv1 producers skip convert + store, 32 the epilogue
+skips the TMEM loads, 64 no proxy fence, 128 plain mbarrier arrives instead of tcgen05.commit.
+
+    STM_CNN_DEBUG=8 python tools/cnn_probe.py
+"""
 import sys, torch, os
 sys.path.insert(0,'.')
 from softtreemax_b200.engine import Engine
