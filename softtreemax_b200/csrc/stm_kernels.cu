@@ -464,7 +464,7 @@ int ensure_scratch(stm_ctx *ctx, int n_envs)
 // the step kernel for this ctx's cartridge: its translated core if the library has one, else the interpreter
 void launch_step_kernel(const stm_ctx *ctx, int blocks, size_t smem, cudaStream_t st, const StepArgs &a)
 {
-    int k = 0; (void)k;
+    [[maybe_unused]] int k = 0;
 #define STM_LAUNCH(name) if (ctx->xl == ++k) { stm_step_kernel<stm::Xl_##name><<<blocks, kStepThreads, smem, st>>>(a); return; }
     STM_XL_LIST(STM_LAUNCH)
 #undef STM_LAUNCH
@@ -618,7 +618,7 @@ int stm_ctx_create(stm_ctx **out, const stm_game_desc *desc, const uint8_t *rom,
                 const char *on = getenv("STM_XLATE");
                 const char *no = (on && atoi(on)) ? "0" : "1";
                 const uint32_t h = stm::rom_hash(rom, desc->rom_size);
-                int k = 0; (void)k; (void)h; (void)no;
+                [[maybe_unused]] int k = 0; (void)h; (void)no;
 #define STM_MATCH(name) \
                 ++k; \
                 if (!(no && atoi(no)) && h == stm::Xl_##name::kRomHash && desc->rom_size == stm::Xl_##name::kRomSize) { \
@@ -640,7 +640,7 @@ int stm_ctx_create(stm_ctx **out, const stm_game_desc *desc, const uint8_t *rom,
         if (pct > 100) pct = 100;
         CUDA_TRY(ctx, set_step_attrs<stm::InterpCore>(smem, pct));
         {
-            int k = 0; (void)k;
+            [[maybe_unused]] int k = 0;
 #define STM_ATTR(name) if (ctx->xl == ++k) CUDA_TRY(ctx, set_step_attrs<stm::Xl_##name>(smem, pct));
             STM_XL_LIST(STM_ATTR)
 #undef STM_ATTR
