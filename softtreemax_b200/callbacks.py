@@ -36,7 +36,8 @@ class TrainingCallback:
                "train/episodic_reward": self.total_rewards, "train/episodic_length": self.episode_length}
         for name in ("alpha", "beta"):
             if hasattr(pol, name):
-                rec["train/" + name] = float(getattr(pol, name))
+                v = getattr(pol, name)
+                rec["train/" + name] = float(v.detach()) if hasattr(v, "detach") else float(v)
         grad_var = 0.0
         for name, hist in pol.gradients_history.items():          # :46-50
             if len(hist) > 1:
