@@ -71,7 +71,7 @@ __device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity)
     asm volatile(
         "{\n\t.reg .pred p;\n\t"
         "WAIT_%=:\n\t"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1, 0x40;\n\t"
         "@p bra DONE_%=;\n\t"
         "bra WAIT_%=;\n\t"
         "DONE_%=:\n\t}"
@@ -108,6 +108,33 @@ __device__ __forceinline__ void umma(uint32_t tmem_d, uint64_t adesc, uint64_t b
         "setp.ne.b32 p, %4, 0;\n\t"
         "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
         :: "r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+}
+// The same with the descriptors as (low word, high word) pairs.  The high words are constants and the low words
+// differ between MMAs only by small immediates (start address in 16-byte units), so an unrolled issue loop costs an
+// add or two per MMA instead of rebuilding 64-bit descriptors — the issuing thread is ONE lane and every instruction
+// it spends per tile is serial time of the whole CTA (it was ~800 instructions per 36-MMA tile: the bottleneck).
+constexpr uint32_t kDescHi = (uint32_t)(1024 >> 4) | (1u << 14) | (2u << 29);      // SBO, version, 128B swizzle
+__device__ __forceinline__ uint32_t desc_lo(uint32_t saddr) { return ((saddr & 0x3FFFF) >> 4) | (1u << 16); }
+template <bool kAccumulate>
+__device__ __forceinline__ void umma_lo(uint32_t tmem_d, uint32_t a_lo, uint32_t b_lo, uint32_t idesc)
+{
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t.reg .b64 da, db;\n\t"
+        "setp.ne.b32 p, %5, 0;\n\t"
+        "mov.b64 da, {%1, %4};\n\t"
+        "mov.b64 db, {%2, %4};\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %3, p;\n\t}"
+        :: "r"(tmem_d), "r"(a_lo), "r"(b_lo), "r"(idesc), "r"(kDescHi), "n"(kAccumulate ? 1 : 0) : "memory");
+}
+__device__ __forceinline__ void umma_lo_rt(uint32_t tmem_d, uint32_t a_lo, uint32_t b_lo, uint32_t idesc, uint32_t accumulate)
+{
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t.reg .b64 da, db;\n\t"
+        "setp.ne.b32 p, %5, 0;\n\t"
+        "mov.b64 da, {%1, %4};\n\t"
+        "mov.b64 db, {%2, %4};\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %3, p;\n\t}"
+        :: "r"(tmem_d), "r"(a_lo), "r"(b_lo), "r"(idesc), "r"(kDescHi), "r"(accumulate) : "memory");
 }
 __device__ __forceinline__ void umma_commit(uint64_t *bar)
 {
@@ -312,6 +339,7 @@ stm_cnn_gemm_kernel(const void *__restrict__ in, const __nv_bfloat16 *__restrict
         // ===================== MMA issuer =====================
         if ((tid & 31) == 0) {
             const uint32_t idesc = make_idesc(N, g.f16);
+            const uint32_t a_lo0 = desc_lo(smem_u32(sA)), b_lo0 = desc_lo(smem_u32(sB));          // + start address in 16-byte units
             uint32_t it = 0, t = 0;
             for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x, t++) {
                 const uint32_t buf = t & 1;
@@ -322,12 +350,13 @@ stm_cnn_gemm_kernel(const void *__restrict__ in, const __nv_bfloat16 *__restrict
                     const uint32_t st = it % kStages, ph = (it / kStages) & 1;
                     mbar_wait(&full[st], ph);
                     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-                    const uint32_t a0 = smem_u32(sA + st * kABytes);
-                    const uint32_t b0 = smem_u32(sB + (kResidentW ? (size_t)kc : (size_t)st) * kBBytes);
+                    const uint32_t a_lo = a_lo0 + st * (uint32_t)(kABytes >> 4);
+                    const uint32_t b_lo = b_lo0 + (kResidentW ? (uint32_t)kc : st) * (uint32_t)(kBBytes >> 4);
                     if (!(g.debug & 2)) {
-                    #pragma unroll
-                    for (int j = 0; j < kChunkK / 16; j++)
-                        umma(tmem_d, make_desc(a0 + j * 32), make_desc(b0 + j * 32), idesc, (kc | j) ? 1u : 0u);
+                        umma_lo_rt(tmem_d, a_lo, b_lo, idesc, kc ? 1u : 0u);
+                        #pragma unroll
+                        for (int j = 1; j < kChunkK / 16; j++)
+                            umma_lo<true>(tmem_d, a_lo + 2u * j, b_lo + 2u * j, idesc);
                     }
                     if (g.debug & 128) mbar_arrive(&empty[st]); else
                     umma_commit(&empty[st]);                        // frees the slot when these MMAs are done
@@ -394,6 +423,246 @@ stm_cnn_gemm_kernel(const void *__restrict__ in, const __nv_bfloat16 *__restrict
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" :: "r"(tmem_base), "r"(kCols) : "memory");
 }
 
+// ---------------------------------------------------------------------------------------------------------
+// Window GEMM for the stride-1 / stride-2 convolutions on bf16 NHWC activations (conv2, conv3).
+//
+// View the input of an image as rows of 128 bytes (conv3: one pixel = 64 channels; conv2: two pixels of 32
+// channels) and number the output positions on the INPUT grid ("virtual" rows: conv3 9x9 per image of which
+// 7x7 are real outputs, conv2 10x20 of which 9x9): then the im2col row of virtual output v for kernel tap t is
+// input row v + off[t], for every v — the A operand of tap t is the SAME shared-memory tile as for every other
+// tap, started off[t] rows further in.  The tensor core takes such a start address (128-byte aligned inside a
+// 128B-swizzled tile whose pieces are keyed by the absolute row: probed, tools/shift_probe.py), so a tile of 128
+// virtual rows needs ONE load of 160 contiguous input rows (20 KB) instead of 8 or 9 gathered 16 KB slices: the
+// producers issue 10 copies per thread and tile instead of 64-72, and the L2 -> shared traffic drops 6-7x.
+// The price is tensor work on the virtual rows that are not outputs (x2.5 for conv2, x1.65 for conv3) — the
+// tensor pipe was 9 % busy — and an epilogue that skips them.
+// ---------------------------------------------------------------------------------------------------------
+struct WinGeom {
+    int V, VW, OH, OW;       // virtual rows per image, virtual grid width, real output height / width
+    int recip_vw;            // ceil(65536 / VW)
+    int nchunks;             // kernel taps = 64-wide K slices
+    int off[9];              // input-row offset of every tap
+    int relu;
+    int debug;               // timing experiments only (STM_CNN_DEBUG): 1 no loads, 2 no MMAs, 4 no epilogue math/stores, 32 no TMEM loads
+};
+constexpr int kWinRows = 160, kWinBytes = kWinRows * 128;          // 128 virtual rows + 32 rows of halo
+
+// tap -> input-row offset, known at compile time so that the issue loop adds immediates (kConv = 2: conv2, 3: conv3)
+template <int kConv> __host__ __device__ constexpr int win_taps() { return kConv == 2 ? 8 : 9; }
+template <int kConv> __host__ __device__ constexpr int win_off(int kc) { return kConv == 2 ? (kc >> 1) * 10 + (kc & 1) : (kc / 3) * 9 + kc % 3; }
+
+template <int kStages, int kConv>
+__global__ void __launch_bounds__(288, 1)
+stm_cnn_window_kernel(const __nv_bfloat16 *__restrict__ in, const __nv_bfloat16 *__restrict__ wt, const float *__restrict__ bias,
+                      __nv_bfloat16 *__restrict__ out, uint32_t M_total, WinGeom g)
+{
+    constexpr int N = 64, kBBytes = N * kChunkK * 2;
+    extern __shared__ __align__(1024) uint8_t smem_raw[];
+    uint8_t *smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+    uint8_t *sW = smem;                                    // kStages windows of 20 KB
+    uint8_t *sB = smem + kStages * kWinBytes;              // nchunks x 8 KB, resident
+    // kAcc accumulators in tensor memory (64 columns each): the MMA thread may run kAcc tiles ahead of the epilogue,
+    // which hides the latency of the tfull -> epilogue -> tempty hand-off (measured: ~1.5 us per round trip)
+    constexpr int kAcc = 8;
+    __shared__ __align__(8) uint64_t full[kStages], empty[kStages], tfull[kAcc], tempty[kAcc];
+    __shared__ uint32_t tmem_base_s;
+    __shared__ float sbias[N];
+    const int tid = threadIdx.x, warp = tid >> 5;
+    const uint32_t ntiles = (M_total + kTileM - 1) / kTileM;
+    constexpr uint32_t kCols = kAcc * N;                  // 512: the whole tensor memory of the SM (one CTA per SM)
+    if (tid < N) sbias[tid] = bias[tid];
+
+    if (warp == 8) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;"
+                     :: "r"(smem_u32(&tmem_base_s)), "r"(kCols) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    if (tid == 0) {
+        for (int i = 0; i < kStages; i++) { mbar_init(&full[i], 4); mbar_init(&empty[i], 1); }
+        for (int i = 0; i < kAcc; i++) { mbar_init(&tfull[i], 1); mbar_init(&tempty[i], 4); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    for (int kc = 0; kc < g.nchunks; kc++) {
+        const uint4 *wsrc = reinterpret_cast<const uint4 *>(wt + (size_t)kc * N * kChunkK);
+        uint4 *wdst = reinterpret_cast<uint4 *>(sB + (size_t)kc * kBBytes);
+        for (int i = tid; i < kBBytes / 16; i += 288) wdst[i] = __ldg(wsrc + i);
+    }
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const uint32_t tmem_base = tmem_base_s;
+
+    if (warp < 4) {
+        // ===================== producers: one contiguous 160-row window per tile =====================
+        constexpr int kDepth = kStages - 1;
+        const int my_tiles = blockIdx.x < ntiles ? (int)((ntiles - blockIdx.x + gridDim.x - 1) / gridDim.x) : 0;
+        uint32_t tile = blockIdx.x, st = 0, ph = 0, st_pub = 0;
+        for (int i = 0; i < my_tiles + kDepth && !(g.debug & 2048); i++) {
+            if (i < my_tiles) {
+                mbar_wait(&empty[st], ph ^ 1);
+                const uint32_t v0 = tile * kTileM, dst0 = smem_u32(sW + st * kWinBytes);
+                #pragma unroll
+                for (int k = 0; k < kWinRows * 8 / 128; k++) {
+                    const uint32_t idx = (uint32_t)tid + 128u * k, r = idx >> 3, pc = idx & 7u;
+                    const uint32_t row = v0 + r;
+                    const bool ok = row < M_total && !(g.debug & 1);    // the input has exactly M_total rows
+                    const __nv_bfloat16 *src = in + (size_t)(ok ? row : 0u) * 64 + pc * 8;
+                    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;"
+                                 :: "r"(dst0 + swz(r, pc)), "l"(src), "r"(ok ? 16u : 0u) : "memory");
+                }
+                tile += gridDim.x;
+                if (++st == kStages) { st = 0; ph ^= 1; }
+            }
+            asm volatile("cp.async.commit_group;" ::: "memory");
+            if (i >= kDepth) {
+                asm volatile("cp.async.wait_group %0;" :: "n"(kDepth) : "memory");
+                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                __syncwarp();
+                if ((tid & 31) == 0) mbar_arrive(&full[st_pub]);
+                if (++st_pub == kStages) st_pub = 0;
+            }
+        }
+    } else if (warp == 8) {
+        // ===================== MMA issuer: every tap reads the same window, started off[tap] rows in =====================
+        if ((tid & 31) == 0) {
+            const uint32_t idesc = make_idesc(N, 0);
+            const uint32_t b_lo0 = desc_lo(smem_u32(sB));
+            uint32_t st = 0, ph = 0, t = 0;
+            for (uint32_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x, t++) {
+                const uint32_t buf = t % kAcc;
+                if (!(g.debug & 1024)) mbar_wait(&tempty[buf], ((t / kAcc) & 1) ^ 1);
+                if (!(g.debug & 2048)) mbar_wait(&full[st], ph);
+                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                const uint32_t tmem_d = tmem_base + buf * N;
+                const uint32_t a_lo0 = desc_lo(smem_u32(sW + st * kWinBytes));
+                if (!(g.debug & 2)) {
+                    #pragma unroll
+                    for (int kc = 0; kc < win_taps<kConv>(); kc++) {
+                        #pragma unroll
+                        for (int j = 0; j < kChunkK / 16; j++) {
+                            const uint32_t a_lo = a_lo0 + (uint32_t)(win_off<kConv>(kc) * 8 + 2 * j), b_lo = b_lo0 + (uint32_t)(kc * (kBBytes >> 4) + 2 * j);
+                            if (kc == 0 && j == 0) umma_lo<false>(tmem_d, a_lo, b_lo, idesc);
+                            else umma_lo<true>(tmem_d, a_lo, b_lo, idesc);
+                        }
+                    }
+                }
+                if (!(g.debug & 2048)) umma_commit(&empty[st]);
+                if (!(g.debug & 1024)) umma_commit(&tfull[buf]);
+                if (++st == kStages) { st = 0; ph ^= 1; }
+            }
+        }
+    } else {
+        // ===================== epilogue: only the virtual rows that are real outputs are stored =====================
+        const int et = tid - 128, ew = et >> 5;
+        uint32_t t = 0;
+        const uint32_t V = (uint32_t)g.V, VW = (uint32_t)g.VW, P = (uint32_t)(g.OH * g.OW);
+        for (uint32_t tile = blockIdx.x; tile < ntiles && !(g.debug & 1024); tile += gridDim.x, t++) {
+            const uint32_t buf = t % kAcc;
+            mbar_wait(&tfull[buf], (t / kAcc) & 1);
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            const uint32_t v = tile * kTileM + et;
+            const uint32_t img = v / V, q = v - img * V;
+            const uint32_t oy = (q * (uint32_t)g.recip_vw) >> 16, ox = q - oy * VW;
+            const bool valid = v < M_total && oy < (uint32_t)g.OH && ox < (uint32_t)g.OW && !(g.debug & 4);
+            __nv_bfloat16 *orow = out + ((size_t)img * P + oy * (uint32_t)g.OW + ox) * N;
+            const uint32_t taddr = tmem_base + buf * N + ((uint32_t)(ew * 32) << 16);
+            #pragma unroll 1
+            for (int c0 = 0; c0 < N; c0 += 16) {
+                if (g.debug & 32) break;
+                uint32_t r[16];
+                asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+                             "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+                             : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+                               "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+                             : "r"(taddr + (uint32_t)c0));
+                asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+                if (valid) {
+                    uint32_t pk[8];
+                    #pragma unroll
+                    for (int j = 0; j < 8; j++) {
+                        float x0 = __uint_as_float(r[2 * j]) + sbias[c0 + 2 * j];
+                        float x1 = __uint_as_float(r[2 * j + 1]) + sbias[c0 + 2 * j + 1];
+                        if (g.relu) { x0 = fmaxf(x0, 0.f); x1 = fmaxf(x1, 0.f); }
+                        __nv_bfloat162 t2 = __floats2bfloat162_rn(x0, x1);
+                        pk[j] = *reinterpret_cast<uint32_t *>(&t2);
+                    }
+                    uint4 *o = reinterpret_cast<uint4 *>(orow + c0);
+                    o[0] = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+                    o[1] = make_uint4(pk[4], pk[5], pk[6], pk[7]);
+                }
+            }
+            asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+            __syncwarp();
+            if ((tid & 31) == 0) mbar_arrive(&tempty[buf]);
+        }
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    if (warp == 8)
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" :: "r"(tmem_base), "r"(kCols) : "memory");
+}
+
+// Probe for the "shifted window" operand trick: a [rows][64] bf16 matrix sits in shared memory in the 128-byte
+// swizzled K-major layout (piece position keyed by the ABSOLUTE row, i.e. by the address); the MMA's A operand is
+// the 128-row window that starts `shift` rows in.  Does the tensor core read it correctly when the start address
+// is only 128-byte aligned, and what must the descriptor's base-offset field (bits 49..51) hold?
+__global__ void __launch_bounds__(128)
+stm_shift_probe_kernel(const __nv_bfloat16 *__restrict__ A, const __nv_bfloat16 *__restrict__ B, float *__restrict__ out,
+                       int rows, int shift, int base_off)
+{
+    extern __shared__ __align__(1024) uint8_t smem_raw[];
+    uint8_t *smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+    uint8_t *sA = smem;                                  // rows x 128 B
+    uint8_t *sB = smem + 32 * 1024;                      // 64 x 128 B
+    __shared__ __align__(8) uint64_t done;
+    __shared__ uint32_t tmem_base_s;
+    const int tid = threadIdx.x, warp = tid >> 5;
+    for (int i = tid; i < rows * 8; i += 128) {
+        int r = i >> 3, pc = i & 7;
+        *reinterpret_cast<uint4 *>(sA + swz(r, pc)) = *reinterpret_cast<const uint4 *>(A + (size_t)r * 64 + pc * 8);
+    }
+    for (int i = tid; i < 64 * 8; i += 128) {
+        int r = i >> 3, pc = i & 7;
+        *reinterpret_cast<uint4 *>(sB + swz(r, pc)) = *reinterpret_cast<const uint4 *>(B + (size_t)r * 64 + pc * 8);
+    }
+    if (warp == 0) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" :: "r"(smem_u32(&tmem_base_s)), "r"(64) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    if (tid == 0) { mbar_init(&done, 1); asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const uint32_t tmem = tmem_base_s;
+    if (tid == 0) {
+        const uint32_t idesc = make_idesc(64, 0);
+        const uint32_t a0 = smem_u32(sA) + (uint32_t)shift * 128u, b0 = smem_u32(sB);
+        for (int j = 0; j < 4; j++) {
+            uint64_t ad = make_desc(a0 + j * 32) | ((uint64_t)(base_off & 7) << 49);
+            umma(tmem, ad, make_desc(b0 + j * 32), idesc, j ? 1u : 0u);
+        }
+        umma_commit(&done);
+    }
+    mbar_wait(&done, 0);
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const uint32_t taddr = tmem + ((uint32_t)(warp * 32) << 16);
+    for (int c0 = 0; c0 < 64; c0 += 16) {
+        uint32_t r[16];
+        asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+                     "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+                     : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+                       "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+                     : "r"(taddr + (uint32_t)c0));
+        asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+        for (int j = 0; j < 16; j++) out[(size_t)tid * 64 + c0 + j] = __uint_as_float(r[j]);
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" :: "r"(tmem), "r"(64) : "memory");
+}
+
 // fp32 torch-layout weights (n_real, K) -> bf16, K reordered (k = s*C + c <- column c*KHW + s), zero padded
 // to N rows, tiled per 64-wide K slice in the 128-byte-swizzled K-major layout the kernel uses:
 //   element (n, k): slice k/64, byte offset n*128 + ((((k%64)/8) ^ (n%8)) * 16) + (k%8)*2
@@ -438,6 +707,33 @@ int launch_layer(stm_ctx *ctx, const void *in, const __nv_bfloat16 *w, const flo
     int per_sm = smem <= 110 * 1024 ? 2 : 1;                         // persistent: fill every SM, CTAs loop over tiles
     long long grid = tiles < 148LL * per_sm ? tiles : 148LL * per_sm;
     stm_cnn_gemm_kernel<N, kResidentW, kStages, kProdWarps><<<(unsigned)grid, cta_threads(kProdWarps), smem, st>>>(in, w, b, out, M, g, n_off, N_total);
+    stm_internal_count_launch(ctx);
+    cudaError_t e = cudaGetLastError();
+    return e == cudaSuccess ? STM_OK : stm_internal_fail(ctx, STM_ERR_CUDA, cudaGetErrorString(e));
+}
+
+template <int kConv>
+int launch_window(stm_ctx *ctx, const __nv_bfloat16 *in, const __nv_bfloat16 *w, const float *b, __nv_bfloat16 *out,
+                  long long n_images, const WinGeom &g, cudaStream_t st)
+{
+    constexpr int kStages = 6;
+    static bool attr_done = false;
+    if (!attr_done) {
+        cudaFuncSetAttribute(stm_cnn_window_kernel<kStages, kConv>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 2048);
+        cudaFuncSetAttribute(stm_cnn_window_kernel<kStages, kConv>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+        attr_done = true;
+    }
+    const long long M = n_images * g.V;
+    if (M >= (1LL << 31) - kTileM) return stm_internal_fail(ctx, STM_ERR_ARG, "stm_cnn: too many rows for one pass");
+    for (int q = 0; q < g.V; q++)
+        if (((q * g.recip_vw) >> 16) != q / g.VW) return stm_internal_fail(ctx, STM_ERR_ARG, "stm_cnn: reciprocal of VW is not exact");
+    if (g.nchunks != win_taps<kConv>()) return stm_internal_fail(ctx, STM_ERR_ARG, "stm_cnn: tap count");
+    for (int c = 0; c < g.nchunks; c++)
+        if (g.off[c] != win_off<kConv>(c) || g.off[c] + kTileM > kWinRows) return stm_internal_fail(ctx, STM_ERR_ARG, "stm_cnn: tap offsets");
+    const size_t smem = (size_t)kStages * kWinBytes + (size_t)g.nchunks * 64 * kChunkK * 2 + 1024;
+    const long long tiles = (M + kTileM - 1) / kTileM;
+    const long long grid = tiles < 148 ? tiles : 148;
+    stm_cnn_window_kernel<kStages, kConv><<<(unsigned)grid, 288, smem, st>>>(in, w, b, out, (uint32_t)M, g);
     stm_internal_count_launch(ctx);
     cudaError_t e = cudaGetLastError();
     return e == cudaSuccess ? STM_OK : stm_internal_fail(ctx, STM_ERR_CUDA, cudaGetErrorString(e));
@@ -511,6 +807,17 @@ int stm_cnn_set_weights(stm_ctx *ctx, const float *conv1_w, const float *conv1_b
     return e == cudaSuccess ? STM_OK : stm_internal_fail(ctx, STM_ERR_CUDA, cudaGetErrorString(e));
 }
 
+int stm_debug_shift_probe(stm_ctx *ctx, const void *A, const void *B, float *out, int rows, int shift, int base_off, void *stream)
+{
+    if (!ctx || !A || !B || !out || rows < 128 || rows > 250 || shift < 0 || shift + 128 > rows)
+        return stm_internal_fail(ctx, STM_ERR_ARG, "stm_debug_shift_probe: bad argument");
+    cudaFuncSetAttribute(stm_shift_probe_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 48 * 1024);
+    stm_shift_probe_kernel<<<1, 128, 41 * 1024 + 1024, (cudaStream_t)stream>>>(
+        reinterpret_cast<const __nv_bfloat16 *>(A), reinterpret_cast<const __nv_bfloat16 *>(B), out, rows, shift, base_off);
+    cudaError_t e = cudaGetLastError();
+    return e == cudaSuccess ? STM_OK : stm_internal_fail(ctx, STM_ERR_CUDA, cudaGetErrorString(e));
+}
+
 int stm_cnn_forward(stm_ctx *ctx, const uint8_t *obs, long long n, float *heads, void *stream)
 {
     if (!ctx || !obs || !heads || n < 0) return stm_internal_fail(ctx, STM_ERR_ARG, "stm_cnn_forward: bad argument");
@@ -535,12 +842,22 @@ int stm_cnn_forward(stm_ctx *ctx, const uint8_t *obs, long long n, float *heads,
         long long c = n - i0 < chunk ? n - i0 : chunk;
         int rc;
         LayerGeom g1 = { MODE_CONV1, 400, 20, 84, 84, 4, 0, 4, 256, 32, 1, 0, 1.0f / 255.0f, (65536 + 20 - 1) / 20, 1, dbg };
-        if ((rc = launch_layer<32, true, 4, 8>(ctx, obs + (size_t)i0 * 4 * 84 * 84, s->w[0], s->b[0], s->act1, c * 400, g1, 0, 32, st))) return rc;
+        if (!(dbg & 512) && (rc = launch_layer<32, true, 4, 8>(ctx, obs + (size_t)i0 * 4 * 84 * 84, s->w[0], s->b[0], s->act1, c * 400, g1, 0, 32, st))) return rc;
         if (dbg & 8) continue;                                       // timing experiments: conv1 alone
-        LayerGeom g2 = { MODE_NHWC, 81, 9, 20, 20, 32, 4 * 32, 2, 512, 64, 1, 0, 1.0f, (65536 + 9 - 1) / 9, 0, dbg };
-        if ((rc = launch_layer<64, true, 8, 4>(ctx, s->act1, s->w[1], s->b[1], s->act2, c * 81, g2, 0, 64, st))) return rc;
-        LayerGeom g3 = { MODE_NHWC, 49, 7, 9, 9, 64, 3 * 64, 1, 576, 64, 1, 0, 1.0f, (65536 + 7 - 1) / 7, 0, dbg };
-        if ((rc = launch_layer<64, true, 8, 4>(ctx, s->act2, s->w[2], s->b[2], s->act3, c * 49, g3, 0, 64, st))) return rc;
+        if (!(dbg & 256)) {
+            // conv2: rows of two pixels on the 10 x 20 virtual grid; tap (ky, kx in {0, 2}) = input row + 10 ky + kx / 2
+            WinGeom w2 = { 200, 20, 9, 9, (65536 + 20 - 1) / 20, 8, { 0, 1, 10, 11, 20, 21, 30, 31, 0 }, 1, dbg };
+            if ((rc = launch_window<2>(ctx, s->act1, s->w[1], s->b[1], s->act2, c, w2, st))) return rc;
+            // conv3: rows of one pixel on the 9 x 9 input grid; tap (ky, kx) = input row + 9 ky + kx
+            WinGeom w3 = { 81, 9, 7, 7, (65536 + 9 - 1) / 9, 9, { 0, 1, 2, 9, 10, 11, 18, 19, 20 }, 1, dbg };
+            if ((rc = launch_window<3>(ctx, s->act2, s->w[2], s->b[2], s->act3, c, w3, st))) return rc;
+        } else {                                                      // the gather kernels (kept for A/B timing)
+            LayerGeom g2 = { MODE_NHWC, 81, 9, 20, 20, 32, 4 * 32, 2, 512, 64, 1, 0, 1.0f, (65536 + 9 - 1) / 9, 0, dbg };
+            if ((rc = launch_layer<64, true, 8, 4>(ctx, s->act1, s->w[1], s->b[1], s->act2, c * 81, g2, 0, 64, st))) return rc;
+            LayerGeom g3 = { MODE_NHWC, 49, 7, 9, 9, 64, 3 * 64, 1, 576, 64, 1, 0, 1.0f, (65536 + 7 - 1) / 7, 0, dbg };
+            if ((rc = launch_layer<64, true, 8, 4>(ctx, s->act2, s->w[2], s->b[2], s->act3, c * 49, g3, 0, 64, st))) return rc;
+        }
+        if (dbg & 512) continue;                                     // timing experiments: conv2 + conv3 alone (with bit 9: no conv1 either)
         LayerGeom g4 = { MODE_NHWC, 1, 1, 1, 1, 3136, 3136, 1, 3136, 512, 1, 0, 1.0f, 65536, 0, dbg };
         for (int half = 0; half < 2; half++)
             if ((rc = launch_layer<256, false, 4, 4>(ctx, s->act3, s->w[3], s->b[3], s->feat, c, g4, half * 256, 512, st))) return rc;
