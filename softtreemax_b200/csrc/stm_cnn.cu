@@ -603,6 +603,172 @@ stm_cnn_window_kernel(const __nv_bfloat16 *__restrict__ in, const __nv_bfloat16 
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" :: "r"(tmem_base), "r"(kCols) : "memory");
 }
 
+// ---------------------------------------------------------------------------------------------------------
+// conv1 as a window GEMM.  The 8x8 stride-4 convolution over the 4 x 84 x 84 u8 stack is a 2x2 stride-1
+// convolution over the 21 x 21 grid of 4x4-pixel blocks with 64 "channels" (4 frames x 4 x 4 pixels): virtual
+// output v = block index, tap (dy, dx) = window row v + 21 dy + dx.  The producers BUILD the window: thread
+// (row r, half h) fetches the eight 4-byte pixel runs (2 frames x 4 image rows) of block r that make up half of
+// its 128-byte fp16 row, widens them on the integer / half2 pipes and stores them swizzled — every pixel is
+// loaded and converted ONCE per tile (the gather kernel did it four times), the loads of the next tile are in
+// flight while this one is converted.  320 of the 384 producer threads work (160 window rows x 2 halves).
+// ---------------------------------------------------------------------------------------------------------
+constexpr int kC1Threads = 12 * 32 + 128 + 32;
+template <int kStages>
+__global__ void __launch_bounds__(kC1Threads, 1)
+stm_cnn_conv1_window_kernel(const uint8_t *__restrict__ in, const __nv_bfloat16 *__restrict__ wt, const float *__restrict__ bias,
+                            __nv_bfloat16 *__restrict__ out, uint32_t M_total, int debug)
+{
+    constexpr int N = 32, kBBytes = N * kChunkK * 2, kTaps = 4, kAcc = 8, kProd = 384, kMmaWarp = 16;
+    constexpr int V = 441, VW = 21, OH = 20, OW = 20, P = 400;
+    extern __shared__ __align__(1024) uint8_t smem_raw[];
+    uint8_t *smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+    uint8_t *sW = smem;                                    // kStages windows of 20 KB
+    uint8_t *sB = smem + kStages * kWinBytes;              // 4 taps x 4 KB, resident
+    __shared__ __align__(8) uint64_t full[kStages], empty[kStages], tfull[kAcc], tempty[kAcc];
+    __shared__ uint32_t tmem_base_s;
+    __shared__ float sbias[N];
+    const int tid = threadIdx.x, warp = tid >> 5;
+    const uint32_t ntiles = (M_total + kTileM - 1) / kTileM;
+    constexpr uint32_t kCols = kAcc * N;                   // 256 columns
+    if (tid < N) sbias[tid] = bias[tid];
+    if (warp == kMmaWarp) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;"
+                     :: "r"(smem_u32(&tmem_base_s)), "r"(kCols) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    if (tid == 0) {
+        for (int i = 0; i < kStages; i++) { mbar_init(&full[i], 10); mbar_init(&empty[i], 1); }
+        for (int i = 0; i < kAcc; i++) { mbar_init(&tfull[i], 1); mbar_init(&tempty[i], 4); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    for (int i = tid; i < kTaps * kBBytes / 16; i += kC1Threads)
+        reinterpret_cast<uint4 *>(sB)[i] = __ldg(reinterpret_cast<const uint4 *>(wt) + i);
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const uint32_t tmem_base = tmem_base_s;
+
+    if (warp < 10) {
+        // ===================== producers =====================
+        const uint32_t r = (uint32_t)tid % kWinRows, half = (uint32_t)tid / kWinRows;
+        const int my_tiles = blockIdx.x < ntiles ? (int)((ntiles - blockIdx.x + gridDim.x - 1) / gridDim.x) : 0;
+        uint32_t tile = blockIdx.x, st = 0, ph = 0;
+        uint32_t cur[8], nxt[8];
+        auto load_next = [&](uint32_t *w) {
+            const uint32_t v = tile * kTileM + r;
+            const bool ok = v < M_total && !(debug & 1);
+            const uint32_t img = v / V, q = v - img * V, by = q / VW, bx = q - by * VW;
+            const uint8_t *p = in + (size_t)img * (4 * 84 * 84) + (2 * half) * (84 * 84) + (4 * by) * 84 + 4 * bx;
+            #pragma unroll
+            for (int cc = 0; cc < 2; cc++)
+                #pragma unroll
+                for (int iy = 0; iy < 4; iy++)
+                    w[cc * 4 + iy] = ok ? __ldg(reinterpret_cast<const uint32_t *>(p + cc * (84 * 84) + iy * 84)) : 0u;
+            tile += gridDim.x;
+        };
+        if (my_tiles > 0) load_next(nxt);
+        const __half2 k1024 = __half2half2(__ushort_as_half((unsigned short)0x6400));
+        auto widen = [&](uint32_t w, uint32_t sel) -> uint32_t {
+            uint32_t biased = __byte_perm(w, 0x64646464u, sel);
+            __half2 h = __hsub2(*reinterpret_cast<__half2 *>(&biased), k1024);
+            return *reinterpret_cast<uint32_t *>(&h);
+        };
+        for (int i = 0; i < my_tiles; i++) {
+            #pragma unroll
+            for (int k = 0; k < 8; k++) cur[k] = nxt[k];
+            if (i + 1 < my_tiles) load_next(nxt);
+            mbar_wait(&empty[st], ph ^ 1);
+            uint8_t *wbase = sW + st * kWinBytes;
+            if (!(debug & 16)) {
+            #pragma unroll
+            for (int k = 0; k < 4; k++) {                           // 16-byte piece 4 half + k = (frame 2 half + k / 2, image rows 2 (k & 1), +1)
+                const uint32_t w0 = cur[(k >> 1) * 4 + 2 * (k & 1)], w1 = cur[(k >> 1) * 4 + 2 * (k & 1) + 1];
+                *reinterpret_cast<uint4 *>(wbase + swz(r, 4 * half + k)) =
+                    make_uint4(widen(w0, 0x5140), widen(w0, 0x7362), widen(w1, 0x5140), widen(w1, 0x7362));
+            }
+            }
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+            __syncwarp();
+            if ((tid & 31) == 0) mbar_arrive(&full[st]);
+            if (++st == kStages) { st = 0; ph ^= 1; }
+        }
+    } else if (warp == kMmaWarp) {
+        if ((tid & 31) == 0) {
+            const uint32_t idesc = make_idesc(N, 1);
+            const uint32_t b_lo0 = desc_lo(smem_u32(sB));
+            uint32_t st = 0, ph = 0, t = 0;
+            for (uint32_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x, t++) {
+                const uint32_t buf = t % kAcc;
+                mbar_wait(&tempty[buf], ((t / kAcc) & 1) ^ 1);
+                mbar_wait(&full[st], ph);
+                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                const uint32_t tmem_d = tmem_base + buf * N;
+                const uint32_t a_lo0 = desc_lo(smem_u32(sW + st * kWinBytes));
+                if (!(debug & 2)) {
+                    #pragma unroll
+                    for (int kc = 0; kc < kTaps; kc++) {
+                        #pragma unroll
+                        for (int j = 0; j < kChunkK / 16; j++) {
+                            const uint32_t a_lo = a_lo0 + (uint32_t)(((kc >> 1) * VW + (kc & 1)) * 8 + 2 * j);
+                            const uint32_t b_lo = b_lo0 + (uint32_t)(kc * (kBBytes >> 4) + 2 * j);
+                            if (kc == 0 && j == 0) umma_lo<false>(tmem_d, a_lo, b_lo, idesc);
+                            else umma_lo<true>(tmem_d, a_lo, b_lo, idesc);
+                        }
+                    }
+                }
+                umma_commit(&empty[st]);
+                umma_commit(&tfull[buf]);
+                if (++st == kStages) { st = 0; ph ^= 1; }
+            }
+        }
+    } else if (warp >= 12 && warp < 16) {
+        // ===================== epilogue =====================
+        const int et = tid - kProd, ew = et >> 5;
+        uint32_t t = 0;
+        for (uint32_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x, t++) {
+            const uint32_t buf = t % kAcc;
+            mbar_wait(&tfull[buf], (t / kAcc) & 1);
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            const uint32_t v = tile * kTileM + et;
+            const uint32_t img = v / V, q = v - img * V, oy = q / VW, ox = q - oy * VW;
+            const bool valid = v < M_total && oy < OH && ox < OW && !(debug & 4);
+            __nv_bfloat16 *orow = out + ((size_t)img * P + oy * OW + ox) * N;
+            const uint32_t taddr = tmem_base + buf * N + ((uint32_t)(ew * 32) << 16);
+            #pragma unroll
+            for (int c0 = 0; c0 < N; c0 += 16) {
+                uint32_t rr[16];
+                asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+                             "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+                             : "=r"(rr[0]), "=r"(rr[1]), "=r"(rr[2]), "=r"(rr[3]), "=r"(rr[4]), "=r"(rr[5]), "=r"(rr[6]), "=r"(rr[7]),
+                               "=r"(rr[8]), "=r"(rr[9]), "=r"(rr[10]), "=r"(rr[11]), "=r"(rr[12]), "=r"(rr[13]), "=r"(rr[14]), "=r"(rr[15])
+                             : "r"(taddr + (uint32_t)c0));
+                asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+                if (valid) {
+                    uint32_t pk[8];
+                    #pragma unroll
+                    for (int j = 0; j < 8; j++) {
+                        const float x0 = fmaxf(__uint_as_float(rr[2 * j]) * (1.0f / 255.0f) + sbias[c0 + 2 * j], 0.f);
+                        const float x1 = fmaxf(__uint_as_float(rr[2 * j + 1]) * (1.0f / 255.0f) + sbias[c0 + 2 * j + 1], 0.f);
+                        __nv_bfloat162 t2 = __floats2bfloat162_rn(x0, x1);
+                        pk[j] = *reinterpret_cast<uint32_t *>(&t2);
+                    }
+                    uint4 *o = reinterpret_cast<uint4 *>(orow + c0);
+                    o[0] = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+                    o[1] = make_uint4(pk[4], pk[5], pk[6], pk[7]);
+                }
+            }
+            asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+            __syncwarp();
+            if ((tid & 31) == 0) mbar_arrive(&tempty[buf]);
+        }
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    if (warp == kMmaWarp)
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" :: "r"(tmem_base), "r"(kCols) : "memory");
+}
+
 // Probe for the "shifted window" operand trick: a [rows][64] bf16 matrix sits in shared memory in the 128-byte
 // swizzled K-major layout (piece position keyed by the ABSOLUTE row, i.e. by the address); the MMA's A operand is
 // the 128-row window that starts `shift` rows in.  Does the tensor core read it correctly when the start address
@@ -667,13 +833,18 @@ stm_shift_probe_kernel(const __nv_bfloat16 *__restrict__ A, const __nv_bfloat16 
 // to N rows, tiled per 64-wide K slice in the 128-byte-swizzled K-major layout the kernel uses:
 //   element (n, k): slice k/64, byte offset n*128 + ((((k%64)/8) ^ (n%8)) * 16) + (k%8)*2
 __global__ void stm_tile_weights_kernel(const float *__restrict__ w, __nv_bfloat16 *__restrict__ dst, int n_real, int N,
-                                        int K, int KHW, int C, int f16)
+                                        int K, int KHW, int C, int f16, int s2d = 0)
 {
     int idx = blockIdx.x * blockDim.x + threadIdx.x;
     if (idx >= N * K) return;
     int n = idx / K, k = idx % K;
     int s = k / C, c = k % C;
-    float v = n < n_real ? w[(size_t)n * K + (size_t)c * KHW + s] : 0.f;
+    size_t col = (size_t)c * KHW + s;
+    if (s2d) {          // conv1 on 4x4-pixel blocks: k = tap (dy, dx) * 64 + frame * 16 + iy * 4 + ix  <-  W[n][frame][4 dy + iy][4 dx + ix]
+        int t = k / 64, kk = k % 64, fr = kk / 16, iy = (kk / 4) % 4, ix = kk % 4;
+        col = (size_t)fr * 64 + (size_t)(4 * (t / 2) + iy) * 8 + 4 * (t % 2) + ix;
+    }
+    float v = n < n_real ? w[(size_t)n * K + col] : 0.f;
     int kc = k / 64, kk = k % 64;
     size_t off = (size_t)kc * N * 64 + (size_t)n * 64 + (((kk / 8) ^ (n % 8)) * 8) + (kk % 8);
     if (f16) reinterpret_cast<__half *>(dst)[off] = __float2half_rn(v);
@@ -683,6 +854,7 @@ __global__ void stm_tile_weights_kernel(const float *__restrict__ w, __nv_bfloat
 struct CnnState {
     int A = 0;
     __nv_bfloat16 *w[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
+    __nv_bfloat16 *w_c1 = nullptr;                     // conv1 weights in the block (space-to-depth) order of the window kernel, fp16
     float *b[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
     __nv_bfloat16 *act1 = nullptr, *act2 = nullptr, *act3 = nullptr, *feat = nullptr;
     long long cap_images = 0;
@@ -739,10 +911,32 @@ int launch_window(stm_ctx *ctx, const __nv_bfloat16 *in, const __nv_bfloat16 *w,
     return e == cudaSuccess ? STM_OK : stm_internal_fail(ctx, STM_ERR_CUDA, cudaGetErrorString(e));
 }
 
+int launch_conv1_window(stm_ctx *ctx, const uint8_t *obs, const __nv_bfloat16 *w, const float *b, __nv_bfloat16 *out,
+                        long long n_images, int debug, cudaStream_t st)
+{
+    constexpr int kStages = 6;
+    static bool attr_done = false;
+    if (!attr_done) {
+        cudaFuncSetAttribute(stm_cnn_conv1_window_kernel<kStages>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 2048);
+        cudaFuncSetAttribute(stm_cnn_conv1_window_kernel<kStages>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+        attr_done = true;
+    }
+    const long long M = n_images * 441;
+    if (M >= (1LL << 31) - kTileM) return stm_internal_fail(ctx, STM_ERR_ARG, "stm_cnn: too many rows for one pass");
+    const size_t smem = (size_t)kStages * kWinBytes + 4 * 32 * kChunkK * 2 + 1024;
+    const long long tiles = (M + kTileM - 1) / kTileM;
+    const long long grid = tiles < 148 ? tiles : 148;
+    stm_cnn_conv1_window_kernel<kStages><<<(unsigned)grid, kC1Threads, smem, st>>>(obs, w, b, out, (uint32_t)M, debug);
+    stm_internal_count_launch(ctx);
+    cudaError_t e = cudaGetLastError();
+    return e == cudaSuccess ? STM_OK : stm_internal_fail(ctx, STM_ERR_CUDA, cudaGetErrorString(e));
+}
+
 void free_state(CnnState *s)
 {
     if (!s) return;
     for (int i = 0; i < 5; i++) { cudaFree(s->w[i]); cudaFree(s->b[i]); }
+    cudaFree(s->w_c1);
     cudaFree(s->act1); cudaFree(s->act2); cudaFree(s->act3); cudaFree(s->feat);
     delete s;
 }
@@ -788,6 +982,9 @@ int stm_cnn_set_weights(stm_ctx *ctx, const float *conv1_w, const float *conv1_b
         stm_internal_count_launch(ctx);
         cudaMemcpyAsync(s->b[i], spec[i].b, (size_t)spec[i].n_real * 4, cudaMemcpyDeviceToDevice, st);
     }
+    if (!s->w_c1 && cudaMalloc(&s->w_c1, 32 * 256 * 2) != cudaSuccess) return stm_internal_fail(ctx, STM_ERR_NOMEM, "stm_cnn_set_weights: cudaMalloc");
+    stm_tile_weights_kernel<<<(32 * 256 + 255) / 256, 256, 0, st>>>(conv1_w, s->w_c1, 32, 32, 256, 1, 256, 1, 1);
+    stm_internal_count_launch(ctx);
     // heads: rows 0..A-1 = action_net, row A = value_net, zero padded to 32 rows
     if (!s->w[4] && cudaMalloc(&s->w[4], 32 * 512 * 2) != cudaSuccess) return stm_internal_fail(ctx, STM_ERR_NOMEM, "cudaMalloc");
     if (!s->b[4] && cudaMalloc(&s->b[4], 32 * 4) != cudaSuccess) return stm_internal_fail(ctx, STM_ERR_NOMEM, "cudaMalloc");
@@ -842,7 +1039,11 @@ int stm_cnn_forward(stm_ctx *ctx, const uint8_t *obs, long long n, float *heads,
         long long c = n - i0 < chunk ? n - i0 : chunk;
         int rc;
         LayerGeom g1 = { MODE_CONV1, 400, 20, 84, 84, 4, 0, 4, 256, 32, 1, 0, 1.0f / 255.0f, (65536 + 20 - 1) / 20, 1, dbg };
-        if (!(dbg & 512) && (rc = launch_layer<32, true, 4, 8>(ctx, obs + (size_t)i0 * 4 * 84 * 84, s->w[0], s->b[0], s->act1, c * 400, g1, 0, 32, st))) return rc;
+        if (!(dbg & 512)) {
+            if (!(dbg & 256)) rc = launch_conv1_window(ctx, obs + (size_t)i0 * 4 * 84 * 84, s->w_c1, s->b[0], s->act1, c, dbg, st);
+            else rc = launch_layer<32, true, 4, 8>(ctx, obs + (size_t)i0 * 4 * 84 * 84, s->w[0], s->b[0], s->act1, c * 400, g1, 0, 32, st);
+            if (rc) return rc;
+        }
         if (dbg & 8) continue;                                       // timing experiments: conv1 alone
         if (!(dbg & 256)) {
             // conv2: rows of two pixels on the 10 x 20 virtual grid; tap (ky, kx in {0, 2}) = input row + 10 ky + kx / 2
