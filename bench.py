@@ -31,7 +31,7 @@ CYCLES_PER_NODE_STEP = 4 * 262 * 76          # emulated CPU cyc
 # DRAM bytes per env of one K2 launch, from the `ncu --set full` capture summarised in
 # profiles/r01_k2_step_ncu_full_summary.txt: (dram__bytes_read.sum + dram__bytes_write.sum) / 65 536 envs.
 # It is the native-frame scratch (2 frames x 168 sampled rows x 160 B) plus the 512 B state round trip.
-K2_NCU_DRAM_BYTES_PER_ENV = (92.175872e6 + 3.443887e9) / 65536
+K2_NCU_DRAM_BYTES_PER_ENV = (95.111936e6 + 3.443775e9) / 65536
 
 
 def peaks():
