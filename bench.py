@@ -150,6 +150,7 @@ def main():
     ap.add_argument("--depth", type=int, default=2)
     ap.add_argument("--game", default=GAME, help="cartridge name (softtreemax_b200/roms/games.json)")
     ap.add_argument("--no-policy", action="store_true", help="skip the bfs + CNN + logits arm (sweeps)")
+    ap.add_argument("--two-groups", action="store_true", help="time two root groups in flight on two streams even with --no-policy")
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     ap.add_argument("--scratch-envs", type=int, default=262144, help="envs per K2/K3 pass (native-frame scratch: 67 KB each)")
@@ -228,6 +229,44 @@ def main():
     launches = eng.launch_count - launches0
     per_kernel = eng.timing_read()
     eng.timing(False)
+
+    # ---------------- two root groups in flight (throughput mode) ----------------
+    # A depth-d step is d dependent K2 launches and the first ones leave most of the GPU idle (level 1 of 4 096
+    # roots is one warp per scheduler).  Two independent groups of roots (two contexts, two streams), started half
+    # a step apart, fill that time with the other group's last level — what a rollout with two env groups taking
+    # turns does.  Reported beside the headline, which stays one group at a time.
+    ms_two = 0.0
+    if args.two_groups or not args.no_policy:
+        eng2 = Engine(args.game, device=local, scratch_envs=min(L, args.scratch_envs))
+        states2, stacks2 = make_roots(eng2, R, seed=4321 + rank)
+        out_b = dict(stacks=torch.empty_like(out["stacks"]), rewards=torch.empty_like(out["rewards"]),
+                     done=torch.empty_like(out["done"]), lives=torch.empty_like(out["lives"]), states=None)
+        s_a, s_b = torch.cuda.Stream(device=dev), torch.cuda.Stream(device=dev)
+
+        def two_groups(nsteps):
+            main = torch.cuda.current_stream()
+            s_a.wait_stream(main)
+            s_b.wait_stream(main)
+            with torch.cuda.stream(s_b):
+                torch.cuda._sleep(int(0.45 * ms_total / args.steps * 1e-3 * 1.9e9))     # start group B about half a step later
+            for _ in range(nsteps):
+                with torch.cuda.stream(s_a):
+                    eng.bfs(states, stacks, depth, out=out)
+                with torch.cuda.stream(s_b):
+                    eng2.bfs(states2, stacks2, depth, out=out_b)
+            main.wait_stream(s_a)
+            main.wait_stream(s_b)
+
+        two_groups(2)
+        barrier()
+        g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        g0.record()
+        two_groups(args.steps)
+        g1.record()
+        barrier()
+        ms_two = g0.elapsed_time(g1)
+        eng2.close()
+        del out_b
 
     ms_policy = ms_policy_e2e = ms_pipe = c_ms = 0.0
     hs_pin = hk_pin = None
@@ -356,8 +395,8 @@ def main():
     d2h = int(L * (4 + 1 + 4))
 
     from softtreemax_b200 import shard
-    ms_total, ms_e2e, ms_policy, ms_policy_e2e, ms_pipe = shard.max_over_ranks(
-        [ms_total, ms_e2e, ms_policy, ms_policy_e2e, ms_pipe], dev)
+    ms_total, ms_e2e, ms_policy, ms_policy_e2e, ms_pipe, ms_two = shard.max_over_ranks(
+        [ms_total, ms_e2e, ms_policy, ms_policy_e2e, ms_pipe, ms_two], dev)
 
     if rank == 0:
         ms_step = ms_total / args.steps
@@ -423,6 +462,9 @@ def main():
                 "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                         "ms_per_step": ms_e2e / args.steps,
                         "api": "stm_bfs_host: pinned host roots in; rewards/done/lives to host; leaf stacks stay in HBM"},
+                "two_groups_in_flight": None if not ms_two else {
+                    "value": world * 2 * L * args.steps / (ms_two / 1e3), "unit": UNIT, "ms_per_pair_of_steps": ms_two / args.steps,
+                    "how": "two independent groups of roots_per_gpu roots, two contexts on two streams half a step apart"},
                 "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "kernels": kernels, "policy": policy,
                 "cpu_baseline": {"value": cpu_rate, "unit": UNIT, "cores": os.cpu_count() or 1, "kind": "port",
                                  "sample": f"{cpu_leaves} leaves in {cpu_dt:.1f}s: 64 roots x depth {depth} repeated, oracle port (OpenMP)"}}
