@@ -187,6 +187,11 @@ long long stm_launch_count(const stm_ctx *ctx);
 /* (measurement only, no reference counterpart) index of the ahead-of-time translated step kernel this ctx uses,
  * 0 = the interpreter.  Non-zero only in a library built with -DSTM_WITH_XLATE and a process run with STM_XLATE=1. */
 int stm_translated_core(const stm_ctx *ctx);
+/* (probe, no reference counterpart, not on any product path) runs one 128 x 64 x 64 bf16 tcgen05 MMA whose A operand
+ * starts `shift` rows into a 128B-swizzled [rows][64] shared-memory tile, with `base_off` in the descriptor's
+ * base-offset field; out = A[shift .. shift + 128) x B^T as f32.  tools/shift_probe.py uses it to show that a
+ * 128-byte-aligned operand start is read correctly — the fact the window GEMMs of K4 rest on. */
+int stm_debug_shift_probe(stm_ctx *ctx, const void *A, const void *B, float *out, int rows, int shift, int base_off, void *stream);
 
 #ifdef __cplusplus
 }

@@ -53,6 +53,7 @@ _SIGS = {
     "stm_timing_read": (C.c_int, [C.c_void_p, C.POINTER(C.c_float), C.POINTER(C.c_int)]),
     "stm_launch_count": (C.c_longlong, [C.c_void_p]),
     "stm_translated_core": (C.c_int, [C.c_void_p]),
+    "stm_debug_shift_probe": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p]),
     "stm_step_frames_noalloc": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_float,
                                           C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]),
     "stm_cnn_set_weights": (C.c_int, [C.c_void_p] * 13 + [C.c_int, C.c_void_p]),
