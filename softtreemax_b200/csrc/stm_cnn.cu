@@ -136,6 +136,14 @@ __device__ __forceinline__ void umma_lo_rt(uint32_t tmem_d, uint32_t a_lo, uint3
         "tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %3, p;\n\t}"
         :: "r"(tmem_d), "r"(a_lo), "r"(b_lo), "r"(idesc), "r"(kDescHi), "r"(accumulate) : "memory");
 }
+// one lane of a fully converged warp (elect.sync): the form ptxas recognises, so that tcgen05.mma is issued without
+// the per-instruction election loop it wraps around an MMA that sits under an ordinary divergent branch
+__device__ __forceinline__ bool elect_one()
+{
+    uint32_t pred;
+    asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(pred));
+    return pred != 0;
+}
 __device__ __forceinline__ void umma_commit(uint64_t *bar)
 {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];"
@@ -525,7 +533,8 @@ stm_cnn_window_kernel(const __nv_bfloat16 *__restrict__ in, const __nv_bfloat16 
         }
     } else if (warp == 8) {
         // ===================== MMA issuer: every tap reads the same window, started off[tap] rows in =====================
-        if ((tid & 31) == 0) {
+        // The whole warp walks the tile loop converged (all lanes wait on the barriers); one elected lane issues.
+        {
             const uint32_t idesc = make_idesc(N, 0);
             const uint32_t b_lo0 = desc_lo(smem_u32(sB));
             uint32_t st = 0, ph = 0, t = 0;
@@ -536,19 +545,22 @@ stm_cnn_window_kernel(const __nv_bfloat16 *__restrict__ in, const __nv_bfloat16 
                 asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
                 const uint32_t tmem_d = tmem_base + buf * N;
                 const uint32_t a_lo0 = desc_lo(smem_u32(sW + st * kWinBytes));
-                if (!(g.debug & 2)) {
-                    #pragma unroll
-                    for (int kc = 0; kc < win_taps<kConv>(); kc++) {
+                if (elect_one()) {
+                    if (!(g.debug & 2)) {
                         #pragma unroll
-                        for (int j = 0; j < kChunkK / 16; j++) {
-                            const uint32_t a_lo = a_lo0 + (uint32_t)(win_off<kConv>(kc) * 8 + 2 * j), b_lo = b_lo0 + (uint32_t)(kc * (kBBytes >> 4) + 2 * j);
-                            if (kc == 0 && j == 0) umma_lo<false>(tmem_d, a_lo, b_lo, idesc);
-                            else umma_lo<true>(tmem_d, a_lo, b_lo, idesc);
+                        for (int kc = 0; kc < win_taps<kConv>(); kc++) {
+                            #pragma unroll
+                            for (int j = 0; j < kChunkK / 16; j++) {
+                                const uint32_t a_lo = a_lo0 + (uint32_t)(win_off<kConv>(kc) * 8 + 2 * j), b_lo = b_lo0 + (uint32_t)(kc * (kBBytes >> 4) + 2 * j);
+                                if (kc == 0 && j == 0) umma_lo<false>(tmem_d, a_lo, b_lo, idesc);
+                                else umma_lo<true>(tmem_d, a_lo, b_lo, idesc);
+                            }
                         }
                     }
+                    if (!(g.debug & 2048)) umma_commit(&empty[st]);
+                    if (!(g.debug & 1024)) umma_commit(&tfull[buf]);
                 }
-                if (!(g.debug & 2048)) umma_commit(&empty[st]);
-                if (!(g.debug & 1024)) umma_commit(&tfull[buf]);
+                __syncwarp();
                 if (++st == kStages) { st = 0; ph ^= 1; }
             }
         }
@@ -694,17 +706,18 @@ stm_cnn_conv1_window_kernel(const uint8_t *__restrict__ in, const __nv_bfloat16 
             if (++st == kStages) { st = 0; ph ^= 1; }
         }
     } else if (warp == kMmaWarp) {
-        if ((tid & 31) == 0) {
-            const uint32_t idesc = make_idesc(N, 1);
-            const uint32_t b_lo0 = desc_lo(smem_u32(sB));
-            uint32_t st = 0, ph = 0, t = 0;
-            for (uint32_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x, t++) {
-                const uint32_t buf = t % kAcc;
-                mbar_wait(&tempty[buf], ((t / kAcc) & 1) ^ 1);
-                mbar_wait(&full[st], ph);
-                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-                const uint32_t tmem_d = tmem_base + buf * N;
-                const uint32_t a_lo0 = desc_lo(smem_u32(sW + st * kWinBytes));
+        // the whole warp walks the tile loop converged; one elected lane issues
+        const uint32_t idesc = make_idesc(N, 1);
+        const uint32_t b_lo0 = desc_lo(smem_u32(sB));
+        uint32_t st = 0, ph = 0, t = 0;
+        for (uint32_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x, t++) {
+            const uint32_t buf = t % kAcc;
+            mbar_wait(&tempty[buf], ((t / kAcc) & 1) ^ 1);
+            mbar_wait(&full[st], ph);
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            const uint32_t tmem_d = tmem_base + buf * N;
+            const uint32_t a_lo0 = desc_lo(smem_u32(sW + st * kWinBytes));
+            if (elect_one()) {
                 if (!(debug & 2)) {
                     #pragma unroll
                     for (int kc = 0; kc < kTaps; kc++) {
@@ -719,8 +732,9 @@ stm_cnn_conv1_window_kernel(const uint8_t *__restrict__ in, const __nv_bfloat16 
                 }
                 umma_commit(&empty[st]);
                 umma_commit(&tfull[buf]);
-                if (++st == kStages) { st = 0; ph ^= 1; }
             }
+            __syncwarp();
+            if (++st == kStages) { st = 0; ph ^= 1; }
         }
     } else if (warp >= 12 && warp < 16) {
         // ===================== epilogue =====================
