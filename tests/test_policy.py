@@ -174,7 +174,7 @@ def test_device_roots_match_oracle_roots():
     from oracle import orc
     from softtreemax_b200.engine import Engine
     from softtreemax_b200.roots import make_roots
-    for name in ("synth_breakout", "synth_pong"):
+    for name in ("synth_breakout", "synth_pong", "synth_pacman", "synth_torture"):      # incl. F8 banking and the undocumented opcodes
         eng = Engine(name)
         try:
             st, sk = make_roots(eng, 200, seed=1234)
