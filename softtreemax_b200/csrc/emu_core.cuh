@@ -29,7 +29,7 @@
 #ifdef __CUDACC__
 #define STM_DEV __device__ __forceinline__          /* member functions */
 #define STM_FN  __device__ __forceinline__          /* free functions   */
-#define STM_NOINLINE __device__ __noinline__
+#define STM_NOINLINE static __device__ __noinline__
 #define STM_WARP_ALL(mask, pred) __all_sync((mask), (pred))
 #define STM_WARP_MIN(mask, v) __reduce_min_sync((mask), (v))
 #else
@@ -270,6 +270,14 @@ static inline void build_predecode(const uint8_t *rom, uint32_t rom_size, uint32
 static inline void stamp_cases(uint32_t *pre, const uint16_t *offsets, uint32_t n)
 {
     for (uint32_t k = 0; k < n; k++) pre[2 * offsets[k] + 1] |= (k + 1) << 16;
+}
+
+// identifies a cartridge image (FNV-1a, as tools/xlate_rom.cpp): a translated core belongs to exactly one image
+static inline uint32_t rom_hash(const uint8_t *rom, uint32_t n)
+{
+    uint32_t h = 2166136261u;
+    for (uint32_t i = 0; i < n; i++) { h ^= rom[i]; h *= 16777619u; }
+    return h;
 }
 
 // ---- game constants handed to the kernel ---------------------------------------------------------

@@ -1,0 +1,166 @@
+// stm_step.cuh — K2, the batched Atari 2600 agent-step kernel, as a header: stm_kernels.cu instantiates it with the
+// interpreter (stm::InterpCore), every translated cartridge (csrc/gen/xl_<name>.cu, one translation unit each so that
+// they compile in parallel) instantiates it with its own core.  Reference call site replaced: policies/cule_bfs.py
+// :152-158 (step + get_data x frameskip).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include "../../include/stm_b200.h"
+#include "../../include/stm_palette.h"
+#include "emu_core.cuh"
+
+// arguments of one K2 launch (a named type: it crosses translation units)
+struct StmStepArgs {
+    uint8_t *states; const uint8_t *actions; float *rewards; uint8_t *done; int32_t *lives;
+    const uint32_t *rom; const uint32_t *lut; const uint2 *pre; uint32_t *scratch; uint8_t *stepped;
+    int n, frameskip, episodic_life, render; uint32_t rom_words; float weight;
+    stm::GameParams gp;
+};
+
+namespace stm {
+// what stm_kernels.cu knows about a translated cartridge (filled in by csrc/gen/xl_<name>.cu)
+struct XlEntry {
+    const char *name;
+    uint32_t rom_hash, rom_size, n_cases;
+    const uint16_t *offsets;                                           // image offsets of the translated instructions (stamp_cases)
+    void (*launch)(int blocks, size_t smem, cudaStream_t st, const StmStepArgs &a);
+    cudaError_t (*set_attrs)(size_t smem, int carveout_pct);
+};
+}  // namespace stm
+
+namespace {
+
+using namespace stm;
+typedef StmStepArgs StepArgs;
+
+constexpr int kTileEnvs = 32;                                   // envs per native-scratch tile (= warp)
+constexpr size_t kTileWords = 2ull * STM_VIS_H * 40 * kTileEnvs; // u32 per tile (2 frames)
+constexpr int kStepThreads = 128;
+#ifndef STM_STEP_MIN_CTAS
+#define STM_STEP_MIN_CTAS 4   /* measured: 4 CTAs/SM without spills beats 5 with */
+#endif
+
+// ---------------------------------------------------------------------------------------------
+// K2 — batched agent step.  One env per thread, 128 envs per CTA.
+// Shared memory: the CTA's 128 state blobs, word-interleaved (word k of env t at [k*128 + t], so
+// lane t always hits bank t%32: conflict-free for every access pattern, RAM bytes included), the
+// cartridge image (4 or 8 KB) and the decode table.
+// ---------------------------------------------------------------------------------------------
+__constant__ uint8_t c_gray[128] = STM_GRAY_LUT_INIT;
+
+struct DevMem {
+    uint8_t *blob;             // &sblob[tid] as bytes
+    const uint32_t *rom;       // shared
+    const uint32_t *lut;       // shared
+    const uint2 *pre;          // global, read-only path (L1-resident: 32 KB for a 4 KB cartridge)
+    uint32_t *scr;             // native scratch of this env's tile, + lane
+    uint32_t fsel;             // which of the two native frames is being drawn
+
+    __device__ __forceinline__ uint32_t boff(uint32_t o) const { return (o >> 2) * (kStepThreads * 4) + (o & 3); }
+    __device__ __forceinline__ uint32_t ld8(uint32_t o) const { return blob[boff(o)]; }
+    __device__ __forceinline__ void st8(uint32_t o, uint32_t v) { blob[boff(o)] = (uint8_t)v; }
+    __device__ __forceinline__ uint32_t ld16(uint32_t o) const { return *(const uint16_t *)(blob + boff(o)); }
+    __device__ __forceinline__ void st16(uint32_t o, uint32_t v) { *(uint16_t *)(blob + boff(o)) = (uint16_t)v; }
+    __device__ __forceinline__ uint32_t ld32(uint32_t o) const { return *(const uint32_t *)(blob + boff(o)); }
+    __device__ __forceinline__ void st32(uint32_t o, uint32_t v) { *(uint32_t *)(blob + boff(o)) = v; }
+    __device__ __forceinline__ uint32_t rom8(uint32_t i) const { return (rom[i >> 2] >> ((i & 3) * 8)) & 0xFFu; }
+    __device__ __forceinline__ void fetch(uint32_t off, uint32_t &w, uint32_t &ops) const
+    { uint2 v = __ldg(pre + off); w = v.x; ops = v.y; }
+    __device__ __forceinline__ uint32_t opinfo(uint32_t op) const { return lut[op]; }
+    __device__ __forceinline__ uint32_t grey(uint32_t i) const { return c_gray[i & 127]; }
+    // scr points at this lane's uint4 slot of (frame 0, row 0, quad 0); quads are kTileEnvs uint4 apart
+    __device__ __forceinline__ uint32_t *quad(uint32_t row, uint32_t q) const
+    { return scr + (size_t)((fsel * STM_VIS_H + row) * 10 + q) * (kTileEnvs * 4); }
+    __device__ __forceinline__ void px16(uint32_t row, uint32_t q, uint32_t a, uint32_t b, uint32_t c, uint32_t d)
+    { __stcg(reinterpret_cast<uint4 *>(quad(row, q)), make_uint4(a, b, c, d)); }
+    __device__ __forceinline__ void copy_row(uint32_t dst, uint32_t src)
+    {
+        const uint4 *s = reinterpret_cast<const uint4 *>(quad(src, 0));
+        uint4 *d = reinterpret_cast<uint4 *>(quad(dst, 0));
+        #pragma unroll
+        for (int h = 0; h < 2; h++) {                    // five loads in flight, then five stores
+            uint4 v[5];
+            #pragma unroll
+            for (int q = 0; q < 5; q++) v[q] = __ldcg(s + (size_t)(5 * h + q) * kTileEnvs);   // L2 only: L1 is for the fetch path
+            #pragma unroll
+            for (int q = 0; q < 5; q++) __stcg(d + (size_t)(5 * h + q) * kTileEnvs, v[q]);
+        }
+    }
+    __device__ __forceinline__ void px4(uint32_t row, uint32_t g, uint32_t w) { quad(row, g >> 2)[g & 3] = w; }
+    __device__ __forceinline__ void px1(uint32_t row, uint32_t x, uint32_t v)
+    { reinterpret_cast<uint8_t *>(quad(row, x >> 4))[x & 15] = (uint8_t)v; }
+};
+
+
+
+// Core = stm::InterpCore (any cartridge) or a translated cartridge stm::Xl_<name> (csrc/gen/)
+template <class Core>
+__global__ void __launch_bounds__(kStepThreads, STM_STEP_MIN_CTAS)
+stm_step_kernel(const StepArgs a)
+{
+    extern __shared__ __align__(16) uint32_t smem[];
+    uint32_t *sblob = smem;                              // 64 words x 128 threads
+    uint32_t *srom = sblob + 64 * kStepThreads;
+    uint32_t *slut = srom + a.rom_words;
+    const int tid = threadIdx.x;
+    for (uint32_t i = tid; i < a.rom_words; i += kStepThreads) srom[i] = a.rom[i];
+    for (uint32_t i = tid; i < 256; i += kStepThreads) slut[i] = a.lut[i];
+    const int env = blockIdx.x * kStepThreads + tid;
+    const bool valid = env < a.n;
+    if (valid) {
+        const uint4 *g = reinterpret_cast<const uint4 *>(a.states + (size_t)env * STM_STATE_BYTES);
+        #pragma unroll
+        for (int k = 0; k < 16; k++) {
+            uint4 v = g[k];
+            sblob[(4 * k + 0) * kStepThreads + tid] = v.x; sblob[(4 * k + 1) * kStepThreads + tid] = v.y;
+            sblob[(4 * k + 2) * kStepThreads + tid] = v.z; sblob[(4 * k + 3) * kStepThreads + tid] = v.w;
+        }
+    }
+    __syncthreads();
+    uint32_t done = valid ? a.done[env] : 1u;
+    // lanes that emulate; they advance scanline by scanline in lock-step (Emu::run_frame)
+    const uint32_t lanes = __ballot_sync(0xFFFFFFFFu, valid && !done);
+    if (!valid) return;
+    if (a.stepped) a.stepped[env] = done ? 0 : 1;
+    if (done) return;                                    // frozen env: nothing changes
+
+    DevMem m;
+    m.blob = reinterpret_cast<uint8_t *>(sblob + tid);
+    m.rom = srom; m.lut = slut; m.pre = a.pre;
+    m.scr = a.scratch ? a.scratch + (size_t)(env / kTileEnvs) * kTileWords + (env % kTileEnvs) * 4 : nullptr;
+    m.fsel = 0;
+    Emu<DevMem> e(m, a.gp);
+    e.load();
+    int lives = a.lives[env];
+    float rew = a.rewards[env];
+    uint32_t act = a.actions ? a.actions[env] : (uint32_t)(env % (int)a.gp.n_actions);
+    uint32_t ale = a.gp.actions[act];
+    for (int f = 0; f < a.frameskip; f++) {
+        bool want = a.render && f >= a.frameskip - 2;
+        // the newest frame always goes to slot 1, the one before it to slot 0
+        m.fsel = (f == a.frameskip - 1) ? 1u : 0u;
+        e.template run_frame<Core>(ale, want, lanes);
+        int r = e.get_data(a.episodic_life != 0, done, lives);
+        rew = __fadd_rn(rew, __fmul_rn(a.weight, (float)r));
+    }
+    e.store();
+    uint4 *g = reinterpret_cast<uint4 *>(a.states + (size_t)env * STM_STATE_BYTES);
+    #pragma unroll
+    for (int k = 0; k < 16; k++) {
+        uint4 v;
+        v.x = sblob[(4 * k + 0) * kStepThreads + tid]; v.y = sblob[(4 * k + 1) * kStepThreads + tid];
+        v.z = sblob[(4 * k + 2) * kStepThreads + tid]; v.w = sblob[(4 * k + 3) * kStepThreads + tid];
+        g[k] = v;
+    }
+    a.rewards[env] = rew; a.done[env] = (uint8_t)done; a.lives[env] = lives;
+}
+
+template <class Core>
+cudaError_t set_step_attrs(size_t smem, int pct)
+{
+    cudaError_t e = cudaFuncSetAttribute(stm_step_kernel<Core>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    return cudaFuncSetAttribute(stm_step_kernel<Core>, cudaFuncAttributePreferredSharedMemoryCarveout, pct);
+}
+
+}  // namespace

@@ -55,7 +55,7 @@ class Engine:
 
     @property
     def translated_core(self):
-        """0 = the interpreter kernel; k > 0 = the k-th translated cartridge (STM_WITH_XLATE build + STM_XLATE=1)."""
+        """0 = interpreter only; k > 0 = the k-th translated cartridge of the library also serves this image (small launches)."""
         return lib().stm_translated_core(self._h)
 
     @property

@@ -159,17 +159,20 @@ def test_bfs_matches_oracle(orc, engines, name, R, depth):
     assert np.array_equal(got["states"].cpu().numpy(), want[4].reshape(L, 256))
 
 
+@pytest.mark.parametrize("mode", ["translated", "interpreter"])
 @pytest.mark.parametrize("name,R,depth", [("synth_breakout", 40, 2), ("synth_pong", 9, 2), ("synth_pacman", 5, 2), ("synth_torture", 7, 2)])
-def test_translated_cartridge_kernels_match_oracle(orc, name, R, depth, monkeypatch):
-    """The ahead-of-time translated step kernels (tools/xlate_rom.cpp -> csrc/gen/xl_*.cuh, selected by image hash
-    when STM_XLATE=1; off by default because they measure slower than the interpreter) are bit-exact too."""
+def test_both_step_kernels_match_oracle(orc, name, R, depth, mode, monkeypatch):
+    """K2 exists twice for a bundled cartridge: the interpreter and the ahead-of-time translated kernel
+    (tools/xlate_rom.cpp -> csrc/gen/xl_*.cu, selected by image hash; by default small launches use it and large
+    ones the interpreter).  Forced one way and the other, both are bit-exact."""
     from softtreemax_b200.engine import Engine
-    monkeypatch.setenv("STM_XLATE", "1")
+    if mode == "translated":
+        monkeypatch.setenv("STM_XL_MAX_ENVS", "2000000000")
+    else:
+        monkeypatch.setenv("STM_XLATE", "0")
     g = orc.Game(name)
     eng = Engine(name)
-    if eng.translated_core == 0:
-        eng.close()
-        pytest.skip("library built without -DSTM_WITH_XLATE (the default)")
+    assert (eng.translated_core != 0) == (mode == "translated")
     try:
         roots, stacks = orc.make_roots(g, R, seed=21, base_steps=50, spread=60)
         want = g.bfs(roots, stacks, depth, gamma=0.99, clip_reward=False)
