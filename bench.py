@@ -237,7 +237,12 @@ def main():
     # turns does.  Reported beside the headline, which stays one group at a time.
     ms_two = 0.0
     if args.two_groups or not args.no_policy:
+        # (both groups on interpreter-only contexts: with two launches sharing the SMs the translated kernel of a small
+        # launch is no longer alone on its schedulers, which is the only place it wins)
+        os.environ["STM_XLATE"] = "0"
+        eng_a = Engine(args.game, device=local, scratch_envs=min(L, args.scratch_envs))
         eng2 = Engine(args.game, device=local, scratch_envs=min(L, args.scratch_envs))
+        del os.environ["STM_XLATE"]
         states2, stacks2 = make_roots(eng2, R, seed=4321 + rank)
         out_b = dict(stacks=torch.empty_like(out["stacks"]), rewards=torch.empty_like(out["rewards"]),
                      done=torch.empty_like(out["done"]), lives=torch.empty_like(out["lives"]), states=None)
@@ -251,7 +256,7 @@ def main():
                 torch.cuda._sleep(int(0.45 * ms_total / args.steps * 1e-3 * 1.9e9))     # start group B about half a step later
             for _ in range(nsteps):
                 with torch.cuda.stream(s_a):
-                    eng.bfs(states, stacks, depth, out=out)
+                    eng_a.bfs(states, stacks, depth, out=out)
                 with torch.cuda.stream(s_b):
                     eng2.bfs(states2, stacks2, depth, out=out_b)
             main.wait_stream(s_a)
@@ -266,6 +271,7 @@ def main():
         barrier()
         ms_two = g0.elapsed_time(g1)
         eng2.close()
+        eng_a.close()
         del out_b
 
     ms_policy = ms_policy_e2e = ms_pipe = c_ms = 0.0
