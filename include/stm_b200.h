@@ -185,7 +185,8 @@ int stm_step_frames_noalloc(stm_ctx *ctx, uint8_t *states, const uint8_t *action
 /* number of kernels this ctx has launched since creation (bench.py's gpu_launches) */
 long long stm_launch_count(const stm_ctx *ctx);
 /* (measurement only, no reference counterpart) index of the ahead-of-time translated step kernel this ctx uses,
- * 0 = the interpreter.  Non-zero only in a library built with -DSTM_WITH_XLATE and a process run with STM_XLATE=1. */
+ * also serves this ctx's cartridge image (launches of up to one warp per scheduler use it, larger ones the
+ * interpreter); 0 = interpreter only (an image the library has no translation for, or STM_XLATE=0). */
 int stm_translated_core(const stm_ctx *ctx);
 /* (probe, no reference counterpart, not on any product path) runs one 128 x 64 x 64 bf16 tcgen05 MMA whose A operand
  * starts `shift` rows into a 128B-swizzled [rows][64] shared-memory tile, with `base_off` in the descriptor's

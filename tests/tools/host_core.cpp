@@ -6,7 +6,6 @@
 #include <cstdint>
 #include "../../include/stm_palette.h"
 #include "../../softtreemax_b200/csrc/emu_core.cuh"
-#define STM_WITH_XLATE 1
 #include "../../softtreemax_b200/csrc/gen/xl_index.cuh"
 
 namespace {
