@@ -184,7 +184,7 @@ int stm_step_frames_noalloc(stm_ctx *ctx, uint8_t *states, const uint8_t *action
 
 /* number of kernels this ctx has launched since creation (bench.py's gpu_launches) */
 long long stm_launch_count(const stm_ctx *ctx);
-/* (measurement only, no reference counterpart) index of the ahead-of-time translated step kernel this ctx uses,
+/* (measurement only, no reference counterpart) 1-based index of the ahead-of-time translated step kernel that
  * also serves this ctx's cartridge image (launches of up to one warp per scheduler use it, larger ones the
  * interpreter); 0 = interpreter only (an image the library has no translation for, or STM_XLATE=0). */
 int stm_translated_core(const stm_ctx *ctx);
