@@ -20,8 +20,9 @@ def line_table(want_len=None):
     so = os.path.join(ROOT, "softtreemax_b200", "libstm_b200.so")
     with tempfile.TemporaryDirectory() as d:
         subprocess.run(["cuobjdump", "-xelf", "all", so], cwd=d, capture_output=True)
-        cub = [f for f in os.listdir(d) if f.startswith("stm_kernels")][0]
-        txt = subprocess.run(["nvdisasm", "-g", "-c", os.path.join(d, cub)], capture_output=True, text=True).stdout
+        # the interpreter kernel lives in stm_kernels.cu, every translated cartridge in its own translation unit
+        cubs = [f for f in os.listdir(d) if f.endswith(".cubin") and (f.startswith("stm_kernels") or f.startswith("xl_"))]
+        txt = "".join(subprocess.run(["nvdisasm", "-g", "-c", os.path.join(d, c)], capture_output=True, text=True).stdout for c in cubs)
     secs, cur, cf, cl = {}, None, None, None
     for l in txt.splitlines():
         m = re.match(r"\s*\.section\s+\.text\.(\S+?),", l)
@@ -69,7 +70,7 @@ def main():
     tot = sum(agg.values())
     stot = max(1, sum(samp.values()))
     src = {}
-    for f in ("emu_core.cuh", "stm_kernels.cu"):
+    for f in ("emu_core.cuh", "stm_kernels.cu", "stm_step.cuh"):
         src[f] = open(os.path.join(ROOT, "softtreemax_b200", "csrc", f)).read().splitlines()
     gen = os.path.join(ROOT, "softtreemax_b200", "csrc", "gen")
     for f in os.listdir(gen) if os.path.isdir(gen) else []:
