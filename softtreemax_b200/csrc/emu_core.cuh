@@ -1022,7 +1022,12 @@ struct Emu {
     // Everything after the fetch.  kConst = the caller passes compile-time constants (a translated
     // cartridge, csrc/gen/xl_*.cuh): decode, addressing and dispatch then fold away at compile time and
     // what is left is the few instructions this one 6502 instruction needs.
-    template <bool kConst>
+    // kBlock (translated cores only) = the instruction is part of a straight-line block: it retires without
+    // the end-of-line test (the translator places that test at block ends, and sends an instruction that may
+    // touch TIA / RIOT beyond the end of the line to the interpreter beforehand), and the return value is
+    // "branch taken" for a branch, false otherwise.  Running CPU-and-RAM-only instructions a little past the
+    // end of a scanline before the line is wrapped changes nothing: end_line() reads no CPU or RAM state.
+    template <bool kConst, bool kBlock = false>
     STM_DEV bool exec_body(const uint32_t w, uint32_t b1, uint32_t b2)
     {
         const uint32_t am = w & 7, kind = (w >> 5) & 3, grp = (w >> 13) & 31, data = w >> 22;
@@ -1051,7 +1056,8 @@ struct Emu {
         if (grp == G_BRANCH) {
             uint32_t fsel = data & 3;
             bool fset = fsel == 0 ? (zn & 0x180u) != 0 : (fsel == 1 ? (p & FV) != 0 : (fsel == 2 ? (p & FC) != 0 : (zn & 0xFFu) == 0));
-            if (fset == ((data & 4) != 0)) {
+            const bool taken = fset == ((data & 4) != 0);
+            if (taken) {
                 uint32_t t = (npc + (uint32_t)(int32_t)(int8_t)(uint8_t)b1) & 0xFFFF;
                 cyc += 1 + (((t ^ npc) & 0xFF00) ? 1u : 0u);
                 npc = t;
@@ -1059,6 +1065,7 @@ struct Emu {
             pc = npc;                                          // nothing else to do for a branch: retire
             hcyc += (int32_t)cyc;
             timer -= (int32_t)cyc;
+            if (kBlock) return taken;
             return hcyc >= STM_CYC_PER_LINE;                   // (a branch cannot end the frame)
         }
 
@@ -1172,6 +1179,7 @@ struct Emu {
         pc = npc;
         hcyc += (int32_t)cyc;
         timer -= (int32_t)cyc;
+        if (kBlock) return false;
         return hcyc + brk >= STM_CYC_PER_LINE;
     }
     STM_DEV void finish_line()

@@ -26,7 +26,9 @@ def host_core():
     import subprocess
     d = os.path.join(ROOT, "tests", "tools")
     so = os.path.join(d, "libhost_core.so")
+    gen = os.path.join(ROOT, "softtreemax_b200", "csrc", "gen")
     srcs = [os.path.join(d, "host_core.cpp"), os.path.join(ROOT, "softtreemax_b200", "csrc", "emu_core.cuh")]
+    srcs += [os.path.join(gen, f) for f in sorted(os.listdir(gen)) if f.endswith(".cuh")]
     if not os.path.exists(so) or any(os.path.getmtime(s) > os.path.getmtime(so) for s in srcs):
         subprocess.check_call(["/usr/bin/g++", "-O2", "-std=c++17", "-fPIC", "-shared", "-ffp-contract=off", "-Wno-unknown-pragmas",
                                "-o", so, srcs[0]])

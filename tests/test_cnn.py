@@ -69,3 +69,77 @@ def test_cnn_on_real_leaf_stacks(orc=None):
         assert (val.cpu() - ref_v[:, 0]).abs().max().item() <= 3e-2 * ref_v.abs().max().item()
     finally:
         eng.close()
+
+
+def test_cnn_crosses_the_chunk_boundary():
+    """stm_cnn_forward works in chunks of 32 768 images (csrc/stm_cnn.cu); n = 32 768 + 33 crosses that boundary.
+    A random sample of 256 rows, always including the rows either side of the boundary and the very last one, is
+    compared against the fp32 restatement and the bf16 emulation with the tolerances stated at the top."""
+    from oracle import policy_ref
+    from softtreemax_b200.engine import Engine
+    n, A = 32768 + 33, 4
+    eng = Engine("synth_breakout")
+    try:
+        params = policy_ref.make_params(A, seed=9)
+        params["action_net.weight"] = params["action_net.weight"] * 50
+        g = torch.Generator().manual_seed(77)
+        base = torch.randint(0, 256, (512, 4, 84, 84), generator=g, dtype=torch.uint8)
+        idx = torch.randint(0, 512, (n,), generator=g)
+        obs = base[idx].contiguous()
+        obs[:, 0, 0, 0] = (torch.arange(n) % 251).to(torch.uint8)                     # every image differs
+        obs[:, 3, 83, 83] = (torch.arange(n) // 251 % 251).to(torch.uint8)
+        eng.cnn_set_weights(params)
+        act, val = eng.cnn_forward(obs.to(eng.device))
+        torch.cuda.synchronize()
+        pick = torch.cat([torch.tensor([0, 32766, 32767, 32768, 32769, n - 2, n - 1]),
+                          torch.randint(0, n, (249,), generator=g)])
+        _, ref_a, ref_v = policy_ref.nature_cnn_forward(params, obs[pick])
+        emu_a, emu_v = bf16_emulation(params, obs[pick])
+        sa, sv = ref_a.abs().max().item(), ref_v.abs().max().item()
+        assert torch.isfinite(act).all() and torch.isfinite(val).all()
+        assert (act[pick].cpu() - emu_a).abs().max().item() <= 5e-3 * sa
+        assert (val[pick].cpu() - emu_v[:, 0]).abs().max().item() <= 5e-3 * sv
+        assert (act[pick].cpu() - ref_a).abs().max().item() <= 3e-2 * sa
+        assert (val[pick].cpu() - ref_v[:, 0]).abs().max().item() <= 3e-2 * sv
+    finally:
+        eng.close()
+
+
+# Tolerance of the SoftTreeMax logits (K4 -> K5) against the fp32 restatement of the whole policy
+# (oracle/policy_ref.py: NatureCNN in fp32 -> actor_critic_ts.py:60-95 -> utils.py:52-57), per element:
+#     |logit_kernel - logit_fp32| <= LOGIT_ATOL + LOGIT_RTOL * |logit_fp32|
+# on SB3-initialised weights (policy-head gain 0.01) and with the head scaled x50 (a trained, peaked policy).
+LOGIT_ATOL, LOGIT_RTOL = 4e-3, 1e-2
+
+
+@pytest.mark.parametrize("name,A,depth", [("Breakout d2", 4, 2), ("Breakout d3", 4, 3), ("Pong d3", 6, 3), ("MsPacman d2", 9, 2)])
+@pytest.mark.parametrize("head_gain", [1.0, 50.0])
+def test_softtreemax_logits_tolerance(name, A, depth, head_gain):
+    from oracle import policy_ref
+    from softtreemax_b200 import ops
+    from softtreemax_b200.engine import Engine
+    R, L = 3, A ** depth
+    eng = Engine("synth_breakout")
+    try:
+        params = policy_ref.make_params(A, seed=4)
+        params["action_net.weight"] = params["action_net.weight"] * head_gain
+        g = torch.Generator().manual_seed(A * 10 + depth)
+        obs = torch.randint(0, 256, (R * L, 4, 84, 84), generator=g, dtype=torch.uint8)
+        obs[:, :, 30:, :] //= 6
+        rewards = torch.randint(-1, 2, (R, L), generator=g).float()
+        eng.cnn_set_weights(params)
+        head, val = eng.cnn_forward(obs.to(eng.device))
+        for cumulative in (False, True):
+            logits, _, vmax = ops.softtreemax_logits_full(eng, head.reshape(R, L, A), rewards.to(eng.device), 0.99 ** depth, 1.0, 1.0,
+                                                          0.001, cumulative, values=val.reshape(R, L))
+            torch.cuda.synchronize()
+            _, ref_head, ref_val = policy_ref.nature_cnn_forward(params, obs)
+            ref_logits, _, ref_vmax = policy_ref.softtreemax_logits(ref_head.reshape(R, L, A), rewards, A, 0.99 ** depth, 1.0, 1.0, 0.001,
+                                                                    cumulative, values=ref_val.reshape(R, L))
+            err = (logits.cpu() - ref_logits).abs()
+            bound = LOGIT_ATOL + LOGIT_RTOL * ref_logits.abs()
+            assert (err <= bound).all(), f"{name} cumulative={cumulative}: max err {err.max().item():.3e} (bound {bound.min().item():.3e})"
+            verr = (vmax.cpu() - ref_vmax).abs()
+            assert (verr <= 2e-2 + 2e-2 * ref_vmax.abs()).all(), f"{name}: leaf-value max err {verr.max().item():.3e}"
+    finally:
+        eng.close()
