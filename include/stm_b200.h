@@ -76,10 +76,27 @@ int stm_set_scratch_envs(stm_ctx *ctx, int n_envs);
  * stm_step(render=1), per-pixel max, and frame stacking:
  *   child_stacks[i] = concat(parent_stacks[i / fanout][1:4], new_frame_i)       (u8, 4x84x84)
  * Replaces generate_frames' grey/rescale stage + cule_bfs.py:168-172
- * (`th.max`, `replicate_state`, `th.cat`).  fanout = 1 with parent == the env's own stack gives the
- * plain frame-stack update of a root env (environments/cule_env.py:83,93). */
+ * (`th.max`, `replicate_state`, `th.cat`).  fanout = 1 with parent = the env's previous stack gives the
+ * plain frame-stack update of a root env (environments/cule_env.py:83,93).  parent_stacks and child_stacks
+ * must NOT overlap (the kernel moves the three older planes from many thread blocks at once): an
+ * overlapping pair is refused with STM_ERR_ARG.  The same holds for stm_step_frames_noalloc. */
 int stm_frames(stm_ctx *ctx, const uint8_t *parent_stacks, uint8_t *child_stacks, int n, int fanout,
                void *stream);
+
+/* One emulated FRAME (not a whole agent step) + that frame's reward/done/lives update, for hosts that drive the emulator
+ * frame by frame through raw pointers as the reference does: `super(AtariEnv, env).step(fire_reset, False, actions_ptr,
+ * 0, done_ptr, 0)` followed by `env.get_data(episodic_life, gamma**depth, done_ptr, rewards_ptr, lives_ptr)`
+ * (cule_bfs.py:154-158).  Differences from stm_step(frameskip = 1): `action_codes` are ALE action codes (what
+ * `action_set.repeat(...)` holds, cule_bfs.py:144), not indices into the minimal set; and `frozen` (n bytes, or NULL =
+ * done[]) names the envs that sit the frame out — pass the done flags as they were when the AGENT step began and the
+ * four calls of an agent step equal one stm_step(frameskip = 4) bit for bit (an env that finishes in frame 1 of 4 still
+ * plays frames 2 and 3, as inside stm_step).  The frame is always kept for stm_frame_obs. */
+int stm_step_frame(stm_ctx *ctx, uint8_t *states, const uint8_t *action_codes, int n, int episodic_life, float weight,
+                   float *rewards, uint8_t *done, int32_t *lives, const uint8_t *frozen, void *stream);
+/* Grey 84x84 observation of the frame the last stm_step_frame (or stm_step with render) emulated, n x 84 x 84 u8; an env
+ * that sat the frame out gets zeros.  Replaces `env.generate_frames(rescale, False, num_channels, obs_ptr)`
+ * (cule_bfs.py:162-167); the max over two such frames is the caller's (`th.max`, cule_bfs.py:168). */
+int stm_frame_obs(stm_ctx *ctx, uint8_t *obs, int n, void *stream);
 
 /* Whole breadth-first expansion of n_roots roots to `depth` levels: cule_bfs.py:98-209, batched
  * over roots (reference: one root per call).

@@ -40,6 +40,9 @@ _SIGS = {
     "stm_expand": (C.c_int, [C.c_void_p] * 9 + [C.c_int, C.c_int, C.c_void_p]),
     "stm_step": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_float,
                            C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]),
+    "stm_step_frame": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_float,
+                                 C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "stm_frame_obs": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]),
     "stm_max_step_envs": (C.c_int, [C.c_void_p]),
     "stm_set_scratch_envs": (C.c_int, [C.c_void_p, C.c_int]),
     "stm_frames": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p]),

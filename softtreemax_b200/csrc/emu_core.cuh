@@ -790,29 +790,29 @@ struct Emu {
         // line stays reusable); HMxx / HMCLR are not read by the renderer at all.
         if (reg >= 0x04 && reg <= 0x0F) {                                   // NUSIZ0..PF2 are laid out in register order
             uint32_t o = O_NUSIZ0 + (reg - 4);
-            if (m.ld8(o) == v) return;
+            if (STM_LIKELY(m.ld8(o) == v)) return;
             catchup(x_of(acc)); m.st8(o, v); tia_dirty(); return;
         }
         if (reg >= 0x1D && reg <= 0x1F) {                                   // ENAM0, ENAM1, ENABL
             uint32_t o = O_ENAM0 + (reg - 0x1D);
-            if (m.ld8(o) == v) return;
+            if (STM_LIKELY(m.ld8(o) == v)) return;
             catchup(x_of(acc)); m.st8(o, v); tia_dirty(); return;
         }
         if (reg >= 0x20 && reg <= 0x24) { m.st8(O_HMP0 + (reg - 0x20), v); return; }   // HMP0..HMBL
         if (reg >= 0x25 && reg <= 0x27) {                                   // VDELP0, VDELP1, VDELBL follow them
             uint32_t o = O_HMP0 + (reg - 0x20);
-            if (m.ld8(o) == v) return;
+            if (STM_LIKELY(m.ld8(o) == v)) return;
             catchup(x_of(acc)); m.st8(o, v); tia_dirty(); return;
         }
         if (reg == 0x2B) { m.st8(O_HMP0, 0); m.st8(O_HMP1, 0); m.st8(O_HMM0, 0); m.st8(O_HMM1, 0); m.st8(O_HMBL, 0); return; }
         if (reg == 0x1B) {
             uint32_t g1 = m.ld8(O_GRP1);
-            if (m.ld8(O_GRP0) == v && m.ld8(O_GRP1_OLD) == g1) return;
+            if (STM_LIKELY(m.ld8(O_GRP0) == v && m.ld8(O_GRP1_OLD) == g1)) return;
             catchup(x_of(acc)); m.st8(O_GRP0, v); m.st8(O_GRP1_OLD, g1); tia_dirty(); return;
         }
         if (reg == 0x1C) {
             uint32_t g0 = m.ld8(O_GRP0), bl = m.ld8(O_ENABL);
-            if (m.ld8(O_GRP1) == v && m.ld8(O_GRP0_OLD) == g0 && m.ld8(O_ENABL_OLD) == bl) return;
+            if (STM_LIKELY(m.ld8(O_GRP1) == v && m.ld8(O_GRP0_OLD) == g0 && m.ld8(O_ENABL_OLD) == bl)) return;
             catchup(x_of(acc)); m.st8(O_GRP1, v); m.st8(O_GRP0_OLD, g0); m.st8(O_ENABL_OLD, bl); tia_dirty(); return;
         }
         catchup(x_of(acc));

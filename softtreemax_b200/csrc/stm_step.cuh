@@ -15,6 +15,9 @@ struct StmStepArgs {
     const uint32_t *rom; const uint32_t *lut; const uint2 *pre; uint32_t *scratch; uint8_t *stepped;
     int n, frameskip, episodic_life, render; uint32_t rom_words; float weight;
     stm::GameParams gp;
+    // frame-by-frame driving (stm_step_frame, the torchcule-style surface): `frozen` decides which envs sit the frame out
+    // (the done flags as they were when the agent step began) instead of done[], and `actions` holds ALE action codes
+    const uint8_t *frozen; int action_codes;
 };
 
 namespace stm {
@@ -118,11 +121,12 @@ stm_step_kernel(const StepArgs a)
     }
     __syncthreads();
     uint32_t done = valid ? a.done[env] : 1u;
+    const uint32_t frozen = valid ? (a.frozen ? (uint32_t)a.frozen[env] : done) : 1u;
     // lanes that emulate; they advance scanline by scanline in lock-step (Emu::run_frame)
-    const uint32_t lanes = __ballot_sync(0xFFFFFFFFu, valid && !done);
+    const uint32_t lanes = __ballot_sync(0xFFFFFFFFu, valid && !frozen);
     if (!valid) return;
-    if (a.stepped) a.stepped[env] = done ? 0 : 1;
-    if (done) return;                                    // frozen env: nothing changes
+    if (a.stepped) a.stepped[env] = frozen ? 0 : 1;
+    if (frozen) return;                                  // frozen env: nothing changes
 
     DevMem m;
     m.blob = reinterpret_cast<uint8_t *>(sblob + tid);
@@ -134,7 +138,7 @@ stm_step_kernel(const StepArgs a)
     int lives = a.lives[env];
     float rew = a.rewards[env];
     uint32_t act = a.actions ? a.actions[env] : (uint32_t)(env % (int)a.gp.n_actions);
-    uint32_t ale = a.gp.actions[act];
+    uint32_t ale = a.action_codes ? act : (uint32_t)a.gp.actions[act];
     for (int f = 0; f < a.frameskip; f++) {
         bool want = a.render && f >= a.frameskip - 2;
         // the newest frame always goes to slot 1, the one before it to slot 0

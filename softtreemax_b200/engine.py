@@ -17,6 +17,8 @@ from ._lib import STATE_BYTES, StmError, check, lib
 def _ptr(t):
     if t is None:
         return None
+    if isinstance(t, int):                       # a raw address, as the reference passes `tensor.data_ptr()`
+        return C.c_void_p(t)
     if isinstance(t, np.ndarray):
         assert t.flags["C_CONTIGUOUS"]
         return t.ctypes.data_as(C.c_void_p)
@@ -94,6 +96,16 @@ class Engine:
         check(lib().stm_step(self._h, _ptr(states), _ptr(actions), n, frameskip, int(episodic_life),
                              float(weight), _ptr(rewards), _ptr(done), _ptr(lives), int(render),
                              self._stream()), self._h)
+
+    def step_frame(self, states, action_codes, n, episodic_life, weight, rewards, done, lives, frozen=None):
+        """One emulated frame + get_data (stm_step_frame).  action_codes / rewards / done / lives may be raw device
+        addresses (ints): the torchcule-style calls of the reference hand over `data_ptr()` values."""
+        check(lib().stm_step_frame(self._h, _ptr(states), _ptr(action_codes), int(n), int(episodic_life), float(weight),
+                                   _ptr(rewards), _ptr(done), _ptr(lives), _ptr(frozen), self._stream()), self._h)
+
+    def frame_obs(self, obs, n):
+        """Grey 84x84 observation of the last emulated frame into `obs` (tensor or raw device address), n x 84 x 84 u8."""
+        check(lib().stm_frame_obs(self._h, _ptr(obs), int(n), self._stream()), self._h)
 
     def frames(self, parent_stacks, n, fanout=1, out=None):
         if out is None:

@@ -132,15 +132,16 @@ class SoftTreeMaxPolicy(ActorCriticCnnPolicyDepth0):
         if learn_alpha or learn_beta:                                                                # :34-39
             self.optimizer = self.optimizer_class(self.parameters(), lr=lr_schedule(1), **self.optimizer_kwargs)
         self.use_leaves_v = use_leaves_v
-        self._weights_version = None
 
     # ------------------------------------------------------------------------------------------
     def _sync_kernel_weights(self):
         """K4 holds a bf16 re-tiled copy of the parameters: refresh it when they changed."""
-        ver = tuple(p._version for p in self.parameters())
-        if ver != self._weights_version:
+        # The tiled copy lives in the Engine (one per cartridge and GPU, shared by every policy on it): the
+        # Engine remembers whose parameters, and which version of them, it holds.
+        ver = (id(self), tuple(p._version for p in self.parameters()))
+        if getattr(self.eng, "_cnn_owner", None) != ver:
             self.eng.cnn_set_weights(self.kernel_params())
-            self._weights_version = ver
+            self.eng._cnn_owner = ver
 
     def hash_obs(self, obs):                                                                         # :196-197
         return (obs[:, -2:, :, :].int()).view(obs.shape[0], -1).sum(dim=1)
@@ -234,7 +235,8 @@ class SoftTreeMaxPolicy(ActorCriticCnnPolicyDepth0):
         return values, log_prob, dist.entropy()
 
     def predict(self, obs, state=None, mask=None, deterministic=False):                              # :272-273
-        return self.forward(th.as_tensor(obs, dtype=th.float32, device=self.device), deterministic)[0], None
+        # numpy out, like SB3's BasePolicy.predict (evaluate_policy feeds it to env.step)
+        return self.forward(th.as_tensor(obs, dtype=th.float32, device=self.device), deterministic)[0].cpu().numpy(), None
 
     # ------------------------------------------------------------------------------------------
     def _get_data(self):                                                                             # :230-252

@@ -59,9 +59,14 @@ class PPO:
                 ep_rewards.append(self._ep_ret)
                 self._ep_ret = 0.0
                 obs = self.env.reset()
-        with th.no_grad():                                   # bootstrap with the depth-0 value of the last obs
-            feats = self.policy.extract_features(th.from_numpy(obs)[None].to(self.policy.device))
-            last_val = float(self.policy.value_net(feats).reshape(-1)[0])
+        with th.no_grad():
+            if getattr(self.policy, "use_leaves_v", False):
+                # the stored val[t] are tree values (max over leaves): bootstrap with the same definition.  The tree of
+                # this observation stays in the leaf cache and serves the first step of the next rollout.
+                last_val = float(self.policy.forward(th.from_numpy(obs).float()[None])[1].reshape(-1)[0])
+            else:                                            # SB3: predict_values = the depth-0 value of the last obs
+                feats = self.policy.extract_features(th.from_numpy(obs)[None].to(self.policy.device))
+                last_val = float(self.policy.value_net(feats).reshape(-1)[0])
         adv = np.zeros(n, np.float32)
         gae = 0.0
         for t in reversed(range(n)):                         # GAE(lambda), SB3 RolloutBuffer.compute_returns_and_advantage

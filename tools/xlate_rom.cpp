@@ -165,13 +165,23 @@ int main(int argc, char **argv)
     {
         std::vector<uint32_t> case_no(65536, 0);
         for (size_t k = 0; k < label_list.size(); k++) case_no[label_list[k]] = (uint32_t)k + 1;
+        // entry points that some block jumps to directly get a goto label as well
+        std::set<uint32_t> jumped;
+        for (const Ins &q : ins) {
+            uint32_t a16;
+            if (q.grp == stm::G_BRANCH) a16 = ((0x1000u | (q.off & mask)) + 2u + (uint32_t)(int32_t)(int8_t)q.b1) & 0x1FFFu;
+            else if ((q.grp == stm::G_JMP && q.am == 3) || q.grp == stm::G_JSR) a16 = q.b1 | (q.b2 << 8);
+            else continue;
+            if (a16 & 0x1000) jumped.insert(at(q.off >> 12, a16 & 0x1FFF));
+        }
         for (size_t i = 0; i < ins.size(); i++) {
             const Ins &q = ins[i];
             const bool labeled = label_set.count(q.off) != 0;
             const bool flow = q.grp == stm::G_BRANCH;
             const bool leaves = q.grp == stm::G_JMP || q.grp == stm::G_JSR || q.grp == stm::G_RTS || q.grp == stm::G_RTI || q.grp == stm::G_BRK;
             // a run that falls into a labelled successor placed a split there: test the end of the line before crossing it
-            if (labeled) fprintf(o, "            case %u: L_%04X:                                              // image offset 0x%04X\n", case_no[q.off], q.off, q.off);
+            if (labeled && jumped.count(q.off)) fprintf(o, "            case %u: L_%04X:                                              // image offset 0x%04X\n", case_no[q.off], q.off, q.off);
+            else if (labeled) fprintf(o, "            case %u:                                                      // image offset 0x%04X\n", case_no[q.off], q.off);
             if (q.touch) fprintf(o, "                if (STM_UNLIKELY(e.hcyc > %d)) goto interp;\n", 76 - (int)q.cmax);
             // direct jump to a static target on the bus (same bank) when it is a translated entry point, else the dispatcher
             auto target_goto = [&](uint32_t addr16) {
