@@ -28,10 +28,13 @@ STANDS_FOR = {"synth_breakout": "BreakoutNoFrameskip-v4", "synth_pong": "PongNoF
 METRIC = "tree_leaf_states_per_sec"
 UNIT = "leaves/s"
 CYCLES_PER_NODE_STEP = 4 * 262 * 76          # emulated CPU cycles per node-step (NTSC nominal)
-# DRAM bytes per env of one K2 launch, from the `ncu --set full` capture summarised in
-# profiles/r01_k2_step_ncu_full_summary.txt: (dram__bytes_read.sum + dram__bytes_write.sum) / 65 536 envs.
-# It is the native-frame scratch (2 frames x 168 sampled rows x 160 B) plus the 512 B state round trip.
-K2_NCU_DRAM_BYTES_PER_ENV = (95.111936e6 + 3.443775e9) / 65536
+# From the `ncu --set full` capture of both K2 launches of a depth-2 step of 4 096 synth_breakout roots (16 384 + 65 536 envs),
+# summarised in profiles/r02_k2_block_ncu_full_summary.txt:
+#   DRAM bytes per env   = (dram__bytes_read.sum + dram__bytes_write.sum) / envs: the native-frame scratch + the 512 B state trip;
+#   warp instructions per env (node-step) = smsp__inst_executed.sum / envs: what K2's issue-slot roofline is computed from.
+K2_NCU_DRAM_BYTES_PER_ENV = (14.589184e6 + 0.828351e9 + 87.867904e6 + 3.432753e9) / 81920
+K2_NCU_WARP_INST_PER_ENV = (256814930 + 887476686) / 81920
+K2_NCU_ISSUE_ACTIVE = {"16384_envs": 0.1329, "65536_envs": 0.2092}       # smsp__issue_active of the two launches
 
 
 def peaks():
@@ -119,7 +122,8 @@ def run_reference(args, rank):
     line = {"impl": "reference", "metric": METRIC, "value": rate, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "u8", "data": "synthetic",
-            "config": workload_config(args),
+            "config": dict(workload_config(args), timed_sample=sample,
+                           note="a rate: the CPU arm times 64 roots of this workload repeatedly, not roots_per_gpu roots per step"),
             "cpu_baseline": {"value": rate, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample},
             "e2e": {"value": rate, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "note": "reference CuLE CPU back-end unavailable on this box; oracle port timed instead"}
@@ -141,6 +145,154 @@ def workload_config(args):
             "parallelism": f"roots sharded over {args.gpus} GPU(s), no data-path collective"}
 
 
+def _sb3_params(A, seed=4):
+    """Random-init weights of the architecture: orthogonal, SB3 gains (reference default seed 4, utils.py:67)."""
+    import math
+    import torch
+    g = torch.Generator().manual_seed(seed)
+    shapes = {"cnn.0": (32, 4, 8, 8), "cnn.2": (64, 32, 4, 4), "cnn.4": (64, 64, 3, 3), "linear.0": (512, 3136),
+              "action_net": (A, 512), "value_net": (1, 512)}
+    params = {}
+    for k, shp in shapes.items():
+        w = torch.empty(shp)
+        torch.nn.init.orthogonal_(w, gain={"action_net": 0.01, "value_net": 1.0}.get(k, math.sqrt(2)), generator=g)
+        params[k + ".weight"], params[k + ".bias"] = w, torch.zeros(shp[0])
+    return params
+
+
+def run_leafshard(args, eng, rank, world, local, steps):
+    """BASELINE.json configs[2]: PongNoFrameskip-v4-class (A = 6) tree_depth 3, ONE tree, its 216 leaves sharded over the ranks
+    by leaf block: every rank expands the first levels, keeps its block and resumes from there (stm_bfs_resume), evaluates its
+    leaves with K4, reduces them per first action and the ranks exchange 2*A floats (NCCL all-gather) to finish the logits.
+    Each step is one SoftTreeMax policy evaluation of the root; the result is checked against the whole tree on one GPU."""
+    import torch
+    import torch.distributed as dist
+    from softtreemax_b200 import shard
+    from softtreemax_b200.engine import Engine
+    from softtreemax_b200.roots import make_roots
+    game, depth = "synth_pong", 3
+    own = eng is None
+    if own:
+        eng = Engine(game, device=local)
+    A = eng.n_actions
+    states, stacks = make_roots(eng, 1, seed=1234)                       # the same root on every rank
+    eng.cnn_set_weights(_sb3_params(A))
+    val_coef, beta = 0.99 ** depth, 1.0
+
+    def one():
+        blk = shard.expand_leaf_block(eng, states[0], stacks[0], depth, rank, world)
+        if blk["stacks"].shape[0]:
+            head, _ = eng.cnn_forward(blk["stacks"].contiguous())
+        else:
+            head = torch.empty((0, A), device=eng.device)
+        stat, cnt = shard.partial_action_stats(head, blk["rewards"], blk["first_action"], A, val_coef, beta)
+        return shard.combine_action_stats(stat, cnt)
+
+    for _ in range(3):
+        raw = one()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        raw = one()
+    e1.record()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    ms = shard.max_over_ranks([e0.elapsed_time(e1)], eng.device)[0]
+    # whole tree on this GPU, for the check
+    full = eng.bfs(states, stacks, depth)
+    head, _ = eng.cnn_forward(full["stacks"])
+    fa = torch.arange(A ** depth, device=eng.device) // (A ** (depth - 1))
+    st, ct = shard.partial_action_stats(head, full["rewards"], fa, A, val_coef, beta)
+    ref = st - torch.log(ct)
+    err = float((raw - ref).abs().max())
+    if own:
+        eng.close()
+    return {"metric": "softtreemax_policy_evals_per_sec", "mode": "leafshard", "value": steps / (ms / 1e3), "unit": "evals/s",
+            "ms_per_step": ms / steps, "n_gpus": world, "steps": steps,
+            "leaves_per_sec": A ** depth * steps / (ms / 1e3),
+            "config": {"workload": f"{game} (stands for PongNoFrameskip-v4, A={A}) tree_depth={depth}, one tree of {A ** depth} leaves "
+                                   f"split into {world} leaf block(s)", "scaling": "strong"},
+            "collective": {"op": "all_gather", "backend": "nccl" if world > 1 else "none (one rank)", "bytes_per_rank": 2 * A * 4,
+                           "what": "per-first-action partial logsumexp + count of the leaf logits (actor_critic_ts.py:84-85)"},
+            "max_abs_diff_vs_one_gpu_tree": err}
+
+
+def run_train(args, rank, world, local, steps):
+    """One PPO minibatch per step on every rank (main.py:54: batch 32, depth-2 Breakout-class tree, 16 leaves per root):
+    policy.evaluate_actions on 32 cached roots (K4 on 32*L + 32 images forward and backward, K5 forward and backward),
+    clipped-surrogate loss, backward, gradient all-reduce over the ranks (one flat fp32 bucket, NCCL), Adam step."""
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    from softtreemax_b200 import shard
+    from softtreemax_b200.envs import CuleEnv
+    from softtreemax_b200.policy import ActorCriticCnnTSPolicy
+    dev = torch.device("cuda", local)
+    kw = dict(env_name="BreakoutNoFrameskip-v4", color_mode="gray", repeat_prob=0.0, rescale=True, episodic_life=True, frameskip=4)
+    np.random.seed(100 + rank)
+    torch.manual_seed(4)
+    env = CuleEnv(device=dev, env_kwargs=kw, clip_reward=True, fire_reset=True)
+    depth, B = 2, 32
+    pol = ActorCriticCnnTSPolicy(env.observation_space, env.action_space, lambda _: 2.5e-4, tree_depth=depth, gamma=0.99, step_env=env,
+                                 buffer_size=128, learn_alpha=False, learn_beta=True, max_width=-1, use_leaves_v=False,
+                                 is_cumulative_mode=False, regularization=0.001, device=dev)
+    shard.broadcast_parameters(pol.parameters())
+    obs = env.reset()
+    obs_l, act_l, logp_l = [], [], []
+    while len(obs_l) < B:
+        with torch.no_grad():
+            a, v, lp = pol.forward(torch.from_numpy(np.asarray(obs)).float()[None])
+        key = int(pol.hash_obs(torch.from_numpy(np.asarray(obs)).float()[None])[0])
+        if all(key != k for k, *_ in obs_l):
+            obs_l.append((key, np.asarray(obs).copy())); act_l.append(int(a)); logp_l.append(float(lp))
+        obs, _, done, _ = env.step(int(a))
+        if done:
+            obs = env.reset()
+    ob = torch.from_numpy(np.stack([o for _, o in obs_l])).float()
+    act = torch.tensor(act_l, device=dev)
+    old_lp = torch.tensor(logp_l, device=dev)
+    adv = torch.linspace(-1, 1, B, device=dev)
+    L = env.action_space.n ** depth
+
+    def one():
+        values, logp, ent = pol.evaluate_actions(ob, act)
+        ratio = torch.exp(logp - old_lp)
+        pg = -torch.min(adv * ratio, adv * torch.clamp(ratio, 0.9, 1.1)).mean()
+        loss = pg + 0.01 * (-ent.mean()) + 1.0 * torch.nn.functional.mse_loss(torch.zeros(B, device=dev), values.reshape(-1))
+        pol.optimizer.zero_grad()
+        loss.backward()
+        shard.allreduce_gradients(pol.parameters())
+        torch.nn.utils.clip_grad_norm_(pol.parameters(), 0.5)
+        pol.optimizer.step()
+        return loss
+
+    for _ in range(2):
+        one()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        loss = one()
+    e1.record()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    ms = shard.max_over_ranks([e0.elapsed_time(e1)], dev)[0]
+    n_par = sum(p.numel() for p in pol.parameters() if p.requires_grad)
+    return {"metric": "ppo_update_images_per_sec", "mode": "train", "value": world * (B * L + B) * steps / (ms / 1e3), "unit": "images/s",
+            "ms_per_step": ms / steps, "n_gpus": world, "steps": steps, "loss": float(loss),
+            "config": {"workload": f"synth_breakout tree_depth={depth}: one PPO minibatch of {B} cached roots per rank = {B * L + B} images "
+                                   "forward + backward through NatureCNN, K5 forward + backward, Adam", "scaling": "weak"},
+            "collective": {"op": "all_reduce(sum) of the gradient", "backend": "nccl" if world > 1 else "none (one rank)",
+                           "bytes": 4 * n_par, "parameters": n_par}}
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -151,6 +303,10 @@ def main():
     ap.add_argument("--game", default=GAME, help="cartridge name (softtreemax_b200/roms/games.json)")
     ap.add_argument("--no-policy", action="store_true", help="skip the bfs + CNN + logits arm (sweeps)")
     ap.add_argument("--two-groups", action="store_true", help="time two root groups in flight on two streams even with --no-policy")
+    ap.add_argument("--no-interp", action="store_true", help="skip the interpreter-only figure (sweeps)")
+    ap.add_argument("--no-collectives", action="store_true", help="skip the leaf-shard and PPO-minibatch arms (the two NCCL collectives)")
+    ap.add_argument("--mode", default="bfs", choices=["bfs", "leafshard", "train"],
+                    help="bfs: the headline (plus every side arm); leafshard / train: only that arm (BASELINE.json configs[2] / the PPO update)")
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     ap.add_argument("--scratch-envs", type=int, default=262144, help="envs per K2/K3 pass (native-frame scratch: 67 KB each)")
@@ -176,8 +332,19 @@ def main():
         raise SystemExit("bench.py needs a CUDA device: the product path has no CPU fallback")
     torch.cuda.set_device(local)
     if world > 1:
-        os.environ["NCCL_DEBUG"] = "WARN"            # keep NCCL's version banner off stdout: one JSON line only
+        # NCCL's own log (communicator size, NVLS / ring choice) goes to stderr, so that stdout stays one JSON line
+        os.environ.setdefault("NCCL_DEBUG", "INFO")
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    if args.mode != "bfs":
+        res = (run_leafshard(args, None, rank, world, local, steps=args.steps) if args.mode == "leafshard"
+               else run_train(args, rank, world, local, steps=args.steps))
+        if rank == 0:
+            print(json.dumps(res), flush=True)
+        if world > 1:
+            dist.barrier()
+            dist.destroy_process_group()
+        return
     A, depth, R = n_actions_of(args.game), args.depth, args.roots
     L = R * A ** depth
     eng = Engine(args.game, device=local, scratch_envs=min(L, args.scratch_envs))
@@ -230,19 +397,36 @@ def main():
     per_kernel = eng.timing_read()
     eng.timing(False)
 
+    # ---------------- interpreter only (a cartridge image the library has no translation for) ----------------
+    # The headline runs the block-translated kernel of this very cartridge image (tools/xlate_rom.cpp, matched by hash).
+    # Any other image — a user-supplied ROM — gets the interpreter: the same step is timed with STM_XLATE=0 beside it.
+    ms_interp = 0.0
+    if not args.no_interp:
+        os.environ["STM_XLATE"] = "0"
+        eng_i = Engine(args.game, device=local, scratch_envs=min(L, args.scratch_envs))
+        del os.environ["STM_XLATE"]
+        for _ in range(2):
+            eng_i.bfs(states, stacks, depth, out=out)
+        barrier()
+        i0, i1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        n_i = max(2, args.steps // 2)
+        i0.record()
+        for _ in range(n_i):
+            eng_i.bfs(states, stacks, depth, out=out)
+        i1.record()
+        barrier()
+        ms_interp = i0.elapsed_time(i1) / n_i
+        eng_i.close()
+
     # ---------------- two root groups in flight (throughput mode) ----------------
-    # A depth-d step is d dependent K2 launches and the first ones leave most of the GPU idle (level 1 of 4 096
-    # roots is one warp per scheduler).  Two independent groups of roots (two contexts, two streams), started half
-    # a step apart, fill that time with the other group's last level — what a rollout with two env groups taking
-    # turns does.  Reported beside the headline, which stays one group at a time.
+    # A depth-d step is d dependent K2 launches, each bound by the latency of one emulated CPU per lane, and none fills the
+    # issue slots.  Two independent groups of roots (two contexts, two streams), started half a step apart, overlap one
+    # group's small first level with the other's last level — what a rollout with two env groups taking turns does.
+    # Reported beside the headline, which stays one group at a time.
     ms_two = 0.0
     if args.two_groups or not args.no_policy:
-        # (both groups on interpreter-only contexts: with two launches sharing the SMs the translated kernel of a small
-        # launch is no longer alone on its schedulers, which is the only place it wins)
-        os.environ["STM_XLATE"] = "0"
         eng_a = Engine(args.game, device=local, scratch_envs=min(L, args.scratch_envs))
         eng2 = Engine(args.game, device=local, scratch_envs=min(L, args.scratch_envs))
-        del os.environ["STM_XLATE"]
         states2, stacks2 = make_roots(eng2, R, seed=4321 + rank)
         out_b = dict(stacks=torch.empty_like(out["stacks"]), rewards=torch.empty_like(out["rewards"]),
                      done=torch.empty_like(out["done"]), lives=torch.empty_like(out["lives"]), states=None)
@@ -401,8 +585,22 @@ def main():
     d2h = int(L * (4 + 1 + 4))
 
     from softtreemax_b200 import shard
-    ms_total, ms_e2e, ms_policy, ms_policy_e2e, ms_pipe, ms_two = shard.max_over_ranks(
-        [ms_total, ms_e2e, ms_policy, ms_policy_e2e, ms_pipe, ms_two], dev)
+    # every rank's own step time and kernel times (each rank expands different roots: the step time is the max over ranks)
+    mine = torch.tensor([ms_total / args.steps, per_kernel["step"][0] / args.steps, per_kernel["frames"][0] / args.steps,
+                         per_kernel["clone"][0] / args.steps, ms_interp], dtype=torch.float64, device=dev)
+    if world > 1:
+        allr = [torch.empty_like(mine) for _ in range(world)]
+        dist.all_gather(allr, mine)
+    else:
+        allr = [mine]
+    per_rank = [dict(rank=i, ms_per_step=float(t[0]), k2_ms=float(t[1]), k3_ms=float(t[2]), k1_ms=float(t[3]),
+                     interpreter_only_ms_per_step=float(t[4])) for i, t in enumerate(allr)]
+    ms_total, ms_e2e, ms_policy, ms_policy_e2e, ms_pipe, ms_two, ms_interp = shard.max_over_ranks(
+        [ms_total, ms_e2e, ms_policy, ms_policy_e2e, ms_pipe, ms_two, ms_interp], dev)
+    collectives = None
+    if not args.no_collectives:
+        collectives = {"leaf_shard": run_leafshard(args, eng if args.game == "synth_pong" else None, rank, world, local, steps=max(3, args.steps)),
+                       "ppo_minibatch": run_train(args, rank, world, local, steps=max(3, min(args.steps, 6)))}
 
     if rank == 0:
         ms_step = ms_total / args.steps
@@ -422,16 +620,26 @@ def main():
         def gbs(b, ms):
             return b * args.steps / (ms / 1e3) / 1e9 if ms > 0 else None
         k2 = gbs(k2_bytes, step_ms)
-        roofline = {"kernel": "stm_step_kernel (K2: 6507+TIA+RIOT agent step)", "bound": "hbm",
-                    "achieved": k2, "peak": hbm_peak, "unit": "GB/s", "frac": k2 / hbm_peak if k2 else None,
+        # K2 is bound by issue slots / the latency of one emulated CPU per lane, not by HBM: its roofline is the
+        # warp-instruction issue rate.  achieved = warp instructions per node-step (ncu, profiles/) x node-steps / K2 time;
+        # peak = one warp instruction per cycle on each of the 148 x 4 schedulers at the SM clock sampled during the run.
+        sm_hz = 1e6 * float(clocks.get("sm_mhz") or clocks.get("sm_max_mhz") or 1965)
+        issue_peak = 148 * 4 * sm_hz / 1e9
+        issue = K2_NCU_WARP_INST_PER_ENV * node_steps * args.steps / (step_ms / 1e3) / 1e9
+        roofline = {"kernel": "stm_step_kernel (K2: 6507+TIA+RIOT agent step)", "bound": "issue",
+                    "achieved": issue, "peak": issue_peak, "unit": "G warp-instructions/s", "frac": issue / issue_peak,
+                    "achieved_source": "smsp__inst_executed.sum per env from the ncu capture (profiles/r02_k2_block_ncu_full_summary.txt: "
+                                       "%.0f warp instructions per node-step) x node-steps / the K2 time measured here" % K2_NCU_WARP_INST_PER_ENV,
+                    "peak_source": "148 SMs x 4 schedulers x SM clock sampled during the timed region",
+                    "issue_active_ncu": K2_NCU_ISSUE_ACTIVE,
                     "traffic": K2_NCU_DRAM_BYTES_PER_ENV * node_steps / max(1, step_n / args.steps),
-                    "traffic_source": "ncu --set full, profiles/r01_k2_step_ncu_full_summary.txt (per env) x envs per launch",
-                    "algorithmic_bytes_per_launch": k2_bytes / max(1, step_n / args.steps),
-                    "peak_source": peak_src,
+                    "traffic_source": "ncu --set full, profiles/r02_k2_block_ncu_full_summary.txt (per env) x envs per launch",
                     "avg_launch_ms": step_ms / max(1, step_n), "launches": step_n,
                     "share_of_step": step_ms / ms_total,
-                    "note": "K2 is issue-slot bound, not HBM bound (SURVEY §8d): its HBM floor is 2*S B/node-step, so the HBM "
-                            "fraction is small by construction; the figure of merit is emulated cycles/s below",
+                    "timing": "CUDA event pair around every K1/K2/K3 launch on the launch stream (stm_timing_*), inside the timed loop",
+                    "hbm": {"bound": "hbm", "achieved": k2, "peak": hbm_peak, "unit": "GB/s", "frac": k2 / hbm_peak if k2 else None,
+                            "algorithmic_bytes_per_launch": k2_bytes / max(1, step_n / args.steps), "peak_source": peak_src,
+                            "note": "HBM floor 2*S B/node-step: small by construction, the kernel is not memory bound"},
                     "emulated_cycles_per_s": node_steps * CYCLES_PER_NODE_STEP * args.steps / (step_ms / 1e3),
                     "node_steps_per_s": node_steps * args.steps / (step_ms / 1e3)}
         kernels = {
@@ -471,6 +679,11 @@ def main():
                 "two_groups_in_flight": None if not ms_two else {
                     "value": world * 2 * L * args.steps / (ms_two / 1e3), "unit": UNIT, "ms_per_pair_of_steps": ms_two / args.steps,
                     "how": "two independent groups of roots_per_gpu roots, two contexts on two streams half a step apart"},
+                "interpreter_only": None if not ms_interp else {
+                    "value": world * L / (ms_interp / 1e3), "unit": UNIT, "ms_per_step": ms_interp,
+                    "what": "the same step with STM_XLATE=0: what a cartridge image without a bundled translation gets"},
+                "translated_core": int(eng.translated_core),
+                "per_rank": per_rank, "collectives": collectives,
                 "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "kernels": kernels, "policy": policy,
                 "cpu_baseline": {"value": cpu_rate, "unit": UNIT, "cores": os.cpu_count() or 1, "kind": "port",
                                  "sample": f"{cpu_leaves} leaves in {cpu_dt:.1f}s: 64 roots x depth {depth} repeated, oracle port (OpenMP)"}}

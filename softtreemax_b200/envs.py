@@ -30,7 +30,6 @@ class CuleEnv:
         self.metadata = {"render.modes": ["human", "rgb_array"]}
         self.observation_space = _Space(shape=(n_frame_stack, 84, 84))
         self.action_space = _Space(n=len(actions))
-        self.rng = np.random.RandomState(0)
 
     def _reset_buffer(self):
         for _ in range(self.n_frame_stack):
@@ -52,14 +51,15 @@ class CuleEnv:
         return obs
 
     def reset_no_fire(self):                                                                # cule_env.py:56-72
+        obs = torch.zeros(84, 84, dtype=torch.uint8, device=self.env.device)          # cule_env.py:57
         if self.life_termination:
             self.life_termination = False
-            obs, *_ = self.env.step(torch.tensor([0]))
-            obs = obs[0, :, :, 0]
+            self.env.step(torch.tensor([0]))      # a no-op after the lost life; its frame is NOT shown: a zero frame is (:58-60)
         else:
             self._reset_buffer()
-            noops = self.rng.randint(self.noop_max + 1)
+            noops = np.random.randint(self.noop_max + 1)          # the globally seeded generator (utils.set_seed), :65
             obs = self.env.reset(initial_steps=noops, verbose=1)[0, :, :, 0]
+            self.env.lives[0] = 5                                 # :67
         self.last_frame = obs
         self.state_buffer.append(obs)
         self.lives = int(self.env.lives[0].item())
@@ -120,15 +120,15 @@ class CuleEnvMultiple:
         self.metadata = {"render.modes": ["human", "rgb_array"]}
         self.observation_space = _Space(shape=(n_frame_stack, 84, 84))
         self.action_space = _Space(n=len(actions))
-        self.rng = np.random.RandomState(0)
         self._ended = torch.zeros(n_envs, dtype=torch.bool, device=self.env.device)
 
     def _stack(self):
         return self.env.stacks.cpu().numpy()                                              # :50,74
 
     def reset(self):                                                                        # :44-50
-        noops = self.rng.randint(self.noop_max + 1)
+        noops = np.random.randint(self.noop_max + 1)            # the globally seeded generator, cule_env_multiple.py:47
         self.env.reset(initial_steps=noops, verbose=1)
+        self.env.lives[0] = 5                                   # :49 (env 0 only, as the reference writes it)
         self.env.stacks[:, :3] = 0                              # _reset_buffer(): three zero frames under the first observation
         self.last_frame = self.env.stacks[:, 3]
         self.lives = self.env.lives.cpu().numpy()
@@ -160,7 +160,7 @@ class CuleEnvMultiple:
         self.training = False
 
     def seed(self, seed=None):
-        self.rng = np.random.RandomState(seed)
+        np.random.seed(seed)
 
     def render(self):
         raise NotImplementedError

@@ -12,6 +12,9 @@ ENV_ALIASES = {
     "Breakout": "synth_breakout",
     "Pong": "synth_pong",
     "MsPacman": "synth_pacman",
+    # the rest of the reference's sweep (yamls/example_sweep.yml:19-26), by size of the minimal action set
+    "Asteroids": "synth_joy14", "KungFuMaster": "synth_joy14", "Gopher": "synth_joy8", "Phoenix": "synth_joy8",
+    "Krull": "synth_joy18", "NameThisGame": "synth_pong", "VideoPinball": "synth_pacman",
 }
 
 

@@ -751,6 +751,17 @@ def build():
         score_addr=[255, 76, 77], score2_addr=[255, 255, 255],
         lives_addr=255, lives_shift=0, lives_mask=255, term_addr=255, term_mask=255, term_value=0)
 
+    # Action-count classes of the reference's sweep (yamls/example_sweep.yml:19-26: Asteroids 14, Breakout 4, Gopher 8, Krull 18,
+    # KungFuMaster 14, NameThisGame 6, Phoenix 8, VideoPinball 9 minimal actions): the joystick cartridge under wider action
+    # sets.  What a tree costs depends on the branching factor A (A^d leaves per root), not on which game draws the frames.
+    fire = lambda names: [ALE[n] for n in names]
+    base = dict(games["synth_pong"])
+    games["synth_joy8"] = dict(base, stands_for="Gopher / Phoenix (8 actions)",
+                               actions=fire(["NOOP", "FIRE", "UP", "RIGHT", "LEFT", "UPFIRE", "RIGHTFIRE", "LEFTFIRE"]))
+    games["synth_joy14"] = dict(base, stands_for="Asteroids / KungFuMaster (14 actions)",
+                                actions=fire(["NOOP", "FIRE", "UP", "RIGHT", "LEFT", "DOWN", "UPRIGHT", "UPLEFT", "UPFIRE", "RIGHTFIRE",
+                                              "LEFTFIRE", "DOWNFIRE"]) + [14, 15])
+    games["synth_joy18"] = dict(base, stands_for="Krull (18 actions)", actions=list(range(18)))
     json.dump(games, open(os.path.join(out, "games.json"), "w"), indent=1, sort_keys=True)
     return games
 
