@@ -25,6 +25,7 @@ sys.path.insert(0, ROOT)
 GAME = "synth_breakout"          # default cartridge; --game overrides
 STANDS_FOR = {"synth_breakout": "BreakoutNoFrameskip-v4", "synth_pong": "PongNoFrameskip-v4",
               "synth_pacman": "MsPacmanNoFrameskip-v4", "synth_torture": "opcode/TIA torture cartridge"}
+_JSON_OUT = None                  # where the JSON line goes (stdout; a private copy of it when NCCL logs share the descriptor)
 METRIC = "tree_leaf_states_per_sec"
 UNIT = "leaves/s"
 CYCLES_PER_NODE_STEP = 4 * 262 * 76          # emulated CPU cycles per node-step (NTSC nominal)
@@ -286,7 +287,7 @@ def run_train(args, rank, world, local, steps):
     ms = shard.max_over_ranks([e0.elapsed_time(e1)], dev)[0]
     n_par = sum(p.numel() for p in pol.parameters() if p.requires_grad)
     return {"metric": "ppo_update_images_per_sec", "mode": "train", "value": world * (B * L + B) * steps / (ms / 1e3), "unit": "images/s",
-            "ms_per_step": ms / steps, "n_gpus": world, "steps": steps, "loss": float(loss),
+            "ms_per_step": ms / steps, "n_gpus": world, "steps": steps, "loss": float(loss.detach()),
             "config": {"workload": f"synth_breakout tree_depth={depth}: one PPO minibatch of {B} cached roots per rank = {B * L + B} images "
                                    "forward + backward through NatureCNN, K5 forward + backward, Adam", "scaling": "weak"},
             "collective": {"op": "all_reduce(sum) of the gradient", "backend": "nccl" if world > 1 else "none (one rank)",
@@ -332,15 +333,19 @@ def main():
         raise SystemExit("bench.py needs a CUDA device: the product path has no CPU fallback")
     torch.cuda.set_device(local)
     if world > 1:
-        # NCCL's own log (communicator size, NVLS / ring choice) goes to stderr, so that stdout stays one JSON line
+        # NCCL's own log (communicator size, NVLS / ring choice) is wanted, but it goes to file descriptor 1: keep a private
+        # copy of stdout for the one JSON line and point descriptor 1 at stderr for everything else.
         os.environ.setdefault("NCCL_DEBUG", "INFO")
-        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
+        sys.stdout.flush()
+        global _JSON_OUT
+        _JSON_OUT = os.fdopen(os.dup(1), "w")
+        os.dup2(2, 1)
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     if args.mode != "bfs":
         res = (run_leafshard(args, None, rank, world, local, steps=args.steps) if args.mode == "leafshard"
                else run_train(args, rank, world, local, steps=args.steps))
         if rank == 0:
-            print(json.dumps(res), flush=True)
+            print(json.dumps(res), file=_JSON_OUT or sys.stdout, flush=True)
         if world > 1:
             dist.barrier()
             dist.destroy_process_group()
@@ -687,7 +692,7 @@ def main():
                 "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "kernels": kernels, "policy": policy,
                 "cpu_baseline": {"value": cpu_rate, "unit": UNIT, "cores": os.cpu_count() or 1, "kind": "port",
                                  "sample": f"{cpu_leaves} leaves in {cpu_dt:.1f}s: 64 roots x depth {depth} repeated, oracle port (OpenMP)"}}
-        print(json.dumps(line), flush=True)
+        print(json.dumps(line), file=_JSON_OUT or sys.stdout, flush=True)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()

@@ -168,7 +168,7 @@ int stm_logits_bwd(stm_ctx *ctx, const float *head, const float *rewards, const 
 /* K4 — NatureCNN + heads.  stm_cnn_set_weights takes DEVICE pointers to fp32 parameters in the
  * layout SB3 1.4.0's ActorCriticCnnPolicy holds them (features_extractor.cnn.{0,2,4}, .linear.0,
  * action_net, value_net: conv (out,in,kh,kw), linear (out,in)) and re-tiles them to bf16 for the
- * tensor cores (call again after every optimizer step; synchronises `stream`).
+ * tensor cores (call again after every optimizer step; synchronises `stream`; allocates on the first call only).
  * stm_cnn_forward evaluates n observation stacks (n x 4 x 84 x 84 u8, as stm_bfs / stm_frames write
  * them; the /255 of SB3's preprocess_obs is applied inside) and writes heads n x (A+1) f32:
  * columns 0..A-1 = action_net(features), column A = value_net(features).
@@ -180,6 +180,19 @@ int stm_cnn_set_weights(stm_ctx *ctx, const float *conv1_w, const float *conv1_b
                         const float *action_b, const float *value_w, const float *value_b,
                         int n_actions, void *stream);
 int stm_cnn_forward(stm_ctx *ctx, const uint8_t *obs, long long n, float *heads, void *stream);
+
+/* K4, update path.  policies/actor_critic_ts.py:139 runs `extract_features(th.cat(all_leaves_obs))` under autograd on
+ * 32*L + 32 images per PPO minibatch (main.py:54) and SB3's PPO.train backpropagates through it (cuDNN / cuBLAS fp32 in the
+ * reference).  stm_cnn_forward_train = stm_cnn_forward for one minibatch of n <= 32 768 images that also keeps the bf16
+ * activations inside the ctx; stm_cnn_backward must follow it with the same obs and n and turns dL/dheads (n x (A+1) f32,
+ * columns as stm_cnn_forward writes them) into dL/dparameter for the twelve tensors stm_cnn_set_weights took, in their torch
+ * layouts (conv (out, in, kh, kw), linear (out, in)), OVERWRITING the twelve device buffers.  Data- and weight-gradient
+ * contractions run on the tensor cores (tcgen05, bf16 operands, fp32 accumulation; split-K for the weight gradients).
+ * One minibatch in flight per ctx; a rollout-time stm_cnn_forward in between does not disturb it. */
+int stm_cnn_forward_train(stm_ctx *ctx, const uint8_t *obs, long long n, float *heads, void *stream);
+int stm_cnn_backward(stm_ctx *ctx, const uint8_t *obs, long long n, const float *dheads, float *g_conv1_w, float *g_conv1_b,
+                     float *g_conv2_w, float *g_conv2_b, float *g_conv3_w, float *g_conv3_b, float *g_fc_w, float *g_fc_b,
+                     float *g_action_w, float *g_action_b, float *g_value_w, float *g_value_b, void *stream);
 
 /* (No counterpart in the reference: the reference never manages device memory itself.)
  * stm_step(render=1) followed by stm_frames, for callers that must not cause a device allocation:

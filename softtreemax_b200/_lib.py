@@ -61,6 +61,8 @@ _SIGS = {
                                           C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]),
     "stm_cnn_set_weights": (C.c_int, [C.c_void_p] * 13 + [C.c_int, C.c_void_p]),
     "stm_cnn_forward": (C.c_int, [C.c_void_p, C.c_void_p, C.c_longlong, C.c_void_p, C.c_void_p]),
+    "stm_cnn_forward_train": (C.c_int, [C.c_void_p, C.c_void_p, C.c_longlong, C.c_void_p, C.c_void_p]),
+    "stm_cnn_backward": (C.c_int, [C.c_void_p, C.c_void_p, C.c_longlong, C.c_void_p] + [C.c_void_p] * 12 + [C.c_void_p]),
     "stm_logits_fwd": (C.c_int, [C.c_void_p] * 6 + [C.c_int] * 3 + [C.c_float] * 4 + [C.c_int] + [C.c_void_p] * 4),
     "stm_logits_bwd": (C.c_int, [C.c_void_p] * 5 + [C.c_int] * 3 + [C.c_float] * 4 + [C.c_int] + [C.c_void_p] * 6),
 }

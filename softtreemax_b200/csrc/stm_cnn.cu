@@ -61,6 +61,8 @@ struct LayerGeom {
     int recip_ow;    // ceil(65536 / OW): pos / OW == (pos * recip_ow) >> 16 for every pos < P (checked by the host)
     int f16;         // 1: A and B operands are fp16 (conv1: u8 pixels are exact in fp16 and cheap to make), 0: bf16
     int debug;       // timing experiments only: bit0 producers skip loads, bit1 MMA thread skips the MMAs, bit2 epilogue skips stores, bit3 conv1 only, bit4 conv1 producers skip convert+store, bit5 epilogue skips the TMEM loads
+    int split_chunks; // split-K (weight-gradient GEMMs, whose K is batch x positions): > 0 = CTA column blockIdx.y handles the
+                      // K slices [y * split_chunks, (y + 1) * split_chunks) and writes its fp32 partial to out + y * M * n_real
 };
 
 __device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -190,9 +192,11 @@ stm_cnn_gemm_kernel(const void *__restrict__ in, const __nv_bfloat16 *__restrict
     static_assert(kProdWarps % 4 == 0, "epilogue warps must start at a multiple of 4");
     constexpr int kProducerThreads = kProdWarps * 32, kThreads2 = cta_threads(kProdWarps), kMmaWarp = kProdWarps + 4;
     const int tid = threadIdx.x, warp = tid >> 5;
-    const int nchunks = g.K / kChunkK;
-    const long long ntiles = (M_total + kTileM - 1) / kTileM;
+    const int kc0 = g.split_chunks > 0 ? (int)blockIdx.y * g.split_chunks : 0;
+    const int nchunks = g.split_chunks > 0 ? min(g.split_chunks, g.K / kChunkK - kc0) : g.K / kChunkK;
+    const long long ntiles = nchunks > 0 ? (M_total + kTileM - 1) / kTileM : 0;
     constexpr uint32_t kCols = (2 * N < 32) ? 32 : 2 * N;             // two accumulators
+    if (g.split_chunks > 0) out = reinterpret_cast<float *>(out) + (size_t)blockIdx.y * (size_t)M_total * (size_t)g.n_real;
 
     if (warp == kMmaWarp) {
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;"
@@ -257,7 +261,7 @@ stm_cnn_gemm_kernel(const void *__restrict__ in, const __nv_bfloat16 *__restrict
                     }
                 }
                 mbar_wait(&empty[st], ph ^ 1);
-                const int k0 = kc * kChunkK;
+                const int k0 = (kc0 + kc) * kChunkK;
                 const int kh = k0 / g.KWC, koff = k0 - kh * g.KWC;
                 const uint32_t goff = (uint32_t)((kh * g.IW * g.C + koff) * 2);
                 const uint32_t dst0 = smem_u32(sA + st * kABytes);
@@ -271,7 +275,7 @@ stm_cnn_gemm_kernel(const void *__restrict__ in, const __nv_bfloat16 *__restrict
                 }
                 }
                 if (!kResidentW) {
-                    const uint8_t *wsrc = reinterpret_cast<const uint8_t *>(wt + (size_t)kc * N_total * kChunkK + (size_t)n_off * kChunkK);
+                    const uint8_t *wsrc = reinterpret_cast<const uint8_t *>(wt + (size_t)(kc0 + kc) * N_total * kChunkK + (size_t)n_off * kChunkK);
                     const uint32_t wdst = smem_u32(sB + st * kBBytes);
                     #pragma unroll 4
                     for (int j = tid; j < kBBytes / 16; j += kProducerThreads)
@@ -865,6 +869,20 @@ __global__ void stm_tile_weights_kernel(const float *__restrict__ w, __nv_bfloat
     else dst[off] = __float2bfloat16_rn(v);
 }
 
+// The same layout for a TRANSPOSED weight matrix: row nn = (s, c) of the result (s = spatial tap / position, c = input channel: the
+// order the activations are stored in), column k = output channel, taken from the fp32 torch tensor W[k][c][s]:
+//   element (nn, k) <- w[k * (KHW * C) + (nn % C) * KHW + nn / C]
+__global__ void stm_tile_weights_T_kernel(const float *__restrict__ w, __nv_bfloat16 *__restrict__ dst, int rows, int K, int KHW, int C)
+{
+    int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= rows * K) return;
+    int nn = idx / K, k = idx % K;
+    float v = w[(size_t)k * rows + (size_t)(nn % C) * KHW + nn / C];
+    int kc = k / 64, kk = k % 64;
+    size_t off = (size_t)kc * rows * 64 + (size_t)nn * 64 + (((kk / 8) ^ (nn % 8)) * 8) + (kk % 8);
+    dst[off] = __float2bfloat16_rn(v);
+}
+
 struct CnnState {
     int A = 0;
     __nv_bfloat16 *w[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
@@ -872,6 +890,14 @@ struct CnnState {
     float *b[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
     __nv_bfloat16 *act1 = nullptr, *act2 = nullptr, *act3 = nullptr, *feat = nullptr;
     long long cap_images = 0;
+    float *head_tmp = nullptr;                         // 32 x 512 fp32 staging of the head weights (set_weights)
+    // ---- update path (stm_cnn_forward_train / stm_cnn_backward) ----
+    __nv_bfloat16 *wT[3] = {nullptr, nullptr, nullptr};   // conv2, conv3, fc weights TRANSPOSED and tiled: the B operands of the data-gradient GEMMs
+    float *wh_f32 = nullptr;                           // (A + 1) x 512 head weights in fp32 (rows: action_net, then value_net)
+    float *zeros = nullptr;                            // 3 136 zeros: the "bias" of the gradient GEMMs
+    __nv_bfloat16 *t_act1 = nullptr, *t_act2 = nullptr, *t_act3 = nullptr, *t_feat = nullptr;   // activations kept from forward_train
+    long long t_cap = 0, t_n = 0;
+    uint8_t *bwd = nullptr; size_t bwd_bytes = 0;      // backward workspace (gradients of activations, transposed operands, split-K partials)
 };
 
 template <int N, bool kResidentW, int kStages, int kProdWarps>
@@ -950,9 +976,297 @@ void free_state(CnnState *s)
 {
     if (!s) return;
     for (int i = 0; i < 5; i++) { cudaFree(s->w[i]); cudaFree(s->b[i]); }
-    cudaFree(s->w_c1);
+    for (int i = 0; i < 3; i++) cudaFree(s->wT[i]);
+    cudaFree(s->w_c1); cudaFree(s->head_tmp); cudaFree(s->wh_f32); cudaFree(s->zeros);
     cudaFree(s->act1); cudaFree(s->act2); cudaFree(s->act3); cudaFree(s->feat);
+    cudaFree(s->t_act1); cudaFree(s->t_act2); cudaFree(s->t_act3); cudaFree(s->t_feat); cudaFree(s->bwd);
     delete s;
+}
+
+
+// =========================================================================================================
+// Backward pass (update path).  Every contraction is the same tcgen05 GEMM as the forward's fully connected layer,
+//     D[M, N] = A[M, K] * B[N, K]^T,   A row-major bf16 streamed by the producers, B pre-tiled, fp32 accumulation in TMEM,
+// fed with explicitly laid-out operands (the update batch is 544 - 7 000 images: the extra passes over HBM are a few
+// hundred MB, the GEMMs stay on the tensor cores):
+//   data gradients    dX_col[rows, taps*C] = dY[rows, Cout] * W^T          (B = the transposed, tiled weights made by set_weights)
+//                     followed by a col2im gather (+ the ReLU mask of the layer below)
+//   weight gradients  dW^T[taps*C, Cout]  = col^T[taps*C, rows] * dY^T      (K = rows = batch x positions: split-K over CTA columns,
+//                     fp32 partials reduced and permuted into torch's (Cout, C, kh, kw) order by the finalize kernel)
+// The heads (A + 1 outputs) are too narrow for a tile and run on the CUDA cores.
+// =========================================================================================================
+constexpr long long kMaxTrainImages = 32768;
+
+struct SrcPlain {                     // (r, k) of a row-major [rows, ld] bf16 matrix
+    const __nv_bfloat16 *p; int ld;
+    __device__ __forceinline__ __nv_bfloat16 at(long long r, int k) const { return p[(size_t)r * ld + k]; }
+};
+struct SrcIm2colNhwc {                // (r = (img, oy, ox), k = (ky, kx, c)) of a bf16 NHWC activation
+    const __nv_bfloat16 *p; int IH, IW, C, KW, S, OW, P;
+    __device__ __forceinline__ __nv_bfloat16 at(long long r, int k) const
+    {
+        const long long img = r / P; const int pos = (int)(r - img * P), oy = pos / OW, ox = pos - oy * OW;
+        const int t = k / C, c = k - t * C, ky = t / KW, kx = t - ky * KW;
+        return p[(((size_t)img * IH + oy * S + ky) * IW + ox * S + kx) * C + c];
+    }
+};
+struct SrcIm2colU8 {                  // conv1: (r = (img, oy, ox), k = (c, ky, kx)) of the u8 NCHW observation (pixel values are exact in bf16)
+    const uint8_t *p;
+    __device__ __forceinline__ __nv_bfloat16 at(long long r, int k) const
+    {
+        const long long img = r / 400; const int pos = (int)(r - img * 400), oy = pos / 20, ox = pos - oy * 20;
+        const int c = k >> 6, ky = (k >> 3) & 7, kx = k & 7;
+        return __float2bfloat16_rn((float)p[(((size_t)img * 4 + c) * 84 + oy * 4 + ky) * 84 + ox * 4 + kx]);
+    }
+};
+struct DstRowMajor {                  // dst[k][r], row length rows_pad
+    __nv_bfloat16 *p; long long rows_pad;
+    __device__ __forceinline__ void put(int k, long long r, __nv_bfloat16 v) const { p[(size_t)k * rows_pad + r] = v; }
+};
+struct DstTiled {                     // dst = B operand [N rows = k][K = r] in the tiled, swizzled layout (see stm_tile_weights_kernel)
+    __nv_bfloat16 *p; int N;
+    __device__ __forceinline__ void put(int k, long long r, __nv_bfloat16 v) const
+    {
+        const long long kc = r >> 6; const int kk = (int)(r & 63);
+        p[(size_t)kc * N * 64 + (size_t)k * 64 + (((kk >> 3) ^ (k & 7)) << 3) + (kk & 7)] = v;
+    }
+};
+// dst(k, r) = src(r, k) for k < Kdim, r < rows_pad (zero beyond `rows`): a 32 x 32 shared-memory transpose, reads coalesced along k,
+// writes along r
+template <class Src, class Dst>
+__global__ void __launch_bounds__(256) stm_transpose_kernel(Src src, Dst dst, int Kdim, long long rows, long long rows_pad)
+{
+    __shared__ __nv_bfloat16 tile[32][34];
+    const long long r0 = (long long)blockIdx.x * 32;
+    const int k0 = blockIdx.y * 32, tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+    #pragma unroll
+    for (int j = 0; j < 4; j++) {
+        const long long r = r0 + ty + 8 * j; const int k = k0 + tx;
+        tile[ty + 8 * j][tx] = (r < rows && k < Kdim) ? src.at(r, k) : __float2bfloat16_rn(0.f);
+    }
+    __syncthreads();
+    #pragma unroll
+    for (int j = 0; j < 4; j++) {
+        const int k = k0 + ty + 8 * j; const long long r = r0 + tx;
+        if (k < Kdim && r < rows_pad) dst.put(k, r, tile[tx][ty + 8 * j]);
+    }
+}
+
+// heads backward: dfeat[i][k] = feat[i][k] > 0 ? sum_a dheads[i][a] * Wh[a][k] : 0     (ReLU of the fully connected layer folded in)
+__global__ void stm_heads_dgrad_kernel(const float *__restrict__ dheads, const float *__restrict__ wh, const __nv_bfloat16 *__restrict__ feat,
+                                       __nv_bfloat16 *__restrict__ dfeat, long long n, int A1)
+{
+    const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= n * 512) return;
+    const long long i = idx >> 9; const int k = (int)(idx & 511);
+    float acc = 0.f;
+    for (int a = 0; a < A1; a++) acc += dheads[i * A1 + a] * __ldg(wh + a * 512 + k);
+    dfeat[idx] = __float2bfloat16_rn(__bfloat162float(feat[idx]) > 0.f ? acc : 0.f);
+}
+// dWh[a][k] = sum_i dheads[i][a] * feat[i][k]; rows a < A go to the action head, row A to the value head.  grid (A1, 4), block 128.
+__global__ void stm_heads_wgrad_kernel(const float *__restrict__ dheads, const __nv_bfloat16 *__restrict__ feat, float *__restrict__ g_action_w,
+                                       float *__restrict__ g_value_w, float *__restrict__ g_action_b, float *__restrict__ g_value_b,
+                                       long long n, int A1)
+{
+    const int a = blockIdx.x, k = blockIdx.y * 128 + threadIdx.x;
+    float acc = 0.f, bsum = 0.f;
+    for (long long i = 0; i < n; i++) {
+        const float d = dheads[i * A1 + a];
+        acc += d * __bfloat162float(feat[i * 512 + k]);
+        bsum += d;
+    }
+    if (a < A1 - 1) g_action_w[a * 512 + k] = acc; else g_value_w[k] = acc;
+    if (k == 0) { if (a < A1 - 1) g_action_b[a] = bsum; else g_value_b[0] = bsum; }
+}
+// out[c] += sum_r x[r][c]  (out zeroed by the caller); cols is 32, 64 or 512
+__global__ void stm_colsum_kernel(const __nv_bfloat16 *__restrict__ x, float *__restrict__ out, long long rows, int cols)
+{
+    const int per = 256 / (cols < 256 ? cols : 256);                 // row lanes per block (1 when cols >= 256)
+    for (int c = threadIdx.x % (cols < 256 ? cols : 256); c < cols; c += 256) {
+        const int lane = cols < 256 ? threadIdx.x / cols : 0;
+        float acc = 0.f;
+        for (long long r = (long long)blockIdx.x * per + lane; r < rows; r += (long long)gridDim.x * per) acc += __bfloat162float(x[(size_t)r * cols + c]);
+        atomicAdd(out + c, acc);
+    }
+}
+// d = act > 0 ? d : 0, eight elements per thread
+__global__ void stm_relu_mask_kernel(__nv_bfloat16 *__restrict__ d, const __nv_bfloat16 *__restrict__ act, long long n8)
+{
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n8) return;
+    uint4 dv = reinterpret_cast<uint4 *>(d)[i];
+    const uint4 av = reinterpret_cast<const uint4 *>(act)[i];
+    uint32_t *dw = reinterpret_cast<uint32_t *>(&dv); const uint32_t *aw = reinterpret_cast<const uint32_t *>(&av);
+    #pragma unroll
+    for (int j = 0; j < 4; j++) {                                   // a post-ReLU bf16 is > 0 iff its bits are non-zero and the sign is clear
+        const uint32_t lo = aw[j] & 0xFFFFu, hi = aw[j] >> 16;
+        const uint32_t keep = ((lo != 0 && !(lo & 0x8000u)) ? 0x0000FFFFu : 0u) | ((hi != 0 && !(hi & 0x8000u)) ? 0xFFFF0000u : 0u);
+        dw[j] &= keep;
+    }
+    reinterpret_cast<uint4 *>(d)[i] = dv;
+}
+// col2im as a gather: dact[img][iy][ix][c] = (act > 0) * sum over the taps (ky, kx) that reach (iy, ix) of dcol[(img, oy, ox)][(ky, kx, c)]
+__global__ void stm_col2im_kernel(const __nv_bfloat16 *__restrict__ dcol, const __nv_bfloat16 *__restrict__ act, __nv_bfloat16 *__restrict__ dact,
+                                  long long n, int IH, int IW, int C, int KH, int KW, int S, int OH, int OW)
+{
+    const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= n * IH * IW * C) return;
+    const int c = (int)(idx % C); long long t = idx / C;
+    const int ix = (int)(t % IW); t /= IW;
+    const int iy = (int)(t % IH); const long long img = t / IH;
+    float acc = 0.f;
+    if (__bfloat162float(act[idx]) > 0.f) {
+        const int Kc = KH * KW * C;
+        for (int ky = iy % S; ky < KH; ky += S) {
+            const int oy = (iy - ky) / S;
+            if (iy - ky < 0 || oy >= OH) continue;
+            for (int kx = ix % S; kx < KW; kx += S) {
+                const int ox = (ix - kx) / S;
+                if (ix - kx < 0 || ox >= OW) continue;
+                acc += __bfloat162float(dcol[((size_t)img * OH * OW + oy * OW + ox) * Kc + (ky * KW + kx) * C + c]);
+            }
+        }
+    }
+    dact[idx] = __float2bfloat16_rn(acc);
+}
+// grad[nn][c * KHW + t] = scale * sum_s part[s][m = t * C + c][nn]     (fp32 split-K partials -> torch's (Cout, C, kh, kw) order)
+__global__ void stm_wgrad_finalize_kernel(const float *__restrict__ part, float *__restrict__ grad, int S, int M, int N, int KHW, int C, float scale)
+{
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= M * N) return;
+    const int m = idx / N, nn = idx - m * N;
+    float acc = 0.f;
+    for (int s2 = 0; s2 < S; s2++) acc += part[(size_t)s2 * M * N + idx];
+    const int t = m / C, c = m - t * C;
+    grad[(size_t)nn * M + (size_t)c * KHW + t] = acc * scale;
+}
+
+// D[M, N range] = A[M, K] (row-major bf16) * B[N_total, K]^T (tiled bf16).  splits > 1: split-K, fp32 partials out[split][M][N_total].
+template <int N>
+int launch_rm(stm_ctx *ctx, const __nv_bfloat16 *A, const __nv_bfloat16 *Bt, const float *zeros, void *out, long long M, int K,
+              int n_off, int N_total, int out_f32, int splits, cudaStream_t st)
+{
+    static bool attr_done = false;
+    constexpr int kStages = 4, kProdWarps = 4;
+    const size_t smem = (size_t)kStages * kABytes + (size_t)kStages * N * kChunkK * 2 + 1024;
+    if (!attr_done) {
+        cudaFuncSetAttribute(stm_cnn_gemm_kernel<N, false, kStages, kProdWarps>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 2048);
+        cudaFuncSetAttribute(stm_cnn_gemm_kernel<N, false, kStages, kProdWarps>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+        attr_done = true;
+    }
+    if (K % kChunkK || M >= (1LL << 31) - kTileM) return stm_internal_fail(ctx, STM_ERR_ARG, "stm_cnn_backward: GEMM shape");
+    const int total = K / kChunkK;
+    int split_chunks = 0, S = 1;
+    if (splits > 1) { split_chunks = (total + splits - 1) / splits; S = (total + split_chunks - 1) / split_chunks; }
+    LayerGeom g = { MODE_NHWC, 1, 1, 1, 1, K, K, 1, K, N_total, 0, out_f32, 1.0f, 65536, 0, 0, split_chunks };
+    const long long tiles = (M + kTileM - 1) / kTileM;
+    const int per_sm = smem <= 110 * 1024 ? 2 : 1;
+    long long gx = tiles < 148LL * per_sm ? tiles : 148LL * per_sm;
+    stm_cnn_gemm_kernel<N, false, kStages, kProdWarps><<<dim3((unsigned)gx, (unsigned)S), cta_threads(kProdWarps), smem, st>>>(
+        A, Bt, zeros, out, M, g, n_off, N_total);
+    stm_internal_count_launch(ctx);
+    cudaError_t e = cudaGetLastError();
+    return e == cudaSuccess ? S : stm_internal_fail(ctx, STM_ERR_CUDA, cudaGetErrorString(e));       // > 0: the number of partials written
+}
+// all N_total columns in pieces of 256 / 64 / 32
+int gemm_rm(stm_ctx *ctx, const __nv_bfloat16 *A, const __nv_bfloat16 *Bt, const float *zeros, void *out, long long M, int K, int N_total,
+            int out_f32, int splits, cudaStream_t st)
+{
+    int S = 1, n_off = 0;
+    while (n_off < N_total) {
+        int rc;
+        if (N_total - n_off >= 256) { rc = launch_rm<256>(ctx, A, Bt, zeros, out, M, K, n_off, N_total, out_f32, splits, st); n_off += 256; }
+        else if (N_total - n_off >= 64) { rc = launch_rm<64>(ctx, A, Bt, zeros, out, M, K, n_off, N_total, out_f32, splits, st); n_off += 64; }
+        else { rc = launch_rm<32>(ctx, A, Bt, zeros, out, M, K, n_off, N_total, out_f32, splits, st); n_off += 32; }
+        if (rc < 0) return rc;
+        S = rc;
+    }
+    return S;
+}
+
+template <class Src, class Dst>
+void transpose_to(stm_ctx *ctx, Src src, Dst dst, int Kdim, long long rows, long long rows_pad, cudaStream_t st)
+{
+    dim3 grid((unsigned)((rows_pad + 31) / 32), (unsigned)((Kdim + 31) / 32));
+    stm_transpose_kernel<<<grid, 256, 0, st>>>(src, dst, Kdim, rows, rows_pad);
+    stm_internal_count_launch(ctx);
+}
+
+inline long long pad64(long long v) { return (v + 63) / 64 * 64; }
+
+int backward_impl(stm_ctx *ctx, CnnState *s, const uint8_t *obs, long long n, const float *dheads, float *const *grads, cudaStream_t st)
+{
+    const int A1 = s->A + 1;
+    const long long rows1 = n * 400, rows2 = n * 81, rows3 = n * 49;
+    const long long r1p = pad64(rows1), r2p = pad64(rows2), r3p = pad64(rows3), np = pad64(n);
+    // workspace carve-up (bytes, 256-byte aligned pieces)
+    size_t off = 0;
+    auto take = [&](size_t bytes) { size_t o = off; off += (bytes + 255) & ~(size_t)255; return o; };
+    const size_t o_dfeat = take((size_t)n * 512 * 2), o_dfeatT = take((size_t)512 * np * 2), o_act3T = take((size_t)3136 * np * 2);
+    const size_t o_dact3 = take((size_t)n * 3136 * 2), o_dY3T = take((size_t)64 * r3p * 2), o_col3T = take((size_t)576 * r3p * 2);
+    const size_t o_dcol3 = take((size_t)rows3 * 576 * 2), o_dact2 = take((size_t)rows2 * 64 * 2), o_dY2T = take((size_t)64 * r2p * 2);
+    const size_t o_col2T = take((size_t)512 * r2p * 2), o_dcol2 = take((size_t)rows2 * 512 * 2), o_dact1 = take((size_t)rows1 * 32 * 2);
+    const size_t o_dY1T = take((size_t)32 * r1p * 2), o_col1T = take((size_t)256 * r1p * 2);
+    const size_t o_part = take((size_t)8 * 3136 * 512 * 4);
+    if (off > s->bwd_bytes) {
+        cudaFree(s->bwd); s->bwd = nullptr; s->bwd_bytes = 0;
+        if (cudaMalloc(&s->bwd, off) != cudaSuccess) return stm_internal_fail(ctx, STM_ERR_NOMEM, "stm_cnn_backward: workspace");
+        s->bwd_bytes = off;
+    }
+    auto B16 = [&](size_t o) { return reinterpret_cast<__nv_bfloat16 *>(s->bwd + o); };
+    float *part = reinterpret_cast<float *>(s->bwd + o_part);
+    float *g_c1w = grads[0], *g_c1b = grads[1], *g_c2w = grads[2], *g_c2b = grads[3], *g_c3w = grads[4], *g_c3b = grads[5],
+          *g_fcw = grads[6], *g_fcb = grads[7], *g_aw = grads[8], *g_ab = grads[9], *g_vw = grads[10], *g_vb = grads[11];
+    int rc, S;
+    auto colsum = [&](const __nv_bfloat16 *x, float *out, long long rows, int cols) {
+        cudaMemsetAsync(out, 0, (size_t)cols * 4, st);
+        stm_colsum_kernel<<<296, 256, 0, st>>>(x, out, rows, cols);
+        stm_internal_count_launch(ctx);
+    };
+    auto finalize = [&](float *grad, int S2, int M, int N, int KHW, int C, float scale) {
+        stm_wgrad_finalize_kernel<<<(M * N + 255) / 256, 256, 0, st>>>(part, grad, S2, M, N, KHW, C, scale);
+        stm_internal_count_launch(ctx);
+    };
+    // ---- heads (CUDA cores) + the ReLU of the fully connected layer ----
+    stm_heads_dgrad_kernel<<<(unsigned)((n * 512 + 255) / 256), 256, 0, st>>>(dheads, s->wh_f32, s->t_feat, B16(o_dfeat), n, A1);
+    stm_heads_wgrad_kernel<<<dim3(A1, 4), 128, 0, st>>>(dheads, s->t_feat, g_aw, g_vw, g_ab, g_vb, n, A1);
+    stm_internal_count_launch(ctx); stm_internal_count_launch(ctx);
+    colsum(B16(o_dfeat), g_fcb, n, 512);
+    // ---- fully connected: data gradient [n, 3136] = dfeat [n, 512] * Wfc, then conv3's ReLU ----
+    if ((rc = gemm_rm(ctx, B16(o_dfeat), s->wT[2], s->zeros, B16(o_dact3), n, 512, 3136, 0, 1, st)) < 0) return rc;
+    stm_relu_mask_kernel<<<(unsigned)((n * 3136 / 8 + 255) / 256), 256, 0, st>>>(B16(o_dact3), s->t_act3, n * 3136 / 8);
+    stm_internal_count_launch(ctx);
+    // weight gradient: [3136, 512] = act3^T [3136, n] * dfeat^T
+    transpose_to(ctx, SrcPlain{ s->t_act3, 3136 }, DstRowMajor{ B16(o_act3T), np }, 3136, n, np, st);
+    transpose_to(ctx, SrcPlain{ B16(o_dfeat), 512 }, DstTiled{ B16(o_dfeatT), 512 }, 512, n, np, st);
+    if ((S = gemm_rm(ctx, B16(o_act3T), B16(o_dfeatT), s->zeros, part, 3136, (int)np, 512, 1, 8, st)) < 0) return S;
+    finalize(g_fcw, S, 3136, 512, 49, 64, 1.0f);
+    // ---- conv3 ----
+    colsum(B16(o_dact3), g_c3b, rows3, 64);
+    transpose_to(ctx, SrcIm2colNhwc{ s->t_act2, 9, 9, 64, 3, 1, 7, 49 }, DstRowMajor{ B16(o_col3T), r3p }, 576, rows3, r3p, st);
+    transpose_to(ctx, SrcPlain{ B16(o_dact3), 64 }, DstTiled{ B16(o_dY3T), 64 }, 64, rows3, r3p, st);
+    if ((S = gemm_rm(ctx, B16(o_col3T), B16(o_dY3T), s->zeros, part, 576, (int)r3p, 64, 1, 48, st)) < 0) return S;
+    finalize(g_c3w, S, 576, 64, 9, 64, 1.0f);
+    if ((rc = gemm_rm(ctx, B16(o_dact3), s->wT[1], s->zeros, B16(o_dcol3), rows3, 64, 576, 0, 1, st)) < 0) return rc;
+    stm_col2im_kernel<<<(unsigned)((rows2 * 64 + 255) / 256), 256, 0, st>>>(B16(o_dcol3), s->t_act2, B16(o_dact2), n, 9, 9, 64, 3, 3, 1, 7, 7);
+    stm_internal_count_launch(ctx);
+    // ---- conv2 ----
+    colsum(B16(o_dact2), g_c2b, rows2, 64);
+    transpose_to(ctx, SrcIm2colNhwc{ s->t_act1, 20, 20, 32, 4, 2, 9, 81 }, DstRowMajor{ B16(o_col2T), r2p }, 512, rows2, r2p, st);
+    transpose_to(ctx, SrcPlain{ B16(o_dact2), 64 }, DstTiled{ B16(o_dY2T), 64 }, 64, rows2, r2p, st);
+    if ((S = gemm_rm(ctx, B16(o_col2T), B16(o_dY2T), s->zeros, part, 512, (int)r2p, 64, 1, 48, st)) < 0) return S;
+    finalize(g_c2w, S, 512, 64, 16, 32, 1.0f);
+    if ((rc = gemm_rm(ctx, B16(o_dact2), s->wT[0], s->zeros, B16(o_dcol2), rows2, 64, 512, 0, 1, st)) < 0) return rc;
+    stm_col2im_kernel<<<(unsigned)((rows1 * 32 + 255) / 256), 256, 0, st>>>(B16(o_dcol2), s->t_act1, B16(o_dact1), n, 20, 20, 32, 4, 4, 2, 9, 9);
+    stm_internal_count_launch(ctx);
+    // ---- conv1 (no data gradient: the input is the observation) ----
+    colsum(B16(o_dact1), g_c1b, rows1, 32);
+    transpose_to(ctx, SrcIm2colU8{ obs }, DstRowMajor{ B16(o_col1T), r1p }, 256, rows1, r1p, st);
+    transpose_to(ctx, SrcPlain{ B16(o_dact1), 32 }, DstTiled{ B16(o_dY1T), 32 }, 32, rows1, r1p, st);
+    if ((S = gemm_rm(ctx, B16(o_col1T), B16(o_dY1T), s->zeros, part, 256, (int)r1p, 32, 1, 96, st)) < 0) return S;
+    finalize(g_c1w, S, 256, 32, 1, 256, 1.0f / 255.0f);
+    cudaError_t e = cudaGetLastError();
+    return e == cudaSuccess ? STM_OK : stm_internal_fail(ctx, STM_ERR_CUDA, cudaGetErrorString(e));
 }
 
 } // namespace
@@ -1002,8 +1316,8 @@ int stm_cnn_set_weights(stm_ctx *ctx, const float *conv1_w, const float *conv1_b
     // heads: rows 0..A-1 = action_net, row A = value_net, zero padded to 32 rows
     if (!s->w[4] && cudaMalloc(&s->w[4], 32 * 512 * 2) != cudaSuccess) return stm_internal_fail(ctx, STM_ERR_NOMEM, "cudaMalloc");
     if (!s->b[4] && cudaMalloc(&s->b[4], 32 * 4) != cudaSuccess) return stm_internal_fail(ctx, STM_ERR_NOMEM, "cudaMalloc");
-    float *tmp = nullptr;
-    if (cudaMalloc(&tmp, 32 * 512 * 4) != cudaSuccess) return stm_internal_fail(ctx, STM_ERR_NOMEM, "cudaMalloc");
+    if (!s->head_tmp && cudaMalloc(&s->head_tmp, 32 * 512 * 4) != cudaSuccess) return stm_internal_fail(ctx, STM_ERR_NOMEM, "cudaMalloc");
+    float *tmp = s->head_tmp;                                        // allocated once: every later call is allocation-free
     cudaMemsetAsync(tmp, 0, 32 * 512 * 4, st);
     cudaMemsetAsync(s->b[4], 0, 32 * 4, st);
     cudaMemcpyAsync(tmp, action_w, (size_t)n_actions * 512 * 4, cudaMemcpyDeviceToDevice, st);
@@ -1012,8 +1326,24 @@ int stm_cnn_set_weights(stm_ctx *ctx, const float *conv1_w, const float *conv1_b
     cudaMemcpyAsync(s->b[4] + n_actions, value_b, 4, cudaMemcpyDeviceToDevice, st);
     stm_tile_weights_kernel<<<(32 * 512 + 255) / 256, 256, 0, st>>>(tmp, s->w[4], n_actions + 1, 32, 512, 1, 512, 0);
     stm_internal_count_launch(ctx);
+    // update path: transposed, tiled copies of conv2 / conv3 / fc (B operands of the data-gradient GEMMs) and the fp32 heads
+    {
+        struct SpecT { const float *w; int rows, K, KHW, C; } st3[3] = { { conv2_w, 512, 64, 16, 32 }, { conv3_w, 576, 64, 9, 64 }, { fc_w, 3136, 512, 49, 64 } };
+        for (int i = 0; i < 3; i++) {
+            if (!s->wT[i] && cudaMalloc(&s->wT[i], (size_t)st3[i].rows * st3[i].K * 2) != cudaSuccess)
+                return stm_internal_fail(ctx, STM_ERR_NOMEM, "stm_cnn_set_weights: cudaMalloc");
+            const int total = st3[i].rows * st3[i].K;
+            stm_tile_weights_T_kernel<<<(total + 255) / 256, 256, 0, st>>>(st3[i].w, s->wT[i], st3[i].rows, st3[i].K, st3[i].KHW, st3[i].C);
+            stm_internal_count_launch(ctx);
+        }
+        if (!s->wh_f32 && cudaMalloc(&s->wh_f32, 19 * 512 * 4) != cudaSuccess) return stm_internal_fail(ctx, STM_ERR_NOMEM, "cudaMalloc");
+        cudaMemcpyAsync(s->wh_f32, tmp, (size_t)(n_actions + 1) * 512 * 4, cudaMemcpyDeviceToDevice, st);
+        if (!s->zeros) {
+            if (cudaMalloc(&s->zeros, 3136 * 4) != cudaSuccess) return stm_internal_fail(ctx, STM_ERR_NOMEM, "cudaMalloc");
+            cudaMemsetAsync(s->zeros, 0, 3136 * 4, st);
+        }
+    }
     cudaStreamSynchronize(st);
-    cudaFree(tmp);
     cudaError_t e = cudaGetLastError();
     return e == cudaSuccess ? STM_OK : stm_internal_fail(ctx, STM_ERR_CUDA, cudaGetErrorString(e));
 }
@@ -1027,6 +1357,52 @@ int stm_debug_shift_probe(stm_ctx *ctx, const void *A, const void *B, float *out
         reinterpret_cast<const __nv_bfloat16 *>(A), reinterpret_cast<const __nv_bfloat16 *>(B), out, rows, shift, base_off);
     cudaError_t e = cudaGetLastError();
     return e == cudaSuccess ? STM_OK : stm_internal_fail(ctx, STM_ERR_CUDA, cudaGetErrorString(e));
+}
+
+// one pass of the network over c images (c <= 32 768) with the given activation buffers
+static int forward_chunk(stm_ctx *ctx, CnnState *s, const uint8_t *obs, long long c, __nv_bfloat16 *act1, __nv_bfloat16 *act2,
+                         __nv_bfloat16 *act3, __nv_bfloat16 *feat, float *heads, int dbg, cudaStream_t st)
+{
+    const int A1 = s->A + 1;
+    int rc;
+    LayerGeom g1 = { MODE_CONV1, 400, 20, 84, 84, 4, 0, 4, 256, 32, 1, 0, 1.0f / 255.0f, (65536 + 20 - 1) / 20, 1, dbg };
+    if (!(dbg & 512)) {
+        if (!(dbg & 256)) rc = launch_conv1_window(ctx, obs, s->w_c1, s->b[0], act1, c, dbg, st);
+        else rc = launch_layer<32, true, 4, 8>(ctx, obs, s->w[0], s->b[0], act1, c * 400, g1, 0, 32, st);
+        if (rc) return rc;
+    }
+    if (dbg & 8) return STM_OK;                                   // timing experiments: conv1 alone
+    if (!(dbg & 256)) {
+        // conv2: rows of two pixels on the 10 x 20 virtual grid; tap (ky, kx in {0, 2}) = input row + 10 ky + kx / 2
+        WinGeom w2 = { 200, 20, 9, 9, (65536 + 20 - 1) / 20, 8, { 0, 1, 10, 11, 20, 21, 30, 31, 0 }, 1, dbg };
+        if ((rc = launch_window<2>(ctx, act1, s->w[1], s->b[1], act2, c, w2, st))) return rc;
+        // conv3: rows of one pixel on the 9 x 9 input grid; tap (ky, kx) = input row + 9 ky + kx
+        WinGeom w3 = { 81, 9, 7, 7, (65536 + 9 - 1) / 9, 9, { 0, 1, 2, 9, 10, 11, 18, 19, 20 }, 1, dbg };
+        if ((rc = launch_window<3>(ctx, act2, s->w[2], s->b[2], act3, c, w3, st))) return rc;
+    } else {                                                      // the gather kernels (kept for A/B timing)
+        LayerGeom g2 = { MODE_NHWC, 81, 9, 20, 20, 32, 4 * 32, 2, 512, 64, 1, 0, 1.0f, (65536 + 9 - 1) / 9, 0, dbg };
+        if ((rc = launch_layer<64, true, 8, 4>(ctx, act1, s->w[1], s->b[1], act2, c * 81, g2, 0, 64, st))) return rc;
+        LayerGeom g3 = { MODE_NHWC, 49, 7, 9, 9, 64, 3 * 64, 1, 576, 64, 1, 0, 1.0f, (65536 + 7 - 1) / 7, 0, dbg };
+        if ((rc = launch_layer<64, true, 8, 4>(ctx, act2, s->w[2], s->b[2], act3, c * 49, g3, 0, 64, st))) return rc;
+    }
+    if (dbg & 512) return STM_OK;                                 // timing experiments: conv2 + conv3 alone (with bit 9: no conv1 either)
+    LayerGeom g4 = { MODE_NHWC, 1, 1, 1, 1, 3136, 3136, 1, 3136, 512, 1, 0, 1.0f, 65536, 0, dbg };
+    for (int half = 0; half < 2; half++)
+        if ((rc = launch_layer<256, false, 4, 4>(ctx, act3, s->w[3], s->b[3], feat, c, g4, half * 256, 512, st))) return rc;
+    LayerGeom g5 = { MODE_NHWC, 1, 1, 1, 1, 512, 512, 1, 512, A1, 0, 1, 1.0f, 65536, 0, dbg };
+    return launch_layer<32, true, 4, 4>(ctx, feat, s->w[4], s->b[4], heads, c, g5, 0, 32, st);
+}
+
+// timing experiments inside K4 (tools/cnn_probe.py) exist only in builds made with -DSTM_CNN_PROBES; the product
+// library never reads the environment on this path
+static int cnn_debug_bits()
+{
+#ifdef STM_CNN_PROBES
+    const char *e = getenv("STM_CNN_DEBUG");
+    return e ? atoi(e) : 0;
+#else
+    return 0;
+#endif
 }
 
 int stm_cnn_forward(stm_ctx *ctx, const uint8_t *obs, long long n, float *heads, void *stream)
@@ -1046,40 +1422,54 @@ int stm_cnn_forward(stm_ctx *ctx, const uint8_t *obs, long long n, float *heads,
             return stm_internal_fail(ctx, STM_ERR_NOMEM, "stm_cnn_forward: activation scratch");
         s->cap_images = chunk;
     }
-    const int A1 = s->A + 1;
-    const char *dbg_env = getenv("STM_CNN_DEBUG");
-    const int dbg = dbg_env ? atoi(dbg_env) : 0;
+    const int A1 = s->A + 1, dbg = cnn_debug_bits();
     for (long long i0 = 0; i0 < n; i0 += chunk) {
         long long c = n - i0 < chunk ? n - i0 : chunk;
-        int rc;
-        LayerGeom g1 = { MODE_CONV1, 400, 20, 84, 84, 4, 0, 4, 256, 32, 1, 0, 1.0f / 255.0f, (65536 + 20 - 1) / 20, 1, dbg };
-        if (!(dbg & 512)) {
-            if (!(dbg & 256)) rc = launch_conv1_window(ctx, obs + (size_t)i0 * 4 * 84 * 84, s->w_c1, s->b[0], s->act1, c, dbg, st);
-            else rc = launch_layer<32, true, 4, 8>(ctx, obs + (size_t)i0 * 4 * 84 * 84, s->w[0], s->b[0], s->act1, c * 400, g1, 0, 32, st);
-            if (rc) return rc;
-        }
-        if (dbg & 8) continue;                                       // timing experiments: conv1 alone
-        if (!(dbg & 256)) {
-            // conv2: rows of two pixels on the 10 x 20 virtual grid; tap (ky, kx in {0, 2}) = input row + 10 ky + kx / 2
-            WinGeom w2 = { 200, 20, 9, 9, (65536 + 20 - 1) / 20, 8, { 0, 1, 10, 11, 20, 21, 30, 31, 0 }, 1, dbg };
-            if ((rc = launch_window<2>(ctx, s->act1, s->w[1], s->b[1], s->act2, c, w2, st))) return rc;
-            // conv3: rows of one pixel on the 9 x 9 input grid; tap (ky, kx) = input row + 9 ky + kx
-            WinGeom w3 = { 81, 9, 7, 7, (65536 + 9 - 1) / 9, 9, { 0, 1, 2, 9, 10, 11, 18, 19, 20 }, 1, dbg };
-            if ((rc = launch_window<3>(ctx, s->act2, s->w[2], s->b[2], s->act3, c, w3, st))) return rc;
-        } else {                                                      // the gather kernels (kept for A/B timing)
-            LayerGeom g2 = { MODE_NHWC, 81, 9, 20, 20, 32, 4 * 32, 2, 512, 64, 1, 0, 1.0f, (65536 + 9 - 1) / 9, 0, dbg };
-            if ((rc = launch_layer<64, true, 8, 4>(ctx, s->act1, s->w[1], s->b[1], s->act2, c * 81, g2, 0, 64, st))) return rc;
-            LayerGeom g3 = { MODE_NHWC, 49, 7, 9, 9, 64, 3 * 64, 1, 576, 64, 1, 0, 1.0f, (65536 + 7 - 1) / 7, 0, dbg };
-            if ((rc = launch_layer<64, true, 8, 4>(ctx, s->act2, s->w[2], s->b[2], s->act3, c * 49, g3, 0, 64, st))) return rc;
-        }
-        if (dbg & 512) continue;                                     // timing experiments: conv2 + conv3 alone (with bit 9: no conv1 either)
-        LayerGeom g4 = { MODE_NHWC, 1, 1, 1, 1, 3136, 3136, 1, 3136, 512, 1, 0, 1.0f, 65536, 0, dbg };
-        for (int half = 0; half < 2; half++)
-            if ((rc = launch_layer<256, false, 4, 4>(ctx, s->act3, s->w[3], s->b[3], s->feat, c, g4, half * 256, 512, st))) return rc;
-        LayerGeom g5 = { MODE_NHWC, 1, 1, 1, 1, 512, 512, 1, 512, A1, 0, 1, 1.0f, 65536, 0, dbg };
-        if ((rc = launch_layer<32, true, 4, 4>(ctx, s->feat, s->w[4], s->b[4], heads + (size_t)i0 * A1, c, g5, 0, 32, st))) return rc;
+        int rc = forward_chunk(ctx, s, obs + (size_t)i0 * 4 * 84 * 84, c, s->act1, s->act2, s->act3, s->feat, heads + (size_t)i0 * A1, dbg, st);
+        if (rc) return rc;
     }
     return STM_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// Update path: the forward pass that KEEPS its activations, and the backward pass (policies/actor_critic_ts.py:139
+// runs extract_features on the cached leaves with autograd; SB3 1.4.0 PPO.train backpropagates through it).
+// ---------------------------------------------------------------------------------------------------------
+int stm_cnn_forward_train(stm_ctx *ctx, const uint8_t *obs, long long n, float *heads, void *stream)
+{
+    if (!ctx || !obs || !heads || n < 1) return stm_internal_fail(ctx, STM_ERR_ARG, "stm_cnn_forward_train: bad argument");
+    if (n > kMaxTrainImages) return stm_internal_fail(ctx, STM_ERR_ARG, "stm_cnn_forward_train: more than 32 768 images in one minibatch");
+    CnnState *s = reinterpret_cast<CnnState *>(*stm_internal_cnn_slot(ctx));
+    if (!s || !s->w[0]) return stm_internal_fail(ctx, STM_ERR_ARG, "stm_cnn_forward_train: call stm_cnn_set_weights first");
+    if (cudaSetDevice(stm_internal_device(ctx)) != cudaSuccess) return stm_internal_fail(ctx, STM_ERR_CUDA, "cudaSetDevice");
+    cudaStream_t st = (cudaStream_t)stream;
+    if (n > s->t_cap) {
+        cudaFree(s->t_act1); cudaFree(s->t_act2); cudaFree(s->t_act3); cudaFree(s->t_feat);
+        s->t_act1 = s->t_act2 = s->t_act3 = s->t_feat = nullptr; s->t_cap = 0;
+        const long long cap = (n + 63) / 64 * 64;
+        if (cudaMalloc(&s->t_act1, (size_t)cap * 400 * 32 * 2) != cudaSuccess || cudaMalloc(&s->t_act2, (size_t)cap * 81 * 64 * 2) != cudaSuccess ||
+            cudaMalloc(&s->t_act3, (size_t)cap * 49 * 64 * 2) != cudaSuccess || cudaMalloc(&s->t_feat, (size_t)cap * 512 * 2) != cudaSuccess)
+            return stm_internal_fail(ctx, STM_ERR_NOMEM, "stm_cnn_forward_train: activation buffers");
+        s->t_cap = cap;
+    }
+    s->t_n = n;
+    return forward_chunk(ctx, s, obs, n, s->t_act1, s->t_act2, s->t_act3, s->t_feat, heads, 0, st);
+}
+
+int stm_cnn_backward(stm_ctx *ctx, const uint8_t *obs, long long n, const float *dheads, float *g_conv1_w, float *g_conv1_b,
+                     float *g_conv2_w, float *g_conv2_b, float *g_conv3_w, float *g_conv3_b, float *g_fc_w, float *g_fc_b,
+                     float *g_action_w, float *g_action_b, float *g_value_w, float *g_value_b, void *stream)
+{
+    if (!ctx || !obs || !dheads || !g_conv1_w || !g_conv1_b || !g_conv2_w || !g_conv2_b || !g_conv3_w || !g_conv3_b || !g_fc_w ||
+        !g_fc_b || !g_action_w || !g_action_b || !g_value_w || !g_value_b)
+        return stm_internal_fail(ctx, STM_ERR_ARG, "stm_cnn_backward: bad argument");
+    CnnState *s = reinterpret_cast<CnnState *>(*stm_internal_cnn_slot(ctx));
+    if (!s || !s->wT[0] || s->t_n != n || n < 1)
+        return stm_internal_fail(ctx, STM_ERR_ARG, "stm_cnn_backward: must follow stm_cnn_forward_train of the same n images");
+    if (cudaSetDevice(stm_internal_device(ctx)) != cudaSuccess) return stm_internal_fail(ctx, STM_ERR_CUDA, "cudaSetDevice");
+    float *grads[12] = { g_conv1_w, g_conv1_b, g_conv2_w, g_conv2_b, g_conv3_w, g_conv3_b, g_fc_w, g_fc_b, g_action_w, g_action_b,
+                         g_value_w, g_value_b };
+    return backward_impl(ctx, s, obs, n, dheads, grads, (cudaStream_t)stream);
 }
 
 } // extern "C"

@@ -189,6 +189,20 @@ class Engine:
         check(lib().stm_cnn_forward(self._h, _ptr(obs_u8), n, _ptr(heads), self._stream()), self._h)
         return heads[:, :A], heads[:, A]
 
+    def cnn_forward_train(self, obs_u8):
+        """stm_cnn_forward_train: heads (n, A+1) fp32; the activations stay in the ctx for cnn_backward."""
+        n = obs_u8.shape[0]
+        heads = torch.empty((n, self._cnn_actions + 1), dtype=torch.float32, device=self.device)
+        check(lib().stm_cnn_forward_train(self._h, _ptr(obs_u8), n, _ptr(heads), self._stream()), self._h)
+        return heads
+
+    def cnn_backward(self, obs_u8, dheads, like):
+        """stm_cnn_backward: dL/dheads (n, A+1) -> list of 12 gradient tensors shaped like `like` (PARAM_KEYS order)."""
+        grads = [torch.empty_like(p, dtype=torch.float32, device=self.device).contiguous() for p in like]
+        check(lib().stm_cnn_backward(self._h, _ptr(obs_u8), obs_u8.shape[0], _ptr(dheads.contiguous().float()),
+                                     *[_ptr(g) for g in grads], self._stream()), self._h)
+        return grads
+
     def timing(self, on=True):
         check(lib().stm_timing_enable(self._h, int(on)), self._h)
 

@@ -1,4 +1,4 @@
-"""Autograd-aware Python faces of K5 (logits).  The arithmetic is in libstm_b200.so."""
+"""Autograd-aware Python faces of K4 (NatureCNN + heads, update path) and K5 (logits).  The arithmetic is in libstm_b200.so."""
 import ctypes as C
 
 import torch
@@ -69,3 +69,45 @@ def softtreemax_logits_full(eng, head, rewards, val_coef, beta, alpha, eps, cumu
                                float(alpha), float(eps), int(cumulative), _p(logits), _p(raw), _p(vmax),
                                eng._stream()), eng._h)
     return logits, raw, vmax
+
+
+TRAIN_CHUNK = 32768          # images per stm_cnn_forward_train / stm_cnn_backward pair
+
+
+class _CnnHeads(torch.autograd.Function):
+    """heads (n, A+1) = NatureCNN + action_net / value_net on u8 observation stacks, differentiable in the twelve
+    parameters: forward = stm_cnn_forward_train (activations kept in the ctx), backward = stm_cnn_backward.  A batch larger
+    than TRAIN_CHUNK images is evaluated in chunks and its backward re-runs the forward of each chunk (the ctx keeps the
+    activations of one chunk); so does a backward that finds the ctx's activations replaced by a later forward_train."""
+
+    @staticmethod
+    def forward(ctx, eng, obs_u8, *params):
+        ctx.eng, ctx.obs, ctx.params = eng, obs_u8, params
+        n = obs_u8.shape[0]
+        if n <= TRAIN_CHUNK:
+            eng._train_token = ctx.token = object()
+            return eng.cnn_forward_train(obs_u8)
+        ctx.token = None
+        head, val = eng.cnn_forward(obs_u8)
+        return torch.cat([head, val[:, None]], dim=1)
+
+    @staticmethod
+    def backward(ctx, dheads):
+        eng, obs = ctx.eng, ctx.obs
+        dheads = dheads.contiguous().float()
+        total = None
+        for i0 in range(0, obs.shape[0], TRAIN_CHUNK):
+            o, d = obs[i0:i0 + TRAIN_CHUNK], dheads[i0:i0 + TRAIN_CHUNK]
+            if ctx.token is None or getattr(eng, "_train_token", None) is not ctx.token:
+                eng.cnn_forward_train(o)                                  # recompute this chunk's activations
+                eng._train_token = None
+            g = eng.cnn_backward(o, d, ctx.params)
+            total = g if total is None else [a + b for a, b in zip(total, g)]
+        return (None, None) + tuple(g.to(p.dtype) for g, p in zip(total, ctx.params))
+
+
+def cnn_heads(eng, obs_u8, params):
+    """obs (n, 4, 84, 84) uint8 on the device, params: the twelve tensors of Engine.PARAM_KEYS (in that order; the Engine must
+    hold their current values: Engine.cnn_set_weights) -> heads (n, A+1): columns 0..A-1 action_net, column A value_net.
+    Replaces extract_features -> action_net / value_net under autograd (actor_critic_ts.py:139-149)."""
+    return _CnnHeads.apply(eng, obs_u8.contiguous(), *params)

@@ -104,6 +104,12 @@ class ActorCriticCnnPolicyDepth0(nn.Module):
         model.load_state_dict(saved["state_dict"])
         return model
 
+    def kernel_param_list(self):
+        """The twelve parameters themselves (not detached), in Engine.PARAM_KEYS order: what ops.cnn_heads differentiates."""
+        fe = self.features_extractor
+        mods = (fe.cnn[0], fe.cnn[2], fe.cnn[4], fe.linear[0], self.action_net, self.value_net)
+        return [t for m in mods for t in (m.weight, m.bias)]
+
     def kernel_params(self):
         sd = self.state_dict()
         m = {"cnn.0": "features_extractor.cnn.0", "cnn.2": "features_extractor.cnn.2", "cnn.4": "features_extractor.cnn.4",
@@ -132,6 +138,7 @@ class SoftTreeMaxPolicy(ActorCriticCnnPolicyDepth0):
         if learn_alpha or learn_beta:                                                                # :34-39
             self.optimizer = self.optimizer_class(self.parameters(), lr=lr_schedule(1), **self.optimizer_kwargs)
         self.use_leaves_v = use_leaves_v
+        self.update_backend = kwargs.get("update_backend", "kernel")          # "kernel" (K4 forward_train + backward) | "torch"
 
     # ------------------------------------------------------------------------------------------
     def _sync_kernel_weights(self):
@@ -219,19 +226,29 @@ class SoftTreeMaxPolicy(ActorCriticCnnPolicyDepth0):
             groups.append(fa)
         L = leaves[0].shape[0]
         val_coef = self.cule_bfs.gamma ** self.cule_bfs.max_depth
-        feats = self.extract_features(th.cat([obs.to(th.uint8)] + leaves))                           # :122,139
-        values = self.value_net(feats[:B])                                                           # :145-147
-        head = self.action_net(feats[B:]).reshape(B, L, A)
+        all_obs = th.cat([obs.round().clamp(0, 255).to(th.uint8) if obs.dtype != th.uint8 else obs] + leaves)   # :122,139
         rew = th.stack(rewards)
-        depth0 = self.action_net(feats[:B]) if self.learn_alpha else None
+        if self.update_backend == "kernel":
+            # K4 on the update path too: forward that keeps its activations + tcgen05 data / weight gradients (stm_cnn_backward)
+            self._sync_kernel_weights()
+            heads = ops.cnn_heads(self.eng, all_obs, self.kernel_param_list())                       # (B + B L, A + 1)
+            values = heads[:B, A:A + 1]                                                              # :145-147
+            head = heads[B:, :A].reshape(B, L, A)
+            depth0 = heads[:B, :A] if self.learn_alpha else None
+            leaf_values = heads[B:, A].reshape(B, L)
+        else:                                                                                        # torch autograd (cuDNN), kept for A/B tests
+            feats = self.extract_features(all_obs)
+            values = self.value_net(feats[:B])
+            head = self.action_net(feats[B:]).reshape(B, L, A)
+            depth0 = self.action_net(feats[:B]) if self.learn_alpha else None
+            leaf_values = self.value_net(feats[B:]).reshape(B, L) if self.use_leaves_v else None
         group = th.stack([g.reshape(-1) for g in groups]) if groups[0] is not None else None          # :163-171
         logits = ops.softtreemax_logits(self.eng, head, rew, val_coef, self.beta, self.alpha, self.regularization,
                                         self.is_cumulative_mode, depth0, group)                       # K5 fwd + bwd
         dist = self._distribution(logits)
         log_prob = dist.log_prob(actions.to(self.device).reshape(-1))
         if self.use_leaves_v:
-            lv = self.value_net(feats[B:]).reshape(B, L)
-            values = (val_coef * lv + rew).max(dim=1, keepdim=True).values
+            values = (val_coef * leaf_values + rew).max(dim=1, keepdim=True).values
         return values, log_prob, dist.entropy()
 
     def predict(self, obs, state=None, mask=None, deterministic=False):                              # :272-273
