@@ -335,12 +335,18 @@ def main():
     if world > 1:
         # NCCL's own log (communicator size, NVLS / ring choice) is wanted, but it goes to file descriptor 1: keep a private
         # copy of stdout for the one JSON line and point descriptor 1 at stderr for everything else.
-        os.environ.setdefault("NCCL_DEBUG", "INFO")
+        # (NCCL_DEBUG is left as the launcher set it)
         sys.stdout.flush()
         global _JSON_OUT
         _JSON_OUT = os.fdopen(os.dup(1), "w")
         os.dup2(2, 1)
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+        chk = torch.tensor([float(rank), 1.0], device=torch.device("cuda", local))
+        dist.all_reduce(chk)                                     # every rank took part: sum of ranks and count of ranks
+        nccl_check = {"backend": "nccl", "ranks_counted": int(chk[1].item()), "sum_of_ranks_ok": int(chk[0].item()) == world * (world - 1) // 2,
+                      "nccl_version": ".".join(str(v) for v in torch.cuda.nccl.version())}
+    if world == 1:
+        nccl_check = {"backend": "none (one rank)", "ranks_counted": 1, "sum_of_ranks_ok": True}
     if args.mode != "bfs":
         res = (run_leafshard(args, None, rank, world, local, steps=args.steps) if args.mode == "leafshard"
                else run_train(args, rank, world, local, steps=args.steps))
@@ -688,7 +694,7 @@ def main():
                     "value": world * L / (ms_interp / 1e3), "unit": UNIT, "ms_per_step": ms_interp,
                     "what": "the same step with STM_XLATE=0: what a cartridge image without a bundled translation gets"},
                 "translated_core": int(eng.translated_core),
-                "per_rank": per_rank, "collectives": collectives,
+                "per_rank": per_rank, "collectives": collectives, "comm": nccl_check,
                 "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "kernels": kernels, "policy": policy,
                 "cpu_baseline": {"value": cpu_rate, "unit": UNIT, "cores": os.cpu_count() or 1, "kind": "port",
                                  "sample": f"{cpu_leaves} leaves in {cpu_dt:.1f}s: 64 roots x depth {depth} repeated, oracle port (OpenMP)"}}

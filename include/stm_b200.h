@@ -41,6 +41,13 @@ size_t stm_state_bytes(const stm_ctx *ctx);
 /* size of the minimal action set: torchcule Rom.minimal_actions(), cule_bfs.py:29-31 */
 int stm_num_actions(const stm_ctx *ctx);
 
+/* Colour-index -> grey table of the observation path (`generate_frames` in grey mode, cule_bfs.py:162-167): 128 bytes, entry
+ * i = the 8-bit grey of NTSC colour index i = COLUxx >> 1.  `grey128` is a HOST pointer.  It is DATA of the ctx, not of the
+ * build: the default (include/stm_palette.h) is computed from a YIQ formula because ALE's NTSC table — what CuLE's grey path
+ * uses — is not available offline; a user who has that table installs it here and nothing is recompiled.  Synchronises the
+ * device.  (The 160x210 -> 84x84 resize rule is still fixed at build time: DESIGN.md §2 lists what is unpinned.) */
+int stm_set_palette(stm_ctx *ctx, const uint8_t *grey128);
+
 /* Power-on state written to `states[0..n)`: replaces `super(AtariEnv, env).reset(0)`,
  * cule_bfs.py:57.  rewards/done/lives may be NULL. */
 int stm_reset_states(stm_ctx *ctx, uint8_t *states, float *rewards, uint8_t *done, int32_t *lives,
@@ -135,12 +142,6 @@ int stm_bfs_host(stm_ctx *ctx, const uint8_t *root_states, const uint8_t *root_s
                  uint8_t *leaf_stacks, int leaf_stacks_on_device, float *leaf_rewards,
                  uint8_t *leaf_done, int32_t *leaf_lives, void *stream);
 
-/* Per-kernel device timing for bench.py's roofline: when enabled, a CUDA event pair is recorded on
- * the launch stream around every K1/K2/K3 launch.  stm_timing_read waits for them and returns the
- * summed milliseconds and launch counts by kind {0: clone, 1: step, 2: frames}, then clears. */
-int stm_timing_enable(stm_ctx *ctx, int on);
-int stm_timing_read(stm_ctx *ctx, float *ms_by_kind, int *launches_by_kind);
-
 /* K5 — SoftTreeMax logits for R roots of a full-width tree (L = A^d leaves each), fused:
  * m = val_coef*head + reward; per root action (L/A consecutive leaves x A head outputs) logsumexp(beta*m)
  * - log(count) [cumulative == 0] or beta*mean(m) [cumulative != 0]; NaN -> 0; alpha-mix with the depth-0
@@ -211,18 +212,6 @@ int stm_step_frames_noalloc(stm_ctx *ctx, uint8_t *states, const uint8_t *action
                             int frameskip, int episodic_life, float weight, float *rewards,
                             uint8_t *done, int32_t *lives, const uint8_t *parent_stacks,
                             uint8_t *child_stacks, int fanout, void *stream);
-
-/* number of kernels this ctx has launched since creation (bench.py's gpu_launches) */
-long long stm_launch_count(const stm_ctx *ctx);
-/* (measurement only, no reference counterpart) 1-based index of the ahead-of-time translated step kernel that
- * also serves this ctx's cartridge image (launches of up to one warp per scheduler use it, larger ones the
- * interpreter); 0 = interpreter only (an image the library has no translation for, or STM_XLATE=0). */
-int stm_translated_core(const stm_ctx *ctx);
-/* (probe, no reference counterpart, not on any product path) runs one 128 x 64 x 64 bf16 tcgen05 MMA whose A operand
- * starts `shift` rows into a 128B-swizzled [rows][64] shared-memory tile, with `base_off` in the descriptor's
- * base-offset field; out = A[shift .. shift + 128) x B^T as f32.  tools/shift_probe.py uses it to show that a
- * 128-byte-aligned operand start is read correctly — the fact the window GEMMs of K4 rest on. */
-int stm_debug_shift_probe(stm_ctx *ctx, const void *A, const void *B, float *out, int rows, int shift, int base_off, void *stream);
 
 #ifdef __cplusplus
 }

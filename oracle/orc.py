@@ -59,6 +59,7 @@ def lib():
                               C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                               C.c_void_p, C.c_int]
         L.orc_bfs.restype = C.c_int
+        L.orc_set_palette.argtypes = [C.c_void_p]
         _LIB = L
     return _LIB
 
@@ -155,6 +156,17 @@ class Game:
         if rc != 0:
             raise MemoryError("orc_bfs")
         return stack, rew, done, lives, st
+
+
+def set_palette(grey128):
+    """Install a colour-index -> grey table in the oracle (process-wide); None restores the bundled default."""
+    if grey128 is None:
+        import re
+        txt = open(os.path.join(_ROOT, "include", "stm_palette.h")).read()
+        body = txt[txt.index("STM_GRAY_LUT_INIT {") + len("STM_GRAY_LUT_INIT {"):]
+        grey128 = [int(t) for t in re.findall(r"\d+", body[:body.index("}")])]
+    g = np.ascontiguousarray(np.asarray(grey128, np.uint8).reshape(128))
+    lib().orc_set_palette(_p(g))
 
 
 def render_obs(fb):

@@ -46,7 +46,9 @@ typedef struct orc_game {
     uint16_t rom_mask;   /* address mask inside one 4K (or 2K) window */
 } orc_game;
 
-static const uint8_t GRAY[128] = STM_GRAY_LUT_INIT;
+static uint8_t GRAY[128] = STM_GRAY_LUT_INIT;
+/* the grey table is data (stm_set_palette on the CUDA side): tests install the same table on both sides */
+void orc_set_palette(const uint8_t *grey128) { memcpy(GRAY, grey128, 128); }
 
 /* status flags */
 enum { FC = 1, FZ = 2, FI = 4, FD = 8, FB = 16, FU = 32, FV = 64, FN = 128 };

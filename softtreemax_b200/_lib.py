@@ -36,6 +36,7 @@ _SIGS = {
     "stm_last_error": (C.c_char_p, [C.c_void_p]),
     "stm_state_bytes": (C.c_size_t, [C.c_void_p]),
     "stm_num_actions": (C.c_int, [C.c_void_p]),
+    "stm_set_palette": (C.c_int, [C.c_void_p, C.c_void_p]),
     "stm_reset_states": (C.c_int, [C.c_void_p] * 5 + [C.c_int, C.c_void_p]),
     "stm_expand": (C.c_int, [C.c_void_p] * 9 + [C.c_int, C.c_int, C.c_void_p]),
     "stm_step": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_float,

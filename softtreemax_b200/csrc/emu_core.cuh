@@ -32,7 +32,15 @@
 #define STM_NOINLINE static __device__ __noinline__
 #define STM_WARP_ALL(mask, pred) __all_sync((mask), (pred))
 #define STM_WARP_MIN(mask, v) __reduce_min_sync((mask), (v))
+// scanline lock-step scope: the warp (default) or, with -DSTM_CTA_LOCKSTEP, the whole thread block, so that the warps
+// that share an SM's instruction caches walk the same code region together
+#ifdef STM_CTA_LOCKSTEP
+#define STM_LINE_ALL(mask, pred) (__syncthreads_and(pred) != 0)
 #else
+#define STM_LINE_ALL(mask, pred) __all_sync((mask), (pred))
+#endif
+#else
+#define STM_LINE_ALL(mask, pred) (pred)
 #define STM_DEV inline
 #define STM_FN  static inline
 #define STM_NOINLINE static
@@ -1216,7 +1224,7 @@ struct Emu {
                 if (ended) finish_line();
                 over = (flags & STM_F_FRAME_DONE) != 0;
             }
-        } while (!STM_WARP_ALL(lanes, over));
+        } while (!STM_LINE_ALL(lanes, over));
         if (want_pixels) {
             int r0 = (int)end_line_no - STM_YSTART; if (r0 < 0) r0 = 0;
             for (int r = r0; r < STM_VIS_H; r++)

@@ -33,6 +33,7 @@
 #include <new>
 #include <cstdlib>
 #include "../../include/stm_b200.h"
+#include "../../include/stm_b200_debug.h"
 
 extern "C" int stm_internal_fail(stm_ctx *ctx, int code, const char *msg);
 extern "C" void stm_internal_count_launch(stm_ctx *ctx);

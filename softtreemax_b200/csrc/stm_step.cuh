@@ -13,6 +13,7 @@
 struct StmStepArgs {
     uint8_t *states; const uint8_t *actions; float *rewards; uint8_t *done; int32_t *lives;
     const uint32_t *rom; const uint32_t *lut; const uint2 *pre; uint32_t *scratch; uint8_t *stepped;
+    const uint32_t *grey;                 // the ctx's colour-index -> grey table, 128 bytes as 32 words (stm_set_palette)
     int n, frameskip, episodic_life, render; uint32_t rom_words; float weight;
     stm::GameParams gp;
     // frame-by-frame driving (stm_step_frame, the torchcule-style surface): `frozen` decides which envs sit the frame out
@@ -49,12 +50,12 @@ constexpr int kStepThreads = 128;
 // lane t always hits bank t%32: conflict-free for every access pattern, RAM bytes included), the
 // cartridge image (4 or 8 KB) and the decode table.
 // ---------------------------------------------------------------------------------------------
-__constant__ uint8_t c_gray[128] = STM_GRAY_LUT_INIT;
 
 struct DevMem {
     uint8_t *blob;             // &sblob[tid] as bytes
     const uint32_t *rom;       // shared
     const uint32_t *lut;       // shared
+    const uint8_t *sgrey;      // shared: colour index -> grey (data of the ctx, not of the build)
     const uint2 *pre;          // global, read-only path (L1-resident: 32 KB for a 4 KB cartridge)
     uint32_t *scr;             // native scratch of this env's tile, + lane
     uint32_t fsel;             // which of the two native frames is being drawn
@@ -70,7 +71,7 @@ struct DevMem {
     __device__ __forceinline__ void fetch(uint32_t off, uint32_t &w, uint32_t &ops) const
     { uint2 v = __ldg(pre + off); w = v.x; ops = v.y; }
     __device__ __forceinline__ uint32_t opinfo(uint32_t op) const { return lut[op]; }
-    __device__ __forceinline__ uint32_t grey(uint32_t i) const { return c_gray[i & 127]; }
+    __device__ __forceinline__ uint32_t grey(uint32_t i) const { return sgrey[i & 127]; }
     // scr points at this lane's uint4 slot of (frame 0, row 0, quad 0); quads are kTileEnvs uint4 apart
     __device__ __forceinline__ uint32_t *quad(uint32_t row, uint32_t q) const
     { return scr + (size_t)((fsel * STM_VIS_H + row) * 10 + q) * (kTileEnvs * 4); }
@@ -108,6 +109,8 @@ stm_step_kernel(const StepArgs a)
     const int tid = threadIdx.x;
     for (uint32_t i = tid; i < a.rom_words; i += kStepThreads) srom[i] = a.rom[i];
     for (uint32_t i = tid; i < 256; i += kStepThreads) slut[i] = a.lut[i];
+    uint32_t *sgrey = slut + 256;
+    if (tid < 32) sgrey[tid] = a.grey[tid];
     const int env = blockIdx.x * kStepThreads + tid;
     const bool valid = env < a.n;
     if (valid) {
@@ -130,7 +133,7 @@ stm_step_kernel(const StepArgs a)
 
     DevMem m;
     m.blob = reinterpret_cast<uint8_t *>(sblob + tid);
-    m.rom = srom; m.lut = slut; m.pre = a.pre;
+    m.rom = srom; m.lut = slut; m.pre = a.pre; m.sgrey = reinterpret_cast<const uint8_t *>(sgrey);
     m.scr = a.scratch ? a.scratch + (size_t)(env / kTileEnvs) * kTileWords + (env % kTileEnvs) * 4 : nullptr;
     m.fsel = 0;
     Emu<DevMem> e(m, a.gp);

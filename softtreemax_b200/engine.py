@@ -67,6 +67,11 @@ class Engine:
     def set_scratch_envs(self, n):
         check(lib().stm_set_scratch_envs(self._h, int(n)), self._h)
 
+    def set_palette(self, grey128):
+        """Install a colour-index -> grey table (128 uint8 values, e.g. ALE's NTSC palette reduced to luma)."""
+        g = np.ascontiguousarray(np.asarray(grey128, dtype=np.uint8).reshape(128))
+        check(lib().stm_set_palette(self._h, _ptr(g)), self._h)
+
     def alloc(self, n):
         d = self.device
         return (torch.empty((n, STATE_BYTES), dtype=torch.uint8, device=d),

@@ -38,6 +38,11 @@ class CuleEnv:
     def _obs(self):
         return torch.stack(list(self.state_buffer), 0).cpu().numpy()                      # cule_env.py:72,93
 
+    def obs_tensor(self):
+        """The current observation stack (4, 84, 84) u8 ON THE GPU: what reset()/step() just returned as numpy, without the
+        device->host copy.  A rollout that keeps its observations on the device reads this."""
+        return torch.stack(list(self.state_buffer), 0)
+
     def reset(self):                                                                        # cule_env.py:43-54
         obs = self.reset_no_fire()
         if not self.fire_reset:
@@ -65,7 +70,8 @@ class CuleEnv:
         self.lives = int(self.env.lives[0].item())
         return self._obs()
 
-    def step(self, action):                                                                 # cule_env.py:74-93
+    def step(self, action, want_obs=True):                                                  # cule_env.py:74-93
+        """want_obs=False: the caller reads obs_tensor() instead; None is returned in place of the numpy stack."""
         obs, reward, done, info = self.env.step(torch.tensor([action]))
         info = {"ale.lives": info["ale.lives"], "orig_reward": float(reward[0].item())}
         if self.clip_reward:
@@ -79,7 +85,7 @@ class CuleEnv:
             self.life_termination = True
             done = True
         self.lives = lives
-        return self._obs(), reward[0].cpu().numpy(), done, info
+        return (self._obs() if want_obs else None), reward[0].cpu().numpy(), done, info
 
     def train(self):
         self.training = True

@@ -150,6 +150,13 @@ class SoftTreeMaxPolicy(ActorCriticCnnPolicyDepth0):
             self.eng.cnn_set_weights(self.kernel_params())
             self.eng._cnn_owner = ver
 
+    def _host_scalars(self):
+        """beta and alpha as Python floats, re-read from the device only when the optimizer has changed them."""
+        ver = (getattr(self.beta, "_version", 0), getattr(self.alpha, "_version", 0))
+        if getattr(self, "_scalars_ver", None) != ver:
+            self._scalars, self._scalars_ver = (float(self.beta), float(self.alpha)), ver
+        return self._scalars
+
     def hash_obs(self, obs):                                                                         # :196-197
         return (obs[:, -2:, :, :].int()).view(obs.shape[0], -1).sum(dim=1)
 
@@ -191,10 +198,15 @@ class SoftTreeMaxPolicy(ActorCriticCnnPolicyDepth0):
         self._sync_kernel_weights()
         A = self.action_space.n
         root_u8 = obs.round().clamp(0, 255).to(th.uint8).contiguous() if obs.dtype != th.uint8 else obs.contiguous()
-        head_leaf, val_leaf = self.eng.cnn_forward(leaves.contiguous())                              # K4
-        head_root, val_root = self.eng.cnn_forward(root_u8)
+        if leaves.dtype == th.uint8:                                                                 # K4: root + leaves in one pass
+            head_all, val_all = self.eng.cnn_forward(th.cat([root_u8[:1], leaves]))
+            head_root, val_root, head_leaf, val_leaf = head_all[:1], val_all[:1], head_all[1:], val_all[1:]
+        else:                                                                                        # float_obs trees
+            head_leaf, val_leaf = self.eng.cnn_forward(leaves.round().clamp(0, 255).to(th.uint8).contiguous())
+            head_root, val_root = self.eng.cnn_forward(root_u8)
+        beta, alpha = self._host_scalars()
         logits, _, vmax = ops.softtreemax_logits_full(                                               # K5
-            self.eng, head_leaf.reshape(1, -1, A), rewards.reshape(1, -1), val_coef, float(self.beta), float(self.alpha),
+            self.eng, head_leaf.reshape(1, -1, A), rewards.reshape(1, -1), val_coef, beta, alpha,
             self.regularization, self.is_cumulative_mode, depth0=head_root if self.learn_alpha else None,
             values=val_leaf.reshape(1, -1) if self.use_leaves_v else None,
             group=first_action.reshape(1, -1) if first_action is not None else None)                 # :70-79
@@ -209,6 +221,32 @@ class SoftTreeMaxPolicy(ActorCriticCnnPolicyDepth0):
             del self.timestep2obs_dict[old]
         self.time_step += 1
         return actions, value_root, log_prob
+
+    @th.no_grad()
+    def forward_roots(self, obs, root_blobs, deterministic=False):
+        """forward() for R roots at once (the reference evaluates one root per call: main.py:47, n_envs = 1): obs (R, 4, 84, 84)
+        observation stacks, root_blobs (R, 256) emulator states of the same roots.  One stm_bfs over all roots, one K4 pass
+        over the R + R*L images, one K5 launch -> (actions (R,), values (R,), log_prob (R,)).  No leaf cache is kept (a
+        vectorised rollout that wants evaluate_actions later keeps the returned trees itself); full-width trees only."""
+        if self.max_width != -1:
+            raise NotImplementedError("forward_roots: full-width trees (max_width = -1)")
+        obs = th.as_tensor(obs).to(self.device)
+        root_u8 = obs.round().clamp(0, 255).to(th.uint8).contiguous() if obs.dtype != th.uint8 else obs.contiguous()
+        R, A, d = root_u8.shape[0], self.action_space.n, self.cule_bfs.max_depth
+        out = self.cule_bfs.bfs_batch(root_blobs.to(self.device), root_u8, d)
+        val_coef = self.cule_bfs.gamma ** d
+        self._sync_kernel_weights()
+        head_all, val_all = self.eng.cnn_forward(th.cat([root_u8, out["stacks"]]))
+        head_root, val_root, head_leaf, val_leaf = head_all[:R], val_all[:R], head_all[R:], val_all[R:]
+        beta, alpha = self._host_scalars()
+        logits, _, vmax = ops.softtreemax_logits_full(
+            self.eng, head_leaf.reshape(R, -1, A), out["rewards"].reshape(R, -1), val_coef, beta, alpha, self.regularization,
+            self.is_cumulative_mode, depth0=head_root if self.learn_alpha else None,
+            values=val_leaf.reshape(R, -1) if self.use_leaves_v else None)
+        values = vmax if self.use_leaves_v else val_root
+        dist = self._distribution(logits)
+        actions = logits.argmax(dim=1) if deterministic else dist.sample()
+        return actions, values, dist.log_prob(actions), logits
 
     def evaluate_actions(self, obs, actions):                                                        # :106-194
         self.add_gradients_history()

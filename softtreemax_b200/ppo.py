@@ -38,17 +38,28 @@ class PPO:
         self._step_cb = None
 
     def _rollout(self, obs, episode_start):
+        """n_steps of one root env.  When the env can hand its observation over on the GPU (CuleEnv.obs_tensor) the rollout
+        never moves an observation to the host: obs, the rollout buffer's observations and the policy input stay device
+        tensors (the reference copies every observation device -> host -> device, cule_env.py:93 + SB3's obs_as_tensor)."""
         n = self.n_steps
-        buf = dict(obs=np.zeros((n, 4, 84, 84), np.uint8), act=np.zeros(n, np.int64), rew=np.zeros(n, np.float32),
-                   start=np.zeros(n, np.float32), val=np.zeros(n, np.float32), logp=np.zeros(n, np.float32))
+        on_dev = hasattr(self.env, "obs_tensor")
+        dev = self.policy.device
+        buf = dict(obs=(th.zeros((n, 4, 84, 84), dtype=th.uint8, device=dev) if on_dev else np.zeros((n, 4, 84, 84), np.uint8)),
+                   act=np.zeros(n, np.int64), rew=np.zeros(n, np.float32),
+                   start=np.zeros(n, np.float32), val=th.zeros(n, device=dev), logp=th.zeros(n, device=dev))
         ep_rewards = []
+        cur = self.env.obs_tensor() if on_dev else obs
         for t in range(n):
             with th.no_grad():
-                a, v, lp = self.policy.forward(th.from_numpy(obs).float()[None])
-            a = int(a)
-            buf["obs"][t], buf["act"][t], buf["start"][t] = obs, a, float(episode_start)
-            buf["val"][t], buf["logp"][t] = float(v.reshape(-1)[0]), float(lp.reshape(-1)[0])
-            obs, r, done, info = self.env.step(a)
+                a, v, lp = self.policy.forward(cur[None] if on_dev else th.from_numpy(cur).float()[None])
+            buf["obs"][t] = cur
+            buf["val"][t], buf["logp"][t] = v.reshape(-1)[0], lp.reshape(-1)[0]          # device-side: no sync
+            a = int(a)                                                                   # the one sync of the step: the env needs the action
+            buf["act"][t], buf["start"][t] = a, float(episode_start)
+            if on_dev:
+                _, r, done, info = self.env.step(a, want_obs=False)
+            else:
+                cur, r, done, info = self.env.step(a)
             if self._step_cb is not None:
                 self._step_cb(self, [info], [done])
             buf["rew"][t] = float(r)
@@ -58,15 +69,20 @@ class PPO:
             if done:
                 ep_rewards.append(self._ep_ret)
                 self._ep_ret = 0.0
-                obs = self.env.reset()
+                cur = self.env.reset()
+            if on_dev:
+                cur = self.env.obs_tensor()
+        obs = cur
         with th.no_grad():
+            o1 = obs[None] if on_dev else th.from_numpy(obs)[None]
             if getattr(self.policy, "use_leaves_v", False):
                 # the stored val[t] are tree values (max over leaves): bootstrap with the same definition.  The tree of
                 # this observation stays in the leaf cache and serves the first step of the next rollout.
-                last_val = float(self.policy.forward(th.from_numpy(obs).float()[None])[1].reshape(-1)[0])
+                last_val = float(self.policy.forward(o1.float())[1].reshape(-1)[0])
             else:                                            # SB3: predict_values = the depth-0 value of the last obs
-                feats = self.policy.extract_features(th.from_numpy(obs)[None].to(self.policy.device))
+                feats = self.policy.extract_features(o1.to(dev))
                 last_val = float(self.policy.value_net(feats).reshape(-1)[0])
+        buf["val"], buf["logp"] = buf["val"].cpu().numpy(), buf["logp"].cpu().numpy()
         adv = np.zeros(n, np.float32)
         gae = 0.0
         for t in reversed(range(n)):                         # GAE(lambda), SB3 RolloutBuffer.compute_returns_and_advantage
@@ -76,6 +92,8 @@ class PPO:
             gae = delta + self.gamma * self.gae_lambda * nonterminal * gae
             adv[t] = gae
         buf["adv"], buf["ret"] = adv, adv + buf["val"]
+        if on_dev:
+            obs = obs.cpu().numpy()                          # the caller (learn) carries the last observation as numpy
         return buf, obs, episode_start, ep_rewards
 
     def _rollout_vec(self, obs, episode_start):
@@ -127,7 +145,7 @@ class PPO:
             perm = self.rng.permutation(total)
             for s in range(0, total, self.batch_size):
                 idx = perm[s:s + self.batch_size]
-                obs = th.from_numpy(buf["obs"][idx]).float()
+                obs = buf["obs"][th.from_numpy(idx).to(buf["obs"].device)] if isinstance(buf["obs"], th.Tensor) else th.from_numpy(buf["obs"][idx]).float()
                 act = th.from_numpy(buf["act"][idx]).to(dev)
                 adv = th.from_numpy(buf["adv"][idx]).to(dev)
                 adv = (adv - adv.mean()) / (adv.std() + 1e-8)

@@ -310,3 +310,27 @@ def test_leaf_blocks_of_one_tree_equal_the_whole_tree(orc, engines, name, depth,
                     assert torch.equal(got, want[key]), (name, r, clip, world, key)
                 fa = torch.cat([p["first_action"] for p in parts])
                 assert torch.equal(fa.cpu(), torch.arange(A ** depth) // (A ** (depth - 1)))
+
+
+def test_palette_is_data_of_the_ctx():
+    """stm_set_palette: a different colour-index -> grey table changes the observations exactly as the same table does in
+    the oracle, without a rebuild (the default table is a formula: a real NTSC table can be dropped in)."""
+    import torch
+    from oracle import orc
+    from softtreemax_b200.engine import Engine
+    g = orc.Game("synth_pacman")
+    roots, stacks = orc.make_roots(g, 4, seed=9, base_steps=40, spread=8)
+    table = np.random.default_rng(2).integers(0, 256, 128).astype(np.uint8)
+    table[0] = 0                                           # colour index 0 stays black: undrawn rows are zero-filled
+    eng = Engine("synth_pacman")
+    try:
+        base = eng.bfs(torch.from_numpy(roots).to(eng.device), torch.from_numpy(stacks).to(eng.device), 2)["stacks"].clone()
+        eng.set_palette(table)
+        orc.set_palette(table)
+        out = eng.bfs(torch.from_numpy(roots).to(eng.device), torch.from_numpy(stacks).to(eng.device), 2)
+        o_stack, *_ = g.bfs(roots, stacks, 2)
+        assert np.array_equal(out["stacks"].cpu().numpy(), o_stack.reshape(-1, 4, 84, 84))
+        assert not torch.equal(out["stacks"], base)
+    finally:
+        orc.set_palette(None)
+        eng.close()

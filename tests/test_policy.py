@@ -272,3 +272,32 @@ def test_depth0_ppo_on_cule_env_multiple(tmp_path):
     single = CuleEnv(device="cuda:0", env_kwargs=ENV_KWARGS, clip_reward=True, fire_reset=True)
     mean, std = evaluate_policy(pol, single, n_eval_episodes=2)
     assert np.isfinite(mean) and np.isfinite(std)
+
+
+def test_forward_roots_equals_single_root_forwards():
+    """forward_roots (R roots through one bfs, one K4 pass, one K5 launch) against R calls of forward(): same logits
+    (compared through log_prob of the same action) and values.  K4 tiles images in groups of 128 rows, so a root evaluated
+    in a batch of 6 and alone goes through identical arithmetic: the tolerance is exact equality of the logits."""
+    import numpy as np
+    import torch as th
+    from oracle import orc
+    from softtreemax_b200.envs import CuleEnv
+    from softtreemax_b200.policy import ActorCriticCnnTSPolicy
+    kw = dict(env_name="PongNoFrameskip-v4", color_mode="gray", repeat_prob=0.0, rescale=True, episodic_life=True, frameskip=4)
+    np.random.seed(1)
+    th.manual_seed(1)
+    env = CuleEnv(device="cuda:0", env_kwargs=kw, clip_reward=True, fire_reset=True)
+    pol = ActorCriticCnnTSPolicy(env.observation_space, env.action_space, lambda _: 1e-4, tree_depth=2, gamma=0.99, step_env=env,
+                                 buffer_size=128, learn_alpha=True, learn_beta=True, max_width=-1, use_leaves_v=False,
+                                 is_cumulative_mode=False, regularization=0.001)
+    g = orc.Game("synth_pong")
+    roots, stacks = orc.make_roots(g, 6, seed=3, base_steps=50, spread=30)
+    blobs, obs = th.from_numpy(roots).cuda(), th.from_numpy(stacks).cuda()
+    _, values, _, logits = pol.forward_roots(obs, blobs, deterministic=True)
+    for r in range(6):
+        env.env.blobs[:1] = blobs[r:r + 1]                      # the root emulator state CuleBFS.bfs injects (cule_bfs.py:110-112)
+        a, v, lp = pol.forward(obs[r:r + 1].float(), deterministic=True)
+        ref = th.log_softmax(logits[r], 0)
+        assert int(a) == int(logits[r].argmax())
+        assert abs(float(lp) - float(ref[int(a)])) <= 1e-6
+        assert abs(float(v.reshape(-1)[0]) - float(values[r])) <= 1e-6
