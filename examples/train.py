@@ -66,7 +66,13 @@ def main():
                              is_cumulative_mode=bool(args.is_cumulative_mode), regularization=args.regularization)
         model = PPO(ActorCriticCnnTSPolicy, env, policy_kwargs=policy_kwargs, verbose=1, seed=args.seed, **ppo_params)
     if args.run_type == "train":
+        import time
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
         model.learn(args.total_timesteps, callback=TrainingCallback(path=args.log_jsonl))      # callbacks.py:11-57
+        torch.cuda.synchronize()
+        dt = time.perf_counter() - t0
+        print(f"learn: {model.num_timesteps} env steps (rollouts + PPO updates) in {dt:.2f} s = {model.num_timesteps / dt:.0f} steps/s")
         if args.model_filename:
             model.policy.save(args.model_filename)
             print("Saved", args.model_filename)

@@ -24,7 +24,8 @@ pytestmark = pytest.mark.skipif(not os.path.isfile(os.path.join(REF, "main.py"))
 def reference_on_shims(monkeypatch, orc, tmp_path):
     from softtreemax_b200 import atari
     from oracle_engine import OracleEngine
-    monkeypatch.setattr(atari, "_ENGINE_FACTORY", OracleEngine)
+    if not torch.cuda.is_available():                       # with a GPU (and the reference) present this is the real thing, end to end
+        monkeypatch.setattr(atari, "_ENGINE_FACTORY", OracleEngine)
     monkeypatch.setattr(atari, "_ENGINES", {})
     monkeypatch.syspath_prepend(REF)
     monkeypatch.syspath_prepend(os.path.join(ROOT, "shims"))
@@ -59,9 +60,9 @@ def test_reference_cule_bfs_through_the_facade_matches_the_oracle_tree(reference
     leaves, rewards, first_action = tree.bfs(torch.from_numpy(obs)[None], 2)
     assert first_action is None and leaves.shape == (16, 4, 84, 84) and rewards.shape == (16,)
     game = orc.Game("synth_breakout")
-    stack, rew, *_ = game.bfs(root_blob.numpy(), obs.astype(np.uint8)[None], 2, gamma=0.97)
-    assert np.array_equal(leaves.numpy().astype(np.uint8), stack[0]), "leaf observation stacks differ"
-    assert np.array_equal(rewards.numpy(), rew[0]), "leaf rewards differ"
+    stack, rew, *_ = game.bfs(root_blob.cpu().numpy(), obs.astype(np.uint8)[None], 2, gamma=0.97)
+    assert np.array_equal(leaves.cpu().numpy().astype(np.uint8), stack[0]), "leaf observation stacks differ"
+    assert np.array_equal(rewards.cpu().numpy(), rew[0]), "leaf rewards differ"
     # the root env itself was not disturbed by the expansion (cule_bfs.py:110-112 copies OUT of it)
     assert torch.equal(env.env.blobs[:1], root_blob)
 
