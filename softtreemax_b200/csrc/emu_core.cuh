@@ -599,7 +599,7 @@ STM_NOINLINE uint32_t sbc_decimal(uint32_t a, uint32_t v, uint32_t bc)
 
 // native row `src` of the frame being drawn -> row `dst` (whole-line reuse, see Emu::end_line)
 template <class M>
-STM_NOINLINE void tia_copy_row(M m, uint32_t dst, uint32_t src) { m.copy_row(dst, src); }
+STM_NOINLINE void tia_copy_row(M m, uint32_t dst, uint32_t src) { m.copy_row(dst, src); }   // (host test aid only; the device links rows)
 
 // ---- the per-env machine ---------------------------------------------------------------------------
 // M must provide:
@@ -612,7 +612,9 @@ STM_NOINLINE void tia_copy_row(M m, uint32_t dst, uint32_t src) { m.copy_row(dst
 //   void px16(row, q, w0..w3) store 16 pixels (grey values) of native row `row`, quad q (0..9): four packed words
 //   void px4(row, g, word)    store 4 pixels, group g (0..39)
 //   void px1(row, x, v)       store 1 pixel
-//   void copy_row(dst, src)   copy the 160 pixels of native row src to row dst (same frame)
+//   void open_row(row)        pixels of native row `row` are about to be stored (called before every catch-up that draws)
+//   void link_row(dst, src)   native row dst shows exactly what row src shows (whole-line reuse); src is the row opened last
+//   void zero_row(row)        native row `row` is black (rows the frame never reached)
 //
 // One instruction = fetch -> decode -> address -> read phase -> execute (register-only switch over
 // ~25 groups) -> write phase -> retire.  Every memory access goes through ONE read site and ONE
@@ -700,11 +702,17 @@ struct Emu {
         update_latch();
     }
 
+    // the row the current line draws into, announced to the memory policy before the (out-of-line, by-value) renderer runs
+    STM_DEV void open_row()
+    {
+        const int row = (int)line - STM_YSTART;
+        if (render && row_sampled(row)) m.open_row((uint32_t)row);
+    }
     // ---------------- TIA catch-up (out of line: see TiaLine below) ----------------
     STM_DEV void catchup(uint32_t xe)
     {
         if (xe > STM_VIS_W) xe = STM_VIS_W;
-        if (xe > rx) rx = tia_catchup<M>(m, line, rx, xe, flags, render);
+        if (xe > rx) { open_row(); rx = tia_catchup<M>(m, line, rx, xe, flags, render); }
     }
 
     // Whole-line reuse.  Most scanlines of a frame are drawn under exactly the TIA state of the line
@@ -722,8 +730,9 @@ struct Emu {
             int row = (int)line - STM_YSTART;
             bool draw = render && row_sampled(row);
             if (flags & (draw ? F_PIXCLEAN : F_CXCLEAN)) {
-                if (draw) tia_copy_row<M>(m, (uint32_t)row, (flags >> 16) & 0xFFu);
+                if (draw) m.link_row((uint32_t)row, (flags >> 16) & 0xFFu);
             } else {
+                open_row();
                 tia_catchup<M>(m, line, 0, STM_VIS_W, flags, render);
                 if (!(flags & STM_F_HMOVE_BLANK)) {
                     flags |= F_CXCLEAN;
@@ -1228,8 +1237,7 @@ struct Emu {
         if (want_pixels) {
             int r0 = (int)end_line_no - STM_YSTART; if (r0 < 0) r0 = 0;
             for (int r = r0; r < STM_VIS_H; r++)
-                if (row_sampled(r))
-                    for (uint32_t q = 0; q < 10; q++) m.px16((uint32_t)r, q, 0, 0, 0, 0);
+                if (row_sampled(r)) m.zero_row((uint32_t)r);
         }
         m.st32(O_FRAME, m.ld32(O_FRAME) + 1);
     }

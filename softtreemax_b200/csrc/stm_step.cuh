@@ -38,8 +38,17 @@ using namespace stm;
 typedef StmStepArgs StepArgs;
 
 constexpr int kTileEnvs = 32;                                   // envs per native-scratch tile (= warp)
-constexpr size_t kTileWords = 2ull * STM_VIS_H * 40 * kTileEnvs; // u32 per tile (2 frames)
-constexpr int kStepThreads = 128;
+// Native-frame scratch of one tile, two frames.  Pixel area: [frame][slot 0..209][quad 10][lane 32] uint4 — a SLOT holds one
+// distinct row of 160 grey pixels; slot 0 is never written and stays zero.  Row table: [frame][row 0..209][lane 32] bytes — the
+// slot that native row `row` of the lane's frame shows.  K2 stores a row's pixels once, when its content differs from the row
+// above (whole-line reuse: a repeated row is ONE byte in the table, not a 160-byte copy), K3 reads rows through the table.
+constexpr size_t kTilePixWords = 2ull * STM_VIS_H * 40 * kTileEnvs;
+constexpr size_t kTileSlotWords = 2ull * STM_VIS_H * kTileEnvs / 4;
+constexpr size_t kTileWords = kTilePixWords + kTileSlotWords;    // u32 per tile
+#ifndef STM_STEP_THREADS
+#define STM_STEP_THREADS 128
+#endif
+constexpr int kStepThreads = STM_STEP_THREADS;
 #ifndef STM_STEP_MIN_CTAS
 #define STM_STEP_MIN_CTAS 4   /* measured: 4 CTAs/SM without spills beats 5 with */
 #endif
@@ -58,7 +67,9 @@ struct DevMem {
     const uint8_t *sgrey;      // shared: colour index -> grey (data of the ctx, not of the build)
     const uint2 *pre;          // global, read-only path (L1-resident: 32 KB for a 4 KB cartridge)
     uint32_t *scr;             // native scratch of this env's tile, + lane
+    uint8_t *rowslot;          // row table of this env's tile, + lane
     uint32_t fsel;             // which of the two native frames is being drawn
+    uint32_t cur_row, cur_slot, nslots;     // the row opened last, its slot, slots used in this frame
 
     __device__ __forceinline__ uint32_t boff(uint32_t o) const { return (o >> 2) * (kStepThreads * 4) + (o & 3); }
     __device__ __forceinline__ uint32_t ld8(uint32_t o) const { return blob[boff(o)]; }
@@ -72,24 +83,18 @@ struct DevMem {
     { uint2 v = __ldg(pre + off); w = v.x; ops = v.y; }
     __device__ __forceinline__ uint32_t opinfo(uint32_t op) const { return lut[op]; }
     __device__ __forceinline__ uint32_t grey(uint32_t i) const { return sgrey[i & 127]; }
-    // scr points at this lane's uint4 slot of (frame 0, row 0, quad 0); quads are kTileEnvs uint4 apart
-    __device__ __forceinline__ uint32_t *quad(uint32_t row, uint32_t q) const
-    { return scr + (size_t)((fsel * STM_VIS_H + row) * 10 + q) * (kTileEnvs * 4); }
+    // scr points at this lane's uint4 of (frame 0, slot 0, quad 0); quads are kTileEnvs uint4 apart.  Every pixel store goes
+    // to the slot of the row opened last (open_row precedes the renderer), whatever `row` says.
+    __device__ __forceinline__ uint32_t *quad(uint32_t, uint32_t q) const
+    { return scr + (size_t)((fsel * STM_VIS_H + cur_slot) * 10 + q) * (kTileEnvs * 4); }
+    __device__ __forceinline__ void begin_frame(uint32_t f) { fsel = f; cur_row = 0xFFFFFFFFu; cur_slot = 0; nslots = 0; }
+    __device__ __forceinline__ void set_row(uint32_t row, uint32_t slot) { rowslot[(size_t)(fsel * STM_VIS_H + row) * kTileEnvs] = (uint8_t)slot; }
+    __device__ __forceinline__ void open_row(uint32_t row)
+    { if (row != cur_row) { cur_row = row; cur_slot = ++nslots; set_row(row, cur_slot); } }
+    __device__ __forceinline__ void link_row(uint32_t dst, uint32_t) { set_row(dst, cur_slot); }      // src == cur_row: the clean row is the one opened last
+    __device__ __forceinline__ void zero_row(uint32_t row) { set_row(row, 0); }
     __device__ __forceinline__ void px16(uint32_t row, uint32_t q, uint32_t a, uint32_t b, uint32_t c, uint32_t d)
     { __stcg(reinterpret_cast<uint4 *>(quad(row, q)), make_uint4(a, b, c, d)); }
-    __device__ __forceinline__ void copy_row(uint32_t dst, uint32_t src)
-    {
-        const uint4 *s = reinterpret_cast<const uint4 *>(quad(src, 0));
-        uint4 *d = reinterpret_cast<uint4 *>(quad(dst, 0));
-        #pragma unroll
-        for (int h = 0; h < 2; h++) {                    // five loads in flight, then five stores
-            uint4 v[5];
-            #pragma unroll
-            for (int q = 0; q < 5; q++) v[q] = __ldcg(s + (size_t)(5 * h + q) * kTileEnvs);   // L2 only: L1 is for the fetch path
-            #pragma unroll
-            for (int q = 0; q < 5; q++) __stcg(d + (size_t)(5 * h + q) * kTileEnvs, v[q]);
-        }
-    }
     __device__ __forceinline__ void px4(uint32_t row, uint32_t g, uint32_t w) { quad(row, g >> 2)[g & 3] = w; }
     __device__ __forceinline__ void px1(uint32_t row, uint32_t x, uint32_t v)
     { reinterpret_cast<uint8_t *>(quad(row, x >> 4))[x & 15] = (uint8_t)v; }
@@ -135,7 +140,8 @@ stm_step_kernel(const StepArgs a)
     m.blob = reinterpret_cast<uint8_t *>(sblob + tid);
     m.rom = srom; m.lut = slut; m.pre = a.pre; m.sgrey = reinterpret_cast<const uint8_t *>(sgrey);
     m.scr = a.scratch ? a.scratch + (size_t)(env / kTileEnvs) * kTileWords + (env % kTileEnvs) * 4 : nullptr;
-    m.fsel = 0;
+    m.rowslot = a.scratch ? reinterpret_cast<uint8_t *>(a.scratch + (size_t)(env / kTileEnvs) * kTileWords + kTilePixWords) + env % kTileEnvs : nullptr;
+    m.begin_frame(0);
     Emu<DevMem> e(m, a.gp);
     e.load();
     int lives = a.lives[env];
@@ -145,7 +151,7 @@ stm_step_kernel(const StepArgs a)
     for (int f = 0; f < a.frameskip; f++) {
         bool want = a.render && f >= a.frameskip - 2;
         // the newest frame always goes to slot 1, the one before it to slot 0
-        m.fsel = (f == a.frameskip - 1) ? 1u : 0u;
+        m.begin_frame((f == a.frameskip - 1) ? 1u : 0u);
         e.template run_frame<Core>(ale, want, lanes);
         int r = e.get_data(a.episodic_life != 0, done, lives);
         rew = __fadd_rn(rew, __fmul_rn(a.weight, (float)r));

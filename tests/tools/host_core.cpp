@@ -32,6 +32,9 @@ struct HostMem {
     void px16(uint32_t row, uint32_t q, uint32_t a, uint32_t b, uint32_t c, uint32_t d)
     { px4(row, 4 * q, a); px4(row, 4 * q + 1, b); px4(row, 4 * q + 2, c); px4(row, 4 * q + 3, d); }
     void copy_row(uint32_t dst, uint32_t src) { if (fb) memcpy(fb + dst * 160, fb + src * 160, 160); }
+    void open_row(uint32_t) {}
+    void link_row(uint32_t dst, uint32_t src) { copy_row(dst, src); }
+    void zero_row(uint32_t row) { if (fb) memset(fb + row * 160, 0, 160); }
     void px1(uint32_t row, uint32_t x, uint32_t v) { if (fb) fb[row * 160 + x] = (uint8_t)v; }
 };
 uint32_t g_lut[256];
