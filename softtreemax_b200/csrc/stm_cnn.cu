@@ -26,6 +26,7 @@
 //              arrive on tmem_empty[buf] — so the epilogue of tile i overlaps the MMAs of tile i+1.
 // The whole weight matrix of conv1/conv2/conv3/heads (16-72 KB) stays resident in shared memory
 // for the life of the CTA; only fc (3.2 MB) streams its W slices through the ring.
+#include <cuda.h>                 // CUtensorMap and its enums (types only: the encoder is fetched through the runtime, no libcuda link)
 #include <cuda_runtime.h>
 #include <cuda_bf16.h>
 #include <cuda_fp16.h>
@@ -177,6 +178,15 @@ __host__ __device__ constexpr int cta_threads(int prod_warps) { return prod_warp
 
 __device__ __forceinline__ void mbar_arrive(uint64_t *bar)
 { asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" :: "r"(smem_u32(bar)) : "memory"); }
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t *bar, uint32_t bytes)
+{ asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(smem_u32(bar)), "r"(bytes) : "memory"); }
+// TMA: one 2-D tile (box of the tensor map, 128B-swizzled on the way in) from THIS GPU's global memory into shared memory;
+// completion is signalled on the mbarrier as transaction bytes.  No multicast: one CTA, one destination.
+__device__ __forceinline__ void tma_load_2d(void *dst_smem, const CUtensorMap *map, int c0, int c1, uint64_t *bar)
+{
+    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+                 :: "r"(smem_u32(dst_smem)), "l"(reinterpret_cast<uint64_t>(map)), "r"(smem_u32(bar)), "r"(c0), "r"(c1) : "memory");
+}
 
 template <int N, bool kResidentW, int kStages, int kProdWarps>
 __global__ void __launch_bounds__(cta_threads(kProdWarps), 2)
@@ -466,7 +476,7 @@ template <int kConv> __host__ __device__ constexpr int win_off(int kc) { return 
 
 template <int kStages, int kConv>
 __global__ void __launch_bounds__(288, 1)
-stm_cnn_window_kernel(const __nv_bfloat16 *__restrict__ in, const __nv_bfloat16 *__restrict__ wt, const float *__restrict__ bias,
+stm_cnn_window_kernel(const __grid_constant__ CUtensorMap in_map, const __nv_bfloat16 *__restrict__ wt, const float *__restrict__ bias,
                       __nv_bfloat16 *__restrict__ out, uint32_t M_total, WinGeom g)
 {
     constexpr int N = 64, kBBytes = N * kChunkK * 2;
@@ -491,9 +501,10 @@ stm_cnn_window_kernel(const __nv_bfloat16 *__restrict__ in, const __nv_bfloat16 
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     }
     if (tid == 0) {
-        for (int i = 0; i < kStages; i++) { mbar_init(&full[i], 4); mbar_init(&empty[i], 1); }
+        for (int i = 0; i < kStages; i++) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }     // full: one expect_tx arrival + the TMA's bytes
         for (int i = 0; i < kAcc; i++) { mbar_init(&tfull[i], 1); mbar_init(&tempty[i], 4); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("prefetch.tensormap [%0];" :: "l"(reinterpret_cast<uint64_t>(&in_map)) : "memory");
     }
     for (int kc = 0; kc < g.nchunks; kc++) {
         const uint4 *wsrc = reinterpret_cast<const uint4 *>(wt + (size_t)kc * N * kChunkK);
@@ -507,33 +518,17 @@ stm_cnn_window_kernel(const __nv_bfloat16 *__restrict__ in, const __nv_bfloat16 
     const uint32_t tmem_base = tmem_base_s;
 
     if (warp < 4) {
-        // ===================== producers: one contiguous 160-row window per tile =====================
-        constexpr int kDepth = kStages - 1;
-        const int my_tiles = blockIdx.x < ntiles ? (int)((ntiles - blockIdx.x + gridDim.x - 1) / gridDim.x) : 0;
-        uint32_t tile = blockIdx.x, st = 0, ph = 0, st_pub = 0;
-        for (int i = 0; i < my_tiles + kDepth && !(g.debug & 2048); i++) {
-            if (i < my_tiles) {
+        // ===================== producer: one TMA per tile =====================
+        // The window of a tile is 160 consecutive 128-byte rows of the activation matrix: ONE cp.async.bulk.tensor (box 64 x 160,
+        // SWIZZLE_128B — the layout the MMA descriptors expect, written by the copy engine itself) issued by one thread; rows past
+        // the end of the matrix are zero-filled by the hardware.  The ring runs kStages tiles ahead of the MMA warp.
+        if (tid == 0) {
+            uint32_t st = 0, ph = 0;
+            for (uint32_t tile = blockIdx.x; tile < ntiles && !(g.debug & 2048); tile += gridDim.x) {
                 mbar_wait(&empty[st], ph ^ 1);
-                const uint32_t v0 = tile * kTileM, dst0 = smem_u32(sW + st * kWinBytes);
-                #pragma unroll
-                for (int k = 0; k < kWinRows * 8 / 128; k++) {
-                    const uint32_t idx = (uint32_t)tid + 128u * k, r = idx >> 3, pc = idx & 7u;
-                    const uint32_t row = v0 + r;
-                    const bool ok = row < M_total && !(g.debug & 1);    // the input has exactly M_total rows
-                    const __nv_bfloat16 *src = in + (size_t)(ok ? row : 0u) * 64 + pc * 8;
-                    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;"
-                                 :: "r"(dst0 + swz(r, pc)), "l"(src), "r"(ok ? 16u : 0u) : "memory");
-                }
-                tile += gridDim.x;
+                mbar_arrive_expect_tx(&full[st], kWinBytes);
+                tma_load_2d(sW + st * kWinBytes, &in_map, 0, (int)(tile * kTileM), &full[st]);
                 if (++st == kStages) { st = 0; ph ^= 1; }
-            }
-            asm volatile("cp.async.commit_group;" ::: "memory");
-            if (i >= kDepth) {
-                asm volatile("cp.async.wait_group %0;" :: "n"(kDepth) : "memory");
-                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-                __syncwarp();
-                if ((tid & 31) == 0) mbar_arrive(&full[st_pub]);
-                if (++st_pub == kStages) st_pub = 0;
             }
         }
     } else if (warp == 8) {
@@ -671,7 +666,9 @@ stm_cnn_conv1_window_kernel(const uint8_t *__restrict__ in, const __nv_bfloat16 
         const uint32_t r = (uint32_t)tid % kWinRows, half = (uint32_t)tid / kWinRows;
         const int my_tiles = blockIdx.x < ntiles ? (int)((ntiles - blockIdx.x + gridDim.x - 1) / gridDim.x) : 0;
         uint32_t tile = blockIdx.x, st = 0, ph = 0;
-        uint32_t cur[8], nxt[8];
+        // the global loads run TWO tiles ahead of the conversion (one tile, ~0.9 us, does not cover DRAM latency under load:
+        // the producers sat on the scoreboard, ncu long-scoreboard 6.1 per issue)
+        uint32_t cur[8], nxt[8], nx2[8];
         auto load_next = [&](uint32_t *w) {
             const uint32_t v = tile * kTileM + r;
             const bool ok = v < M_total && !(debug & 1);
@@ -685,6 +682,7 @@ stm_cnn_conv1_window_kernel(const uint8_t *__restrict__ in, const __nv_bfloat16 
             tile += gridDim.x;
         };
         if (my_tiles > 0) load_next(nxt);
+        if (my_tiles > 1) load_next(nx2);
         const __half2 k1024 = __half2half2(__ushort_as_half((unsigned short)0x6400));
         auto widen = [&](uint32_t w, uint32_t sel) -> uint32_t {
             uint32_t biased = __byte_perm(w, 0x64646464u, sel);
@@ -693,8 +691,8 @@ stm_cnn_conv1_window_kernel(const uint8_t *__restrict__ in, const __nv_bfloat16 
         };
         for (int i = 0; i < my_tiles; i++) {
             #pragma unroll
-            for (int k = 0; k < 8; k++) cur[k] = nxt[k];
-            if (i + 1 < my_tiles) load_next(nxt);
+            for (int k = 0; k < 8; k++) { cur[k] = nxt[k]; nxt[k] = nx2[k]; }
+            if (i + 2 < my_tiles) load_next(nx2);
             mbar_wait(&empty[st], ph ^ 1);
             uint8_t *wbase = sW + st * kWinBytes;
             if (!(debug & 16)) {
@@ -946,7 +944,28 @@ int launch_window(stm_ctx *ctx, const __nv_bfloat16 *in, const __nv_bfloat16 *w,
     const size_t smem = (size_t)kStages * kWinBytes + (size_t)g.nchunks * 64 * kChunkK * 2 + 1024;
     const long long tiles = (M + kTileM - 1) / kTileM;
     const long long grid = tiles < 148 ? tiles : 148;
-    stm_cnn_window_kernel<kStages, kConv><<<(unsigned)grid, 288, smem, st>>>(in, w, b, out, (uint32_t)M, g);
+    // the activation matrix [M rows][64 bf16] as a 2-D tensor map; box = one window (64 x 160), 128-byte swizzle
+    CUtensorMap map;
+    {
+        typedef CUresult (*EncodeFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *, const cuuint64_t *,
+                                     const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                     CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+        static EncodeFn encode = nullptr;
+        if (!encode) {
+            cudaDriverEntryPointQueryResult q;
+            void *fn = nullptr;
+            if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &q) != cudaSuccess || !fn)
+                return stm_internal_fail(ctx, STM_ERR_CUDA, "stm_cnn: cuTensorMapEncodeTiled is not available from this driver");
+            encode = reinterpret_cast<EncodeFn>(fn);
+        }
+        const cuuint64_t dims[2] = { 64, (cuuint64_t)M }, strides[1] = { 128 };
+        const cuuint32_t box[2] = { 64, (cuuint32_t)kWinRows }, estr[2] = { 1, 1 };
+        if (encode(&map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<__nv_bfloat16 *>(in), dims, strides, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
+            return stm_internal_fail(ctx, STM_ERR_CUDA, "stm_cnn: cuTensorMapEncodeTiled failed");
+    }
+    stm_cnn_window_kernel<kStages, kConv><<<(unsigned)grid, 288, smem, st>>>(map, w, b, out, (uint32_t)M, g);
     stm_internal_count_launch(ctx);
     cudaError_t e = cudaGetLastError();
     return e == cudaSuccess ? STM_OK : stm_internal_fail(ctx, STM_ERR_CUDA, cudaGetErrorString(e));
