@@ -489,7 +489,7 @@ stm_cnn_window_kernel(const __grid_constant__ CUtensorMap in_map, const __nv_bfl
     constexpr int kAcc = 8;
     __shared__ __align__(8) uint64_t full[kStages], empty[kStages], tfull[kAcc], tempty[kAcc];
     __shared__ uint32_t tmem_base_s;
-    __shared__ float sbias[N];
+    __shared__ __align__(16) float sbias[N];
     const int tid = threadIdx.x, warp = tid >> 5;
     const uint32_t ntiles = (M_total + kTileM - 1) / kTileM;
     constexpr uint32_t kCols = kAcc * N;                  // 512: the whole tensor memory of the SM (one CTA per SM)
@@ -579,22 +579,28 @@ stm_cnn_window_kernel(const __grid_constant__ CUtensorMap in_map, const __nv_bfl
             const bool valid = v < M_total && oy < (uint32_t)g.OH && ox < (uint32_t)g.OW && !(g.debug & 4);
             __nv_bfloat16 *orow = out + ((size_t)img * P + oy * (uint32_t)g.OW + ox) * N;
             const uint32_t taddr = tmem_base + buf * N + ((uint32_t)(ew * 32) << 16);
-            #pragma unroll 1
-            for (int c0 = 0; c0 < N; c0 += 16) {
-                if (g.debug & 32) break;
-                uint32_t r[16];
-                asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 "
-                             "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
-                             : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
-                               "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
-                             : "r"(taddr + (uint32_t)c0));
-                asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-                if (valid) {
+            // the whole 64-column accumulator row in two 32-column TMEM loads and ONE wait (it was four loads, each waited for)
+            uint32_t r[64];
+            asm volatile("tcgen05.ld.sync.aligned.32x32b.x32.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+                         : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31]) : "r"(taddr));
+            asm volatile("tcgen05.ld.sync.aligned.32x32b.x32.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+                         : "=r"(r[32]), "=r"(r[33]), "=r"(r[34]), "=r"(r[35]), "=r"(r[36]), "=r"(r[37]), "=r"(r[38]), "=r"(r[39]), "=r"(r[40]), "=r"(r[41]), "=r"(r[42]), "=r"(r[43]), "=r"(r[44]), "=r"(r[45]), "=r"(r[46]), "=r"(r[47]), "=r"(r[48]), "=r"(r[49]), "=r"(r[50]), "=r"(r[51]), "=r"(r[52]), "=r"(r[53]), "=r"(r[54]), "=r"(r[55]), "=r"(r[56]), "=r"(r[57]), "=r"(r[58]), "=r"(r[59]), "=r"(r[60]), "=r"(r[61]), "=r"(r[62]), "=r"(r[63]) : "r"(taddr + 32u));
+            asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+            // the accumulator is in registers: hand the buffer back to the MMA warp before the arithmetic and the stores
+            asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+            __syncwarp();
+            if ((tid & 31) == 0) mbar_arrive(&tempty[buf]);
+            if (valid) {
+                #pragma unroll
+                for (int c0 = 0; c0 < N; c0 += 16) {
                     uint32_t pk[8];
+                    float bb[16];                               // sixteen biases as four 16-byte shared loads
+                    #pragma unroll
+                    for (int j = 0; j < 4; j++) *reinterpret_cast<float4 *>(&bb[4 * j]) = *reinterpret_cast<const float4 *>(&sbias[c0 + 4 * j]);
                     #pragma unroll
                     for (int j = 0; j < 8; j++) {
-                        float x0 = __uint_as_float(r[2 * j]) + sbias[c0 + 2 * j];
-                        float x1 = __uint_as_float(r[2 * j + 1]) + sbias[c0 + 2 * j + 1];
+                        float x0 = __uint_as_float(r[c0 + 2 * j]) + bb[2 * j];
+                        float x1 = __uint_as_float(r[c0 + 2 * j + 1]) + bb[2 * j + 1];
                         if (g.relu) { x0 = fmaxf(x0, 0.f); x1 = fmaxf(x1, 0.f); }
                         __nv_bfloat162 t2 = __floats2bfloat162_rn(x0, x1);
                         pk[j] = *reinterpret_cast<uint32_t *>(&t2);
@@ -604,9 +610,6 @@ stm_cnn_window_kernel(const __grid_constant__ CUtensorMap in_map, const __nv_bfl
                     o[1] = make_uint4(pk[4], pk[5], pk[6], pk[7]);
                 }
             }
-            asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-            __syncwarp();
-            if ((tid & 31) == 0) mbar_arrive(&tempty[buf]);
         }
     }
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
@@ -638,7 +641,7 @@ stm_cnn_conv1_window_kernel(const uint8_t *__restrict__ in, const __nv_bfloat16 
     uint8_t *sB = smem + kStages * kWinBytes;              // 4 taps x 4 KB, resident
     __shared__ __align__(8) uint64_t full[kStages], empty[kStages], tfull[kAcc], tempty[kAcc];
     __shared__ uint32_t tmem_base_s;
-    __shared__ float sbias[N];
+    __shared__ __align__(16) float sbias[N];
     const int tid = threadIdx.x, warp = tid >> 5;
     const uint32_t ntiles = (M_total + kTileM - 1) / kTileM;
     constexpr uint32_t kCols = kAcc * N;                   // 256 columns
@@ -752,21 +755,24 @@ stm_cnn_conv1_window_kernel(const uint8_t *__restrict__ in, const __nv_bfloat16 
             const bool valid = v < M_total && oy < OH && ox < OW && !(debug & 4);
             __nv_bfloat16 *orow = out + ((size_t)img * P + oy * OW + ox) * N;
             const uint32_t taddr = tmem_base + buf * N + ((uint32_t)(ew * 32) << 16);
-            #pragma unroll
-            for (int c0 = 0; c0 < N; c0 += 16) {
-                uint32_t rr[16];
-                asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 "
-                             "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
-                             : "=r"(rr[0]), "=r"(rr[1]), "=r"(rr[2]), "=r"(rr[3]), "=r"(rr[4]), "=r"(rr[5]), "=r"(rr[6]), "=r"(rr[7]),
-                               "=r"(rr[8]), "=r"(rr[9]), "=r"(rr[10]), "=r"(rr[11]), "=r"(rr[12]), "=r"(rr[13]), "=r"(rr[14]), "=r"(rr[15])
-                             : "r"(taddr + (uint32_t)c0));
-                asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-                if (valid) {
+            uint32_t rr[32];                                    // the 32-column accumulator row in one TMEM load
+            asm volatile("tcgen05.ld.sync.aligned.32x32b.x32.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+                         : "=r"(rr[0]), "=r"(rr[1]), "=r"(rr[2]), "=r"(rr[3]), "=r"(rr[4]), "=r"(rr[5]), "=r"(rr[6]), "=r"(rr[7]), "=r"(rr[8]), "=r"(rr[9]), "=r"(rr[10]), "=r"(rr[11]), "=r"(rr[12]), "=r"(rr[13]), "=r"(rr[14]), "=r"(rr[15]), "=r"(rr[16]), "=r"(rr[17]), "=r"(rr[18]), "=r"(rr[19]), "=r"(rr[20]), "=r"(rr[21]), "=r"(rr[22]), "=r"(rr[23]), "=r"(rr[24]), "=r"(rr[25]), "=r"(rr[26]), "=r"(rr[27]), "=r"(rr[28]), "=r"(rr[29]), "=r"(rr[30]), "=r"(rr[31]) : "r"(taddr));
+            asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+            asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");     // registers hold it: the buffer goes back before the arithmetic
+            __syncwarp();
+            if ((tid & 31) == 0) mbar_arrive(&tempty[buf]);
+            if (valid) {
+                #pragma unroll
+                for (int c0 = 0; c0 < N; c0 += 16) {
                     uint32_t pk[8];
+                    float bb[16];
+                    #pragma unroll
+                    for (int j = 0; j < 4; j++) *reinterpret_cast<float4 *>(&bb[4 * j]) = *reinterpret_cast<const float4 *>(&sbias[c0 + 4 * j]);
                     #pragma unroll
                     for (int j = 0; j < 8; j++) {
-                        const float x0 = fmaxf(__uint_as_float(rr[2 * j]) * (1.0f / 255.0f) + sbias[c0 + 2 * j], 0.f);
-                        const float x1 = fmaxf(__uint_as_float(rr[2 * j + 1]) * (1.0f / 255.0f) + sbias[c0 + 2 * j + 1], 0.f);
+                        const float x0 = fmaxf(__uint_as_float(rr[c0 + 2 * j]) * (1.0f / 255.0f) + bb[2 * j], 0.f);
+                        const float x1 = fmaxf(__uint_as_float(rr[c0 + 2 * j + 1]) * (1.0f / 255.0f) + bb[2 * j + 1], 0.f);
                         __nv_bfloat162 t2 = __floats2bfloat162_rn(x0, x1);
                         pk[j] = *reinterpret_cast<uint32_t *>(&t2);
                     }
@@ -775,9 +781,6 @@ stm_cnn_conv1_window_kernel(const uint8_t *__restrict__ in, const __nv_bfloat16 
                     o[1] = make_uint4(pk[4], pk[5], pk[6], pk[7]);
                 }
             }
-            asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-            __syncwarp();
-            if ((tid & 31) == 0) mbar_arrive(&tempty[buf]);
         }
     }
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
