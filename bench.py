@@ -287,7 +287,17 @@ def run_train(args, rank, world, local, steps):
         dist.barrier()
     ms = shard.max_over_ranks([e0.elapsed_time(e1)], dev)[0]
     n_par = sum(p.numel() for p in pol.parameters() if p.requires_grad)
+    # tensor-core roofline of the update: forward + data gradients + weight gradients ~ 3 x the forward FLOPs of every image
+    # (conv1 has no data gradient: 2 x), against the measured bf16 peak
+    A_ = env.action_space.n
+    fwd = 18685952 + 1024 * (A_ + 1)
+    flop_per_image = 3 * fwd - 2 * 400 * 256 * 32
+    peak_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    tf_peak = float(json.load(open(peak_path))["bf16_tflops"]) if os.path.exists(peak_path) else 1590.0
+    tflops = (B * L + B) * flop_per_image * steps / (ms / 1e3) / 1e12
     return {"metric": "ppo_update_images_per_sec", "mode": "train", "value": world * (B * L + B) * steps / (ms / 1e3), "unit": "images/s",
+            "roofline": {"bound": "tensor", "achieved": tflops, "peak": tf_peak, "unit": "TFLOP/s", "frac": tflops / tf_peak,
+                         "note": "per rank; a 544-image minibatch is ~45 small launches: launch latency, not the tensor pipe, sets the time"},
             "ms_per_step": ms / steps, "n_gpus": world, "steps": steps, "loss": float(loss.detach()),
             "config": {"workload": f"synth_breakout tree_depth={depth}: one PPO minibatch of {B} cached roots per rank = {B * L + B} images "
                                    "forward + backward through NatureCNN, K5 forward + backward, Adam", "scaling": "weak"},
