@@ -32,13 +32,20 @@
 #define STM_NOINLINE static __device__ __noinline__
 #define STM_WARP_ALL(mask, pred) __all_sync((mask), (pred))
 #define STM_WARP_MIN(mask, v) __reduce_min_sync((mask), (v))
-// scanline lock-step scope: the warp (default) or, with -DSTM_CTA_LOCKSTEP, the whole thread block, so that the warps
-// that share an SM's instruction caches walk the same code region together
-#ifdef STM_CTA_LOCKSTEP
-#define STM_LINE_ALL(mask, pred) (__syncthreads_and(pred) != 0)
-#else
-#define STM_LINE_ALL(mask, pred) __all_sync((mask), (pred))
-#endif
+// Scanline lock-step scope: the warps of a thread block that share a scheduler (warp id mod 4) and with it an L0 instruction
+// cache — one named barrier per group, `group` = 32 x the group's warps | barrier id << 16.  Walking the same code region together is what
+// keeps the group's instruction fetches in L0 (K2 is bound by instruction supply: DESIGN.md §5).  Every warp of a group must keep
+// calling this until it returns true; stm_step.cuh keeps dead lanes in the loop for that reason.
+static __device__ __forceinline__ bool stm_group_all(uint32_t group, bool pred)     // group = threads | barrier id << 16
+{
+    const uint32_t w = __all_sync(0xFFFFFFFFu, pred);
+    if ((group & 0xFFFFu) == 32u) return w != 0;
+    uint32_t r;
+    asm volatile("{\n .reg .pred p, q;\n setp.ne.u32 q, %1, 0;\n barrier.red.and.pred p, %2, %3, q;\n selp.u32 %0, 1, 0, p;\n}"
+                 : "=r"(r) : "r"(w), "r"(group >> 16), "r"(group & 0xFFFFu) : "memory");
+    return r != 0;
+}
+#define STM_LINE_ALL(group, pred) stm_group_all((group), (pred))
 #else
 #define STM_LINE_ALL(mask, pred) (pred)
 #define STM_DEV inline
@@ -1209,20 +1216,22 @@ struct Emu {
 
     // ---------------- one emulated frame ----------------
     // Rows the frame never reached are zero-filled, as the oracle does.
-    // `lanes` = the warp lanes that run frames together (ballot of live envs); every one of them must
-    // call run_frame the same number of times.  Scanline lock-step: each lane runs instructions until
-    // its scanline ends, then the warp reconverges and wraps the line (the whole-line catch-up render)
-    // with all lanes active; lanes whose frame is over idle until the slowest lane's frame is over.
+    // Scanline lock-step: each lane runs instructions until its scanline ends, then the warp — on the GPU the warps of the
+    // block that share a scheduler, `lanes` = their threads and barrier (stm_group_all) — reconverges and wraps the line (the whole-line catch-up
+    // render) with all lanes active; lanes whose frame is over idle until the slowest lane's frame is over.  Every thread of
+    // the group calls run_frame the same number of times, dead lanes (`live` false) included.
     template <class Core = InterpCore>
-    STM_DEV void run_frame(uint32_t ale_action, bool want_pixels, uint32_t lanes = 0xFFFFFFFFu)
+    STM_DEV void run_frame(uint32_t ale_action, bool want_pixels, uint32_t lanes = 32u, bool live = true)
     {
         (void)lanes;
-        render = want_pixels;
-        set_action(ale_action);
-        flags &= ~(uint32_t)STM_F_FRAME_DONE;
-        brk &= ~BRK_DONE;
-        tia_dirty();                                           // a new native frame: no row to reuse yet
-        bool over = false;
+        if (live) {
+            render = want_pixels;
+            set_action(ale_action);
+            flags &= ~(uint32_t)STM_F_FRAME_DONE;
+            brk &= ~BRK_DONE;
+            tia_dirty();                                       // a new native frame: no row to reuse yet
+        }
+        bool over = !live;
         do {
             // Run every lane to the end of its scanline: Core::run_line (the interpreter loop below, or a
             // translated cartridge).
@@ -1234,6 +1243,7 @@ struct Emu {
                 over = (flags & STM_F_FRAME_DONE) != 0;
             }
         } while (!STM_LINE_ALL(lanes, over));
+        if (!live) return;
         if (want_pixels) {
             int r0 = (int)end_line_no - STM_YSTART; if (r0 < 0) r0 = 0;
             for (int r = r0; r < STM_VIS_H; r++)

@@ -15,6 +15,8 @@ struct StmStepArgs {
     const uint32_t *rom; const uint32_t *lut; const uint2 *pre; uint32_t *scratch; uint8_t *stepped;
     const uint32_t *grey;                 // the ctx's colour-index -> grey table, 128 bytes as 32 words (stm_set_palette)
     int n, frameskip, episodic_life, render; uint32_t rom_words; float weight;
+    int lock_scope;                       // who advances scanline by scanline together: 0 the warps of a scheduler (default), 1 the block, 2 each warp alone (A/B)
+    int warps_per_cta;                    // 1..kStepThreads/32: how many of the block's warps carry envs (the launch spreads its warps over the SMs)
     stm::GameParams gp;
     // frame-by-frame driving (stm_step_frame, the torchcule-style surface): `frozen` decides which envs sit the frame out
     // (the done flags as they were when the agent step began) instead of done[], and `actions` holds ALE action codes
@@ -46,18 +48,20 @@ constexpr size_t kTilePixWords = 2ull * STM_VIS_H * 40 * kTileEnvs;
 constexpr size_t kTileSlotWords = 2ull * STM_VIS_H * kTileEnvs / 4;
 constexpr size_t kTileWords = kTilePixWords + kTileSlotWords;    // u32 per tile
 #ifndef STM_STEP_THREADS
-#define STM_STEP_THREADS 128
+#define STM_STEP_THREADS 512  /* one block per SM: 16 warps, 4 per scheduler, the register file at <= 128 registers a thread */
 #endif
 constexpr int kStepThreads = STM_STEP_THREADS;
 #ifndef STM_STEP_MIN_CTAS
-#define STM_STEP_MIN_CTAS 4   /* measured: 4 CTAs/SM without spills beats 5 with */
+#define STM_STEP_MIN_CTAS 1
 #endif
 
 // ---------------------------------------------------------------------------------------------
-// K2 — batched agent step.  One env per thread, 128 envs per CTA.
-// Shared memory: the CTA's 128 state blobs, word-interleaved (word k of env t at [k*128 + t], so
-// lane t always hits bank t%32: conflict-free for every access pattern, RAM bytes included), the
-// cartridge image (4 or 8 KB) and the decode table.
+// K2 — batched agent step.  One env per thread; one block per SM, of which the first `warps_per_cta` warps carry envs (the
+// host spreads a launch's warps evenly over the SMs: 65 536 envs = 14 warps on each of 147 SMs, 16 384 envs = 4 warps on 128).
+// The warps of a block that share a scheduler advance scanline by scanline together (emu_core.cuh stm_group_all).
+// Shared memory: the block's state blobs, word-interleaved (word k of thread t at [k*512 + t], so lane t always hits
+// bank t%32: conflict-free for every access pattern, RAM bytes included), the cartridge image (4 or 8 KB), the decode
+// table and the grey table.
 // ---------------------------------------------------------------------------------------------
 
 struct DevMem {
@@ -116,8 +120,9 @@ stm_step_kernel(const StepArgs a)
     for (uint32_t i = tid; i < 256; i += kStepThreads) slut[i] = a.lut[i];
     uint32_t *sgrey = slut + 256;
     if (tid < 32) sgrey[tid] = a.grey[tid];
-    const int env = blockIdx.x * kStepThreads + tid;
-    const bool valid = env < a.n;
+    const int warp = tid >> 5;
+    const int env = (blockIdx.x * a.warps_per_cta + warp) * 32 + (tid & 31);
+    const bool valid = warp < a.warps_per_cta && env < a.n;
     if (valid) {
         const uint4 *g = reinterpret_cast<const uint4 *>(a.states + (size_t)env * STM_STATE_BYTES);
         #pragma unroll
@@ -128,13 +133,16 @@ stm_step_kernel(const StepArgs a)
         }
     }
     __syncthreads();
+    if (warp >= a.warps_per_cta) return;                 // whole warps without envs: they are in no scheduler group
+    // threads of this warp's scheduler group (the warps w of the block with w % 4 == warp % 4 that carry envs)
+    const uint32_t gw = a.lock_scope == 1 ? (uint32_t)a.warps_per_cta : a.lock_scope == 2 ? 1u : (uint32_t)((a.warps_per_cta - (warp & 3) + 3) >> 2);
+    const uint32_t lanes = 32u * gw | (a.lock_scope == 1 ? 1u : 1u + (uint32_t)(warp & 3)) << 16;
     uint32_t done = valid ? a.done[env] : 1u;
     const uint32_t frozen = valid ? (a.frozen ? (uint32_t)a.frozen[env] : done) : 1u;
-    // lanes that emulate; they advance scanline by scanline in lock-step (Emu::run_frame)
-    const uint32_t lanes = __ballot_sync(0xFFFFFFFFu, valid && !frozen);
-    if (!valid) return;
-    if (a.stepped) a.stepped[env] = frozen ? 0 : 1;
-    if (frozen) return;                                  // frozen env: nothing changes
+    // every warp of a group has to reach every barrier of the lock-step, so dead lanes (past n, or frozen: nothing changes
+    // for them) stay and idle through run_frame
+    const bool live = valid && !frozen;
+    if (valid && a.stepped) a.stepped[env] = frozen ? 0 : 1;
 
     DevMem m;
     m.blob = reinterpret_cast<uint8_t *>(sblob + tid);
@@ -143,19 +151,25 @@ stm_step_kernel(const StepArgs a)
     m.rowslot = a.scratch ? reinterpret_cast<uint8_t *>(a.scratch + (size_t)(env / kTileEnvs) * kTileWords + kTilePixWords) + env % kTileEnvs : nullptr;
     m.begin_frame(0);
     Emu<DevMem> e(m, a.gp);
-    e.load();
-    int lives = a.lives[env];
-    float rew = a.rewards[env];
-    uint32_t act = a.actions ? a.actions[env] : (uint32_t)(env % (int)a.gp.n_actions);
-    uint32_t ale = a.action_codes ? act : (uint32_t)a.gp.actions[act];
+    int lives = 0; float rew = 0.f; uint32_t ale = 0;
+    if (live) {
+        e.load();
+        lives = a.lives[env];
+        rew = a.rewards[env];
+        uint32_t act = a.actions ? a.actions[env] : (uint32_t)(env % (int)a.gp.n_actions);
+        ale = a.action_codes ? act : (uint32_t)a.gp.actions[act];
+    }
     for (int f = 0; f < a.frameskip; f++) {
         bool want = a.render && f >= a.frameskip - 2;
         // the newest frame always goes to slot 1, the one before it to slot 0
         m.begin_frame((f == a.frameskip - 1) ? 1u : 0u);
-        e.template run_frame<Core>(ale, want, lanes);
-        int r = e.get_data(a.episodic_life != 0, done, lives);
-        rew = __fadd_rn(rew, __fmul_rn(a.weight, (float)r));
+        e.template run_frame<Core>(ale, want, lanes, live);
+        if (live) {
+            int r = e.get_data(a.episodic_life != 0, done, lives);
+            rew = __fadd_rn(rew, __fmul_rn(a.weight, (float)r));
+        }
     }
+    if (!live) return;
     e.store();
     uint4 *g = reinterpret_cast<uint4 *>(a.states + (size_t)env * STM_STATE_BYTES);
     #pragma unroll
