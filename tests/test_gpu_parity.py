@@ -228,6 +228,24 @@ def test_bfs_host_entry_point(orc, engines):
     assert np.array_equal(got["lives"], want[3].reshape(-1))
 
 
+@pytest.mark.parametrize("game,n_roots,depth", [("synth_pong", 5, 2), ("synth_breakout", 7, 3), ("synth_pacman", 3, 2), ("synth_breakout", 300, 2)])
+def test_bfs_host_matches_device_path(orc, engines, game, n_roots, depth):
+    """stm_bfs_host resolves the frames of level 1 after level 2 has been emulated (the root-stack upload hides under both
+    launches): same tree as stm_bfs bit for bit, on ragged level sizes, three levels, and when the scratch is too small
+    for the two levels side by side (the in-order path)."""
+    g = orc.Game(game)
+    eng = engines(game)
+    roots, stacks = orc.make_roots(g, n_roots, seed=5)
+    ref = eng.bfs(dev(roots, eng), dev(stacks, eng), depth)
+    torch.cuda.synchronize()
+    got = eng.bfs_host(roots, stacks, depth)
+    for k in ("stacks", "rewards", "done", "lives"):
+        assert np.array_equal(got[k], ref[k].cpu().numpy()), k
+    want = g.bfs(roots, stacks, depth)
+    assert np.array_equal(got["stacks"], want[0].reshape(-1, 4, 84, 84))
+    assert np.array_equal(got["rewards"], want[1].reshape(-1))
+
+
 def test_full_size_properties(orc, engines):
     """BASELINE size (Breakout depth 3, 1024 roots = 65 536 leaves): too big for the oracle in a test,
     so check size-independent properties: determinism, root-permutation equivariance, the stack-shift
