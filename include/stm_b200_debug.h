@@ -14,7 +14,8 @@ extern "C" {
 
 /* Per-kernel device timing for bench.py's roofline: when enabled, a CUDA event pair is recorded on
  * the launch stream around every K1/K2/K3 launch.  stm_timing_read waits for them and returns the
- * summed milliseconds and launch counts by kind {0: clone, 1: step, 2: frames}, then clears. */
+ * summed milliseconds and launch counts by kind {0: clone, 1: step, 2: frames, 3: stack shift (stm_bfs runs it on its own
+ * stream, under the step kernel)} — arrays of 4 — then clears. */
 int stm_timing_enable(stm_ctx *ctx, int on);
 int stm_timing_read(stm_ctx *ctx, float *ms_by_kind, int *launches_by_kind);
 

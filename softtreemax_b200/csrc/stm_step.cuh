@@ -116,8 +116,10 @@ stm_step_kernel(const StepArgs a)
     uint32_t *srom = sblob + 64 * kStepThreads;
     uint32_t *slut = srom + a.rom_words;
     const int tid = threadIdx.x;
-    for (uint32_t i = tid; i < a.rom_words; i += kStepThreads) srom[i] = a.rom[i];
-    for (uint32_t i = tid; i < 256; i += kStepThreads) slut[i] = a.lut[i];
+    // the block is launched with 32 * warps_per_cta threads (kStepThreads is the shared-memory pitch and the upper bound): what
+    // a smaller block leaves of the SM's registers is room for K3b's copy blocks beside it
+    for (uint32_t i = tid; i < a.rom_words; i += blockDim.x) srom[i] = a.rom[i];
+    for (uint32_t i = tid; i < 256; i += blockDim.x) slut[i] = a.lut[i];
     uint32_t *sgrey = slut + 256;
     if (tid < 32) sgrey[tid] = a.grey[tid];
     const int warp = tid >> 5;
@@ -133,7 +135,6 @@ stm_step_kernel(const StepArgs a)
         }
     }
     __syncthreads();
-    if (warp >= a.warps_per_cta) return;                 // whole warps without envs: they are in no scheduler group
     // threads of this warp's scheduler group (the warps w of the block with w % 4 == warp % 4 that carry envs)
     const uint32_t gw = a.lock_scope == 1 ? (uint32_t)a.warps_per_cta : a.lock_scope == 2 ? 1u : (uint32_t)((a.warps_per_cta - (warp & 3) + 3) >> 2);
     const uint32_t lanes = 32u * gw | (a.lock_scope == 1 ? 1u : 1u + (uint32_t)(warp & 3)) << 16;

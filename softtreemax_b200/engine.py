@@ -212,7 +212,7 @@ class Engine:
         check(lib().stm_timing_enable(self._h, int(on)), self._h)
 
     def timing_read(self):
-        ms = (C.c_float * 3)()
-        cnt = (C.c_int * 3)()
+        ms = (C.c_float * 4)()
+        cnt = (C.c_int * 4)()
         check(lib().stm_timing_read(self._h, ms, cnt), self._h)
-        return {k: (float(ms[i]), int(cnt[i])) for i, k in enumerate(("clone", "step", "frames"))}
+        return {k: (float(ms[i]), int(cnt[i])) for i, k in enumerate(("clone", "step", "frames", "shift"))}
