@@ -112,7 +112,10 @@ int stm_frame_obs(stm_ctx *ctx, uint8_t *obs, int n, void *stream);
  *   leaf_stacks  n_roots x A^depth x 4 x 84 x 84 u8
  *   leaf_rewards n_roots x A^depth f32, sign() applied when clip_reward (cule_bfs.py:204-206)
  *   leaf_done    n_roots x A^depth u8 ; leaf_lives i32 ; leaf_states x256 — each may be NULL.
- * Leaf j of root r sits at r*A^depth + j; its first action is j / A^(depth-1). */
+ * Leaf j of root r sits at r*A^depth + j; its first action is j / A^(depth-1).
+ * Everything is ordered on `stream`; inside the call a second stream of the ctx (forked from and joined back into
+ * `stream` by events, so the call may be captured into a CUDA graph) copies the three older planes of every child
+ * stack while the level is being emulated. */
 int stm_bfs(stm_ctx *ctx, const uint8_t *root_states, const uint8_t *root_stacks, int n_roots,
             int depth, float gamma, int frameskip, int episodic_life, int clip_reward,
             uint8_t *leaf_stacks, float *leaf_rewards, uint8_t *leaf_done, int32_t *leaf_lives,
