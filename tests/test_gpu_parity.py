@@ -92,6 +92,35 @@ def test_k2_k3_one_level_bitexact(orc, engines, name, frameskip):
     assert ob[3 * A:4 * A, 3].max() == 0                        # frozen envs produce an all-zero new frame
 
 
+@pytest.mark.parametrize("wpc,scope", [(3, 0), (5, 0), (16, 0), (6, 1), (4, 2)])
+def test_k2_block_shapes_bitexact(orc, monkeypatch, wpc, scope):
+    """The step kernel under every block shape the host can choose: groups of the scheduler with 1-4 warps each
+    (STM_STEP_WPC = 3, 5, 16 — small launches in the other tests run one warp per block), the block-wide and the
+    warp-only lock-step.  Ragged launch, a frozen env, blocks whose last warps carry no env: same bits as the oracle."""
+    from softtreemax_b200.engine import Engine
+    monkeypatch.setenv("STM_STEP_WPC", str(wpc))
+    monkeypatch.setenv("STM_STEP_SCOPE", str(scope))
+    g = orc.Game("synth_breakout")
+    eng = Engine("synth_breakout")
+    try:
+        A, R = g.n_actions, 150                                 # 600 envs: 19 warps, the last one ragged
+        roots, stacks = orc.make_roots(g, R, seed=9, base_steps=30, spread=23)
+        rew0 = np.zeros(R, np.float32)
+        done0 = np.zeros(R, np.uint8)
+        done0[[3, 64, 65, 66, 67, 68, 69, 70, 71]] = 1           # frozen envs, among them a whole warp of children (64..71 x 4)
+        lives0 = np.array([g.lives(r) for r in roots], np.int32)
+        st, rw, dn, lv, ob = oracle_level(orc, g, roots, rew0, done0, lives0, stacks, A, 0.5, 4)
+        d = eng.expand(dev(roots, eng), dev(rew0, eng), dev(done0, eng), dev(lives0, eng), A)
+        eng.step(*d, frameskip=4, weight=0.5, render=True)
+        obs = eng.frames(dev(stacks, eng), R * A, fanout=A)
+        torch.cuda.synchronize()
+        assert np.array_equal(d[0].cpu().numpy(), st), "state blobs"
+        assert np.array_equal(d[1].cpu().numpy(), rw) and np.array_equal(d[2].cpu().numpy(), dn) and np.array_equal(d[3].cpu().numpy(), lv)
+        assert np.array_equal(obs.cpu().numpy(), ob), "observation stacks"
+    finally:
+        eng.close()
+
+
 @pytest.mark.parametrize("seed", range(9))
 def test_random_rom_step_bitexact(orc, seed):
     """Cartridges of random bytes: every opcode incl. undocumented ones, wild TIA/RIOT traffic,
@@ -244,6 +273,30 @@ def test_bfs_host_matches_device_path(orc, engines, game, n_roots, depth):
     want = g.bfs(roots, stacks, depth)
     assert np.array_equal(got["stacks"], want[0].reshape(-1, 4, 84, 84))
     assert np.array_equal(got["rewards"], want[1].reshape(-1))
+
+
+def test_bfs_replays_from_a_cuda_graph(orc, engines):
+    """stm_bfs forks a second stream for the stack shift and joins it before returning: the whole call captures into one CUDA
+    graph, and a replay on NEW roots written into the same buffers reproduces the eager tree bit for bit."""
+    g = orc.Game("synth_breakout")
+    eng = engines("synth_breakout")
+    roots_a, stacks_a = orc.make_roots(g, 6, seed=21)
+    roots_b, stacks_b = orc.make_roots(g, 6, seed=22)
+    dr, ds = dev(roots_a, eng), dev(stacks_a, eng)
+    eng.bfs(dr, ds, 2)                                   # pools, streams and events exist before the capture
+    torch.cuda.synchronize()
+    out = eng.bfs(dr, ds, 2)
+    graph = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(graph):
+        eng.bfs(dr, ds, 2, out=out)
+    for roots, stacks in ((roots_b, stacks_b), (roots_a, stacks_a)):
+        dr.copy_(torch.from_numpy(roots)); ds.copy_(torch.from_numpy(stacks))
+        graph.replay()
+        torch.cuda.synchronize()
+        want = g.bfs(roots, stacks, 2)
+        assert np.array_equal(out["stacks"].cpu().numpy(), want[0].reshape(-1, 4, 84, 84))
+        assert np.array_equal(out["rewards"].cpu().numpy(), want[1].reshape(-1))
+        assert np.array_equal(out["done"].cpu().numpy(), want[2].reshape(-1))
 
 
 def test_full_size_properties(orc, engines):
