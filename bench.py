@@ -710,7 +710,7 @@ def main():
                     "how": "two independent groups of roots_per_gpu roots, two contexts on two streams half a step apart"},
                 "interpreter_only": None if not ms_interp else {
                     "value": world * L / (ms_interp / 1e3), "unit": UNIT, "ms_per_step": ms_interp,
-                    "what": "the same step with STM_XLATE=0: what a cartridge image without a bundled translation gets"},
+                    "what": "the same step with STM_XLATE=0: what a cartridge image gets that has neither a bundled translation nor a plug-in (translate.py)"},
                 "translated_core": int(eng.translated_core),
                 "per_rank": per_rank, "collectives": collectives, "comm": nccl_check,
                 "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "kernels": kernels, "policy": policy,

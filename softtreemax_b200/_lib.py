@@ -8,6 +8,8 @@ import os
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("STM_B200_LIB", os.path.join(HERE, "libstm_b200.so"))   # override: A/B builds of the same ABI
+# where stm_ctx_create looks for the translated step kernel of a cartridge image the library was not built with (translate.py)
+os.environ.setdefault("STM_XL_PLUGIN_DIR", os.path.join(HERE, "xl_plugins"))
 
 STATE_BYTES = 256
 OBS = 84

@@ -27,11 +27,20 @@ namespace stm {
 // what stm_kernels.cu knows about a translated cartridge (filled in by csrc/gen/xl_<name>.cu)
 struct XlEntry {
     const char *name;
+    uint32_t abi;                                                      // kXlAbi of the build that compiled it (plug-ins: must equal the library's)
     uint32_t rom_hash, rom_size, n_cases;
     const uint16_t *offsets;                                           // image offsets of the translated instructions (stamp_cases)
     void (*launch)(int blocks, size_t smem, cudaStream_t st, const StmStepArgs &a);
     cudaError_t (*set_attrs)(size_t smem, int carveout_pct);
 };
+}  // namespace stm
+
+#ifndef STM_STEP_THREADS
+#define STM_STEP_THREADS 512  /* one block per SM: 16 warps, 4 per scheduler, the register file at <= 128 registers a thread */
+#endif
+namespace stm {
+// what a translated core and the library must agree on: the launch-argument record, the shared-memory pitch, the state blob
+constexpr uint32_t kXlAbi = 0x02000000u + (uint32_t)sizeof(StmStepArgs) * 4096u + (uint32_t)STM_STEP_THREADS;
 }  // namespace stm
 
 namespace {
@@ -47,9 +56,6 @@ constexpr int kTileEnvs = 32;                                   // envs per nati
 constexpr size_t kTilePixWords = 2ull * STM_VIS_H * 40 * kTileEnvs;
 constexpr size_t kTileSlotWords = 2ull * STM_VIS_H * kTileEnvs / 4;
 constexpr size_t kTileWords = kTilePixWords + kTileSlotWords;    // u32 per tile
-#ifndef STM_STEP_THREADS
-#define STM_STEP_THREADS 512  /* one block per SM: 16 warps, 4 per scheduler, the register file at <= 128 registers a thread */
-#endif
 constexpr int kStepThreads = STM_STEP_THREADS;
 #ifndef STM_STEP_MIN_CTAS
 #define STM_STEP_MIN_CTAS 1

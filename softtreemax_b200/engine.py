@@ -27,10 +27,15 @@ def _ptr(t):
 
 
 class Engine:
-    def __init__(self, game, device=0, scratch_envs=None):
+    def __init__(self, game, device=0, scratch_envs=None, translate=False):
+        """translate: build the block-translated step kernel for this cartridge image first if the library has none
+        (translate.build_plugin: g++ + nvcc, about a minute, cached on disk); otherwise such an image is interpreted."""
         if not torch.cuda.is_available():
             raise StmError("softtreemax_b200 needs a CUDA device (sm_100a); there is no CPU fallback")
         self.desc, self.rom, self.info = games.load(game)
+        if translate:
+            from . import translate as _tr
+            _tr.build_plugin(self.rom, self.info.get("bank_scheme", 0))
         self.device = torch.device("cuda", device)
         self._h = C.c_void_p()
         romb = (C.c_uint8 * len(self.rom)).from_buffer_copy(self.rom)
@@ -57,7 +62,8 @@ class Engine:
 
     @property
     def translated_core(self):
-        """0 = interpreter only; k > 0 = the k-th translated cartridge of the library also serves this image (small launches)."""
+        """0 = interpreter only; k > 0 = the k-th translated cartridge of the library serves this image (k = their number + 1:
+        a plug-in built by translate.py)."""
         return lib().stm_translated_core(self._h)
 
     @property

@@ -3,6 +3,7 @@ thin ctypes wrapper over include/stm_b200.h), against the CPU oracle on identica
 Bar: BIT-EXACT (integer / byte / index work; the only float is the reward accumulator, whose
 multiply and add are separately rounded on both sides, so it is compared exactly too)."""
 import ctypes as C
+import os
 
 import numpy as np
 import pytest
@@ -121,23 +122,17 @@ def test_k2_block_shapes_bitexact(orc, monkeypatch, wpc, scope):
         eng.close()
 
 
-@pytest.mark.parametrize("seed", range(9))
-def test_random_rom_step_bitexact(orc, seed):
-    """Cartridges of random bytes: every opcode incl. undocumented ones, wild TIA/RIOT traffic,
-    frames that end on the scanline cap, F8 bank switching."""
+def _random_rom_parity(orc, seed, translate):
     from softtreemax_b200.engine import Engine
-    from softtreemax_b200 import games as pg
     d, rom = random_rom_game(orc, seed)
     g = orc.Game(desc=orc.make_desc(d, len(rom)), rom=rom)
-    eng = Engine.__new__(Engine)
-    # build an Engine around an ad-hoc descriptor (no games.json entry)
-    from softtreemax_b200._lib import lib, check
-    eng.desc, eng.rom, eng.info = pg.make_desc(d, len(rom)), rom, d
-    eng.device = torch.device("cuda", 0)
-    eng._h = C.c_void_p()
-    romb = (C.c_uint8 * len(rom)).from_buffer_copy(rom)
-    check(lib().stm_ctx_create(C.byref(eng._h), C.byref(eng.desc), romb, 0))
-    eng.n_actions = lib().stm_num_actions(eng._h)
+    eng = Engine((d, rom), translate=translate)          # an ad-hoc descriptor (no games.json entry)
+    if translate:
+        from softtreemax_b200 import translate as tr
+        assert os.path.exists(tr.plugin_path(rom)), "translate.build_plugin left no plug-in"
+        assert eng.translated_core > 0, "the library did not load the plug-in"
+    else:
+        assert eng.translated_core == 0, "an image nobody translated must run on the interpreter"
     try:
         A = g.n_actions
         n = 70
@@ -168,6 +163,21 @@ def test_random_rom_step_bitexact(orc, seed):
             assert np.array_equal(dl.cpu().numpy(), lv)
     finally:
         eng.close()
+
+
+@pytest.mark.parametrize("seed", range(9))
+def test_random_rom_step_bitexact(orc, seed):
+    """Cartridges of random bytes: every opcode incl. undocumented ones, wild TIA/RIOT traffic,
+    frames that end on the scanline cap, F8 bank switching."""
+    _random_rom_parity(orc, seed, translate=False)
+
+
+@pytest.mark.parametrize("seed", [10, 11])
+def test_translation_plugin_bitexact(orc, seed):
+    """A cartridge image the library was NOT built with gets its block-translated step kernel at run time: translate.py runs
+    tools/xlate_rom.cpp + nvcc into a plug-in, stm_ctx_create loads it by the image's hash, and the translated kernel matches
+    the oracle bit for bit on random-byte cartridges (seed 11: 8 KB, F8 bank switching)."""
+    _random_rom_parity(orc, seed, translate=True)
 
 
 @pytest.mark.parametrize("name,R,depth", [("synth_breakout", 5, 1), ("synth_breakout", 3, 2), ("synth_breakout", 2, 3),

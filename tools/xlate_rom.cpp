@@ -29,6 +29,13 @@
 #include <vector>
 #include "../softtreemax_b200/csrc/emu_core.cuh"
 
+// does [a16, a16 + reach] touch an F8 bank-switch hotspot ($1FF8 / $1FF9 and their mirrors)?
+static bool spans_hotspot(uint32_t a16, uint32_t reach)
+{
+    for (uint32_t k = 0; k <= reach; k++) { const uint32_t t = ((a16 + k) & 0xFFFFu) & 0x1FFFu; if (t == 0x1FF8u || t == 0x1FF9u) return true; }
+    return false;
+}
+
 int main(int argc, char **argv)
 {
     if (argc != 5) { fprintf(stderr, "usage: xlate_rom <rom.bin> <name> <bank_scheme> <out.cuh>\n"); return 2; }
@@ -81,7 +88,10 @@ int main(int argc, char **argv)
         case stm::G_RTS: case stm::G_RTI: break;
         case stm::G_BRK: push_addr(bank, rom[at(bank, 0xFFFE)] | (rom[at(bank, 0xFFFF)] << 8), true); push_addr(bank, pc + 2, true); break;
         default: {
-            bool hotspot = f8 && am == 3 && (((b1 | (b2 << 8)) & 0x1FFF) == 0x1FF8 || ((b1 | (b2 << 8)) & 0x1FFF) == 0x1FF9);
+            // an absolute operand on an F8 hotspot, or an indexed one whose 256-byte reach covers it: the next instruction may
+            // run in either bank.  (Indirect operands may land there too; those are caught at run time — see dynswitch.)
+            const uint32_t idx = (w >> 3) & 3;
+            bool hotspot = f8 && am == 3 && spans_hotspot(b1 | (b2 << 8), idx ? 255u : 0u);
             if (hotspot) both_banks(next); else push_addr(bank, next, false);
             break; }
         }
@@ -90,7 +100,7 @@ int main(int argc, char **argv)
     std::set<uint32_t> cases(order.begin(), order.end());
 
     // per-instruction facts
-    struct Ins { uint32_t off, w, b1, b2, len, grp, am, idx, kind, cyc, cmax, next; bool touch, strobe, hotspot, next_ok; };
+    struct Ins { uint32_t off, w, b1, b2, len, grp, am, idx, kind, cyc, cmax, next; bool touch, strobe, hotspot, dynswitch, next_ok; };
     std::vector<Ins> ins;
     for (auto it = cases.begin(); it != cases.end(); ++it) {
         Ins q{};
@@ -121,6 +131,9 @@ int main(int argc, char **argv)
         q.strobe = touch && writes && (!tia_static || tia_reg == 0x00 || tia_reg == 0x02);
         if (touch && writes && !tia_static && !stack && q.am == 3 && !q.idx && (a13 & 0x80)) q.strobe = false;   // static RIOT write
         q.hotspot = f8 && q.am == 3 && !q.idx && (a13 == 0x1FF8 || a13 == 0x1FF9);
+        // operands only known at run time that may land on a hotspot (indexed absolute reaching it, any indirect one): the block
+        // goes on, but the bank is compared with the one it was translated for right after the instruction
+        q.dynswitch = f8 && !q.hotspot && ((q.am == 3 && q.idx && spans_hotspot(a16, 255u)) || q.am == 4 || q.am == 5);
         ins.push_back(q);
     }
     // entry points: control-flow targets (collected above), the instruction after a possible strobe, starts of runs,
@@ -198,6 +211,8 @@ int main(int argc, char **argv)
                 continue;
             }
             fprintf(o, "                e.template exec_body<true, true>(0x%08Xu, 0x%02Xu, 0x%02Xu);\n", q.w, q.b1, q.b2);
+            if (q.dynswitch && !leaves)
+                fprintf(o, "                if (STM_UNLIKELY(e.bank != %uu)) { if (e.hcyc + e.brk >= STM_CYC_PER_LINE) return; continue; }\n", q.off >> 12);
             if (q.grp == stm::G_JMP && q.am == 3) {
                 fprintf(o, "                if (e.hcyc >= STM_CYC_PER_LINE) return;\n                ");
                 target_goto(q.b1 | (q.b2 << 8));
