@@ -143,6 +143,8 @@ def workload_config(args):
     return {"workload": f"{args.game} (stands for {STANDS_FOR.get(args.game, args.game)}, A={A}) tree_depth={args.depth} "
                         f"roots_per_gpu={args.roots} frameskip=4 gamma=0.99 clip_reward episodic_life",
             "roots_per_gpu": args.roots, "depth": args.depth, "leaves_per_gpu": args.roots * A ** args.depth,
+            "roots": f"root i of rank r = game seed {args.seed} + ((r + i // 192) mod {args.games}), state after 64 + (i mod 192) agent steps "
+                     f"of random play (softtreemax_b200/roots.py): every rank expands the same mix of {args.games} games",
             "l2": "working set > L2: leaf stacks written per step = %.2f GB per GPU" % (args.roots * A ** args.depth * 28224 / 1e9),
             "parallelism": f"roots sharded over {args.gpus} GPU(s), no data-path collective"}
 
@@ -312,6 +314,10 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--roots", type=int, default=4096, help="root states per GPU")
     ap.add_argument("--depth", type=int, default=2)
+    ap.add_argument("--seed", type=int, default=1234, help="seed of the first synthetic game the roots are taken from")
+    ap.add_argument("--games", type=int, default=8,
+                    help="the roots of every rank are taken, 192 at a time, from this many games (seeds seed .. seed + games - 1), "
+                         "rank r starting at game r: every rank expands the same mix")
     ap.add_argument("--game", default=GAME, help="cartridge name (softtreemax_b200/roms/games.json)")
     ap.add_argument("--no-policy", action="store_true", help="skip the bfs + CNN + logits arm (sweeps)")
     ap.add_argument("--two-groups", action="store_true", help="time two root groups in flight on two streams even with --no-policy")
@@ -372,7 +378,7 @@ def main():
     eng = Engine(args.game, device=local, scratch_envs=min(L, args.scratch_envs))
     dev = eng.device
     # every rank owns its own shard of roots (different seeds => different states per rank)
-    states, stacks = make_roots(eng, R, seed=1234 + rank)
+    states, stacks = make_roots(eng, R, seed=args.seed, trajectories=args.games, first=rank)
     out = dict(stacks=torch.empty((L, 4, 84, 84), dtype=torch.uint8, device=dev),
                rewards=torch.empty((L,), dtype=torch.float32, device=dev),
                done=torch.empty((L,), dtype=torch.uint8, device=dev),
@@ -449,7 +455,7 @@ def main():
     if args.two_groups or not args.no_policy:
         eng_a = Engine(args.game, device=local, scratch_envs=min(L, args.scratch_envs))
         eng2 = Engine(args.game, device=local, scratch_envs=min(L, args.scratch_envs))
-        states2, stacks2 = make_roots(eng2, R, seed=4321 + rank)
+        states2, stacks2 = make_roots(eng2, R, seed=args.seed, trajectories=args.games, first=rank + args.games // 2)
         out_b = dict(stacks=torch.empty_like(out["stacks"]), rewards=torch.empty_like(out["rewards"]),
                      done=torch.empty_like(out["done"]), lives=torch.empty_like(out["lives"]), states=None)
         s_a, s_b = torch.cuda.Stream(device=dev), torch.cuda.Stream(device=dev)

@@ -16,6 +16,7 @@ struct StmStepArgs {
     const uint32_t *grey;                 // the ctx's colour-index -> grey table, 128 bytes as 32 words (stm_set_palette)
     int n, frameskip, episodic_life, render; uint32_t rom_words; float weight;
     int lock_scope;                       // who advances scanline by scanline together: 0 the warps of a scheduler (default), 1 the block, 2 each warp alone (A/B)
+    int deal;                             // 1: warps dealt round-robin to the blocks
     int warps_per_cta;                    // 1..kStepThreads/32: how many of the block's warps carry envs (the launch spreads its warps over the SMs)
     stm::GameParams gp;
     // frame-by-frame driving (stm_step_frame, the torchcule-style surface): `frozen` decides which envs sit the frame out
@@ -129,7 +130,10 @@ stm_step_kernel(const StepArgs a)
     uint32_t *sgrey = slut + 256;
     if (tid < 32) sgrey[tid] = a.grey[tid];
     const int warp = tid >> 5;
-    const int env = (blockIdx.x * a.warps_per_cta + warp) * 32 + (tid & 31);
+    // which 32 envs this warp carries: consecutive warps of the launch go to one block (deal 0), or are dealt round-robin to
+    // the blocks (deal 1: every SM gets a sample of the whole launch, whatever order the caller's envs are in)
+    const int gwarp = a.deal ? (int)(blockIdx.x + warp * gridDim.x) : (int)(blockIdx.x * a.warps_per_cta + warp);
+    const int env = gwarp * 32 + (tid & 31);
     const bool valid = warp < a.warps_per_cta && env < a.n;
     if (valid) {
         const uint4 *g = reinterpret_cast<const uint4 *>(a.states + (size_t)env * STM_STATE_BYTES);

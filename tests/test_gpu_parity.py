@@ -93,14 +93,15 @@ def test_k2_k3_one_level_bitexact(orc, engines, name, frameskip):
     assert ob[3 * A:4 * A, 3].max() == 0                        # frozen envs produce an all-zero new frame
 
 
-@pytest.mark.parametrize("wpc,scope", [(3, 0), (5, 0), (16, 0), (6, 1), (4, 2)])
-def test_k2_block_shapes_bitexact(orc, monkeypatch, wpc, scope):
+@pytest.mark.parametrize("wpc,scope,deal", [(3, 0, 0), (5, 0, 1), (16, 0, 0), (6, 1, 1), (4, 2, 0)])
+def test_k2_block_shapes_bitexact(orc, monkeypatch, wpc, scope, deal):
     """The step kernel under every block shape the host can choose: groups of the scheduler with 1-4 warps each
     (STM_STEP_WPC = 3, 5, 16 — small launches in the other tests run one warp per block), the block-wide and the
     warp-only lock-step.  Ragged launch, a frozen env, blocks whose last warps carry no env: same bits as the oracle."""
     from softtreemax_b200.engine import Engine
     monkeypatch.setenv("STM_STEP_WPC", str(wpc))
     monkeypatch.setenv("STM_STEP_SCOPE", str(scope))
+    monkeypatch.setenv("STM_STEP_DEAL", str(deal))           # warps dealt round-robin to the blocks, or consecutive
     g = orc.Game("synth_breakout")
     eng = Engine("synth_breakout")
     try:

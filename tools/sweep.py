@@ -34,7 +34,7 @@ def depth0_cell(game, roots, steps=20):
     from softtreemax_b200.engine import Engine
     from softtreemax_b200.roots import make_roots
     eng = Engine(game, device=0, scratch_envs=max(roots, 4096))
-    states, stacks = make_roots(eng, roots, seed=1234)
+    states, stacks = make_roots(eng, roots, seed=1234, trajectories=8)
     rw = torch.zeros(roots, device=eng.device)
     dn = torch.zeros(roots, dtype=torch.uint8, device=eng.device)
     lv = torch.full((roots,), 9, dtype=torch.int32, device=eng.device)
