@@ -30,13 +30,13 @@ METRIC = "tree_leaf_states_per_sec"
 UNIT = "leaves/s"
 CYCLES_PER_NODE_STEP = 4 * 262 * 76          # emulated CPU cycles per node-step (NTSC nominal)
 # From the `ncu --set full` capture of both K2 launches of a depth-2 step of 4 096 synth_breakout roots (16 384 + 65 536 envs),
-# summarised in profiles/r02_k2_groups_ncu_full_summary.txt:
+# summarised in profiles/r02_k2_final_ncu_full_summary.txt:
 #   DRAM bytes per env   = (dram__bytes_read.sum + dram__bytes_write.sum) / envs: what reaches HBM of the native rows (distinct rows
 #                          only, most of them still in L2 when K3 reads them) + the 512 B state trip;
 #   warp instructions per env (node-step) = smsp__inst_executed.sum / envs: what K2's issue-slot roofline is computed from.
-K2_NCU_DRAM_BYTES_PER_ENV = (0.004600e9 + 0.034695e9 + 0.020249e9 + 0.293461e9) / 81920
-K2_NCU_WARP_INST_PER_ENV = (245852284 + 854474247) / 81920
-K2_NCU_ISSUE_ACTIVE = {"16384_envs": 0.1403, "65536_envs": 0.3142}       # smsp__issue_active of the two launches
+K2_NCU_DRAM_BYTES_PER_ENV = (0.004644e9 + 0.041460e9 + 0.019603e9 + 0.321036e9) / 81920
+K2_NCU_WARP_INST_PER_ENV = (265868543 + 907441145) / 81920
+K2_NCU_ISSUE_ACTIVE = {"16384_envs": 0.1516, "65536_envs": 0.2805}       # smsp__issue_active of the two launches
 
 
 def peaks():
@@ -657,12 +657,12 @@ def main():
         issue = K2_NCU_WARP_INST_PER_ENV * node_steps * args.steps / (step_ms / 1e3) / 1e9
         roofline = {"kernel": "stm_step_kernel (K2: 6507+TIA+RIOT agent step)", "bound": "issue",
                     "achieved": issue, "peak": issue_peak, "unit": "G warp-instructions/s", "frac": issue / issue_peak,
-                    "achieved_source": "smsp__inst_executed.sum per env from the ncu capture (profiles/r02_k2_groups_ncu_full_summary.txt: "
+                    "achieved_source": "smsp__inst_executed.sum per env from the ncu capture (profiles/r02_k2_final_ncu_full_summary.txt: "
                                        "%.0f warp instructions per node-step) x node-steps / the K2 time measured here" % K2_NCU_WARP_INST_PER_ENV,
                     "peak_source": "148 SMs x 4 schedulers x SM clock sampled during the timed region",
                     "issue_active_ncu": K2_NCU_ISSUE_ACTIVE,
                     "traffic": K2_NCU_DRAM_BYTES_PER_ENV * node_steps / max(1, step_n / args.steps),
-                    "traffic_source": "ncu --set full, profiles/r02_k2_groups_ncu_full_summary.txt (per env) x envs per launch",
+                    "traffic_source": "ncu --set full, profiles/r02_k2_final_ncu_full_summary.txt (per env) x envs per launch",
                     "avg_launch_ms": step_ms / max(1, step_n), "launches": step_n,
                     "share_of_step": step_ms / ms_total,
                     "timing": "CUDA event pair around every K1/K2/K3 launch on the launch stream (stm_timing_*), inside the timed loop",
