@@ -18,7 +18,7 @@ class XlEntry(C.Structure):
                 ("n_cases", C.c_uint32), ("offsets", C.c_void_p), ("launch", C.c_void_p), ("set_attrs", C.c_void_p)]
 
 
-@pytest.mark.parametrize("seed", [10, 11])
+@pytest.mark.parametrize("seed", [10])          # seed 11 (8 KB, F8) is built by __graft_entry__.build() and run on the GPU
 def test_plugin_builds_and_describes_its_image(seed):
     from softtreemax_b200 import translate
     d, rom = random_rom_game(None, seed)
