@@ -574,10 +574,24 @@ def main():
         h_values = torch.empty((R,), dtype=torch.float32).pin_memory()
         hs_pin, hk_pin = states.cpu().pin_memory(), stacks.cpu().pin_memory()
 
+        s_up = torch.cuda.Stream(device=dev)
+        up_done = torch.cuda.Event()
+
         def policy_step_host():
+            # the states (1 MB) on the compute stream, the stacks (116 MB) on their own: the tree starts at once and only its
+            # first stack shift — and the CNN on the root observations — wait for them (stm_bfs_after)
+            main = torch.cuda.current_stream()
+            s_up.wait_stream(main)                          # the previous step is done with `stacks`
             states.copy_(hs_pin, non_blocking=True)
-            stacks.copy_(hk_pin, non_blocking=True)
-            lg, vr = policy_step()
+            with torch.cuda.stream(s_up):
+                stacks.copy_(hk_pin, non_blocking=True)
+                up_done.record(s_up)
+            eng.bfs(states, stacks, depth, out=out, stacks_ready=up_done)
+            head_leaf, _ = eng.cnn_forward(out["stacks"])
+            main.wait_event(up_done)
+            head_root, vr = eng.cnn_forward(stacks)
+            lg, _, _ = ops.softtreemax_logits_full(eng, head_leaf.reshape(R, A ** depth, A), out["rewards"].reshape(R, -1),
+                                                  val_coef, 1.0, 1.0, 0.001, False)
             h_logits.copy_(lg, non_blocking=True)
             h_values.copy_(vr, non_blocking=True)
             torch.cuda.current_stream().synchronize()
@@ -702,7 +716,7 @@ def main():
                                 "how": "two streams: bfs of batch i+1 overlaps CNN + logits of batch i (double-buffered leaves)"},
                   "e2e": {"value": world * R * args.steps / (ms_policy_e2e / 1e3), "unit": "evals/s",
                           "h2d_bytes_per_step": int(hs_pin.numel() + hk_pin.numel()), "d2h_bytes_per_step": int(R * (A + 1) * 4),
-                          "api": "pinned host roots -> stm_bfs + stm_cnn_forward + stm_logits_fwd -> host logits, values"},
+                          "api": "pinned host roots -> stm_bfs_after (stacks uploaded on their own stream) + stm_cnn_forward + stm_logits_fwd -> host logits, values"},
                   "what": "bfs + NatureCNN (K4) on R*A^d leaves and R roots + SoftTreeMax logits (K5); random-init SB3-style weights"}
         cpu_rate, cpu_leaves, cpu_dt = cpu_oracle_rate(depth, args.cpu_seconds, os.cpu_count() or 1, game=args.game)
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,

@@ -121,6 +121,16 @@ int stm_bfs(stm_ctx *ctx, const uint8_t *root_states, const uint8_t *root_stacks
             uint8_t *leaf_stacks, float *leaf_rewards, uint8_t *leaf_done, int32_t *leaf_lives,
             uint8_t *leaf_states, void *stream);
 
+/* stm_bfs for root stacks that are still on their way: `stacks_ready` is a CUDA event (cudaEvent_t) after which
+ * root_stacks holds the roots' observation stacks — e.g. recorded behind their host-to-device copy on another stream.
+ * Only the copy of the older planes into the first level waits for it; the emulation of the tree starts at once, as
+ * stm_bfs_host does with its own upload.  NULL = stm_bfs.  No reference counterpart (the reference's roots live on the
+ * device of the env, cule_bfs.py:99,110-112). */
+int stm_bfs_after(stm_ctx *ctx, const uint8_t *root_states, const uint8_t *root_stacks, int n_roots,
+                  int depth, float gamma, int frameskip, int episodic_life, int clip_reward,
+                  uint8_t *leaf_stacks, float *leaf_rewards, uint8_t *leaf_done, int32_t *leaf_lives,
+                  uint8_t *leaf_states, void *stream, void *stacks_ready);
+
 /* Continue a tree from interior nodes: `n_nodes` nodes of level `level0` (their emulator states, observation
  * stacks, accumulated UNCLIPPED discounted rewards, done flags and lives, e.g. a slice of what stm_bfs returned
  * with clip_reward = 0) are expanded `depth_more` further levels exactly as stm_bfs would have expanded them:

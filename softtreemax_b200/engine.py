@@ -125,7 +125,9 @@ class Engine:
         return out
 
     def bfs(self, root_states, root_stacks, depth, gamma=0.99, frameskip=4, episodic_life=True,
-            clip_reward=True, want_states=False, out=None):
+            clip_reward=True, want_states=False, out=None, stacks_ready=None):
+        """stacks_ready: a torch.cuda.Event after which root_stacks is valid (recorded behind its upload on another stream):
+        the tree starts at once and only the copy of the older planes into the first level waits (stm_bfs_after)."""
         R = root_states.shape[0]
         L = R * self.n_actions ** depth
         d = self.device
@@ -135,10 +137,13 @@ class Engine:
                        done=torch.empty((L,), dtype=torch.uint8, device=d),
                        lives=torch.empty((L,), dtype=torch.int32, device=d),
                        states=torch.empty((L, STATE_BYTES), dtype=torch.uint8, device=d) if want_states else None)
-        check(lib().stm_bfs(self._h, _ptr(root_states), _ptr(root_stacks), R, depth, float(gamma), frameskip,
-                            int(episodic_life), int(clip_reward), _ptr(out["stacks"]), _ptr(out["rewards"]),
-                            _ptr(out["done"]), _ptr(out["lives"]), _ptr(out.get("states")), self._stream()),
-              self._h)
+        args = (self._h, _ptr(root_states), _ptr(root_stacks), R, depth, float(gamma), frameskip,
+                int(episodic_life), int(clip_reward), _ptr(out["stacks"]), _ptr(out["rewards"]),
+                _ptr(out["done"]), _ptr(out["lives"]), _ptr(out.get("states")), self._stream())
+        if stacks_ready is None:
+            check(lib().stm_bfs(*args), self._h)
+        else:
+            check(lib().stm_bfs_after(*args, C.c_void_p(stacks_ready.cuda_event)), self._h)
         return out
 
     def bfs_resume(self, node_states, node_stacks, node_rewards, node_done, node_lives, level0, depth_more, gamma=0.99,

@@ -286,6 +286,30 @@ def test_bfs_host_matches_device_path(orc, engines, game, n_roots, depth):
     assert np.array_equal(got["rewards"], want[1].reshape(-1))
 
 
+def test_bfs_with_root_stacks_arriving_on_another_stream(orc, engines):
+    """stm_bfs_after: the root stacks are uploaded on a side stream while the tree is already being emulated; the event
+    recorded behind the upload is all the call needs.  Same tree as stm_bfs on stacks that were there from the start."""
+    g = orc.Game("synth_pong")
+    eng = engines("synth_pong")
+    roots, stacks = orc.make_roots(g, 9, seed=31)
+    dr = dev(roots, eng)
+    ref = eng.bfs(dr, dev(stacks, eng), 2)
+    torch.cuda.synchronize()
+    pinned = torch.from_numpy(stacks).pin_memory()
+    late = torch.full(stacks.shape, 0xEE, dtype=torch.uint8, device=eng.device)     # garbage until the copy lands
+    side = torch.cuda.Stream(device=eng.device)
+    ready = torch.cuda.Event()
+    torch.cuda.synchronize()
+    with torch.cuda.stream(side):
+        torch.cuda._sleep(20_000_000)                   # ~10 ms: the copy starts well after the tree was enqueued
+        late.copy_(pinned, non_blocking=True)
+        ready.record(side)
+    got = eng.bfs(dr, late, 2, stacks_ready=ready)
+    torch.cuda.synchronize()
+    for k in ("stacks", "rewards", "done", "lives"):
+        assert torch.equal(got[k], ref[k]), k
+
+
 def test_bfs_replays_from_a_cuda_graph(orc, engines):
     """stm_bfs forks a second stream for the stack shift and joins it before returning: the whole call captures into one CUDA
     graph, and a replay on NEW roots written into the same buffers reproduces the eager tree bit for bit."""
