@@ -119,7 +119,7 @@ __global__ void __launch_bounds__(kStepThreads, STM_STEP_MIN_CTAS)
 stm_step_kernel(const StepArgs a)
 {
     extern __shared__ __align__(16) uint32_t smem[];
-    uint32_t *sblob = smem;                              // 64 words x 128 threads
+    uint32_t *sblob = smem;                              // 64 words x kStepThreads (the pitch; a smaller block uses the first columns)
     uint32_t *srom = sblob + 64 * kStepThreads;
     uint32_t *slut = srom + a.rom_words;
     const int tid = threadIdx.x;
