@@ -35,8 +35,10 @@ def plugin_path(rom):
     return os.path.join(plugin_dir(), "libstm_xl_%08x.so" % rom_hash(rom))
 
 
-def build_plugin(rom, bank_scheme="none", force=False):
-    """-> path of the plug-in for this image (built if missing or older than the kernel sources)."""
+def build_plugin(rom, bank_scheme="none", force=False, max_instructions=400):
+    """-> path of the plug-in for this image (built if missing or older than the kernel sources).
+    max_instructions caps what is translated (nvcc's time grows faster than linearly with it: 220 instructions take 1.5 min,
+    650 took 9); code the walk does not reach before the cap is interpreted."""
     rom = bytes(rom)
     out = plugin_path(rom)
     deps = [os.path.join(_build.CSRC, f) for f in ("emu_core.cuh", "stm_step.cuh")] + [os.path.join(ROOT, "tools", "xlate_rom.cpp")]
@@ -55,7 +57,7 @@ def build_plugin(rom, bank_scheme="none", force=False):
         with open(img, "wb") as f:
             f.write(rom)
         cuh = os.path.join(tmp, f"xl_{name}.cuh")
-        subprocess.check_call([exe, img, name, f8, cuh], stderr=subprocess.DEVNULL)
+        subprocess.check_call([exe, img, name, f8, cuh, str(int(max_instructions))], stderr=subprocess.DEVNULL)
         cu = os.path.join(tmp, f"xl_{name}.cu")
         with open(cu, "w") as f:
             f.write(_build.xl_unit_source(name, os.path.join(_build.CSRC, "stm_step.cuh"), cuh, plugin=True))

@@ -38,7 +38,10 @@ static bool spans_hotspot(uint32_t a16, uint32_t reach)
 
 int main(int argc, char **argv)
 {
-    if (argc != 5) { fprintf(stderr, "usage: xlate_rom <rom.bin> <name> <bank_scheme> <out.cuh>\n"); return 2; }
+    if (argc != 5 && argc != 6) { fprintf(stderr, "usage: xlate_rom <rom.bin> <name> <bank_scheme> <out.cuh> [max instructions]\n"); return 2; }
+    // an optional cap on the instructions translated (compile time grows faster than linearly with them); what the walk
+    // does not reach before it is interpreted — every jump into untranslated code goes through the dispatcher anyway
+    const size_t max_ins = argc == 6 ? (size_t)atoi(argv[5]) : 6000u;
     FILE *f = fopen(argv[1], "rb");
     if (!f) { perror(argv[1]); return 1; }
     std::vector<uint8_t> rom(65536);
@@ -88,14 +91,15 @@ int main(int argc, char **argv)
         case stm::G_RTS: case stm::G_RTI: break;
         case stm::G_BRK: push_addr(bank, rom[at(bank, 0xFFFE)] | (rom[at(bank, 0xFFFF)] << 8), true); push_addr(bank, pc + 2, true); break;
         default: {
-            // an absolute operand on an F8 hotspot, or an indexed one whose 256-byte reach covers it: the next instruction may
-            // run in either bank.  (Indirect operands may land there too; those are caught at run time — see dynswitch.)
+            // an absolute operand on an F8 hotspot: the next instruction runs in the other bank — walk both.  (Indexed and
+            // indirect operands may land there too; those are caught at run time — see dynswitch — and what they reach in the
+            // other bank is interpreted unless something else leads the walk there.)
             const uint32_t idx = (w >> 3) & 3;
-            bool hotspot = f8 && am == 3 && spans_hotspot(b1 | (b2 << 8), idx ? 255u : 0u);
+            bool hotspot = f8 && am == 3 && !idx && spans_hotspot(b1 | (b2 << 8), 0u);
             if (hotspot) both_banks(next); else push_addr(bank, next, false);
             break; }
         }
-        if (order.size() > 6000) { fprintf(stderr, "too many reachable instructions\n"); return 1; }
+        if (order.size() >= max_ins) { for (uint32_t o : work) seen.erase(o); work.clear(); }
     }
     std::set<uint32_t> cases(order.begin(), order.end());
 
