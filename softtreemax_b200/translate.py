@@ -62,6 +62,7 @@ def build_plugin(rom, bank_scheme="none", force=False, max_instructions=400):
         with open(cu, "w") as f:
             f.write(_build.xl_unit_source(name, os.path.join(_build.CSRC, "stm_step.cuh"), cuh, plugin=True))
         flags = [f for f in _build.FLAGS]
-        subprocess.check_call([_build.NVCC] + flags + ["-o", out + ".tmp", cu])
-        os.replace(out + ".tmp", out)
+        part = "%s.%d.tmp" % (out, os.getpid())                 # several ranks may build the same plug-in at once
+        subprocess.check_call([_build.NVCC] + flags + ["-o", part, cu])
+        os.replace(part, out)
     return out
