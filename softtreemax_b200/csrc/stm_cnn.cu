@@ -628,6 +628,9 @@ stm_cnn_window_kernel(const __grid_constant__ CUtensorMap in_map, const __nv_bfl
 // flight while this one is converted.  320 of the 384 producer threads work (160 window rows x 2 halves).
 // ---------------------------------------------------------------------------------------------------------
 constexpr int kC1Threads = 12 * 32 + 128 + 32;
+#ifndef STM_C1_AHEAD
+#define STM_C1_AHEAD 2      /* tiles the producers' global loads run ahead of the conversion */
+#endif
 template <int kStages>
 __global__ void __launch_bounds__(kC1Threads, 1)
 stm_cnn_conv1_window_kernel(const uint8_t *__restrict__ in, const __nv_bfloat16 *__restrict__ wt, const float *__restrict__ bias,
@@ -669,9 +672,10 @@ stm_cnn_conv1_window_kernel(const uint8_t *__restrict__ in, const __nv_bfloat16 
         const uint32_t r = (uint32_t)tid % kWinRows, half = (uint32_t)tid / kWinRows;
         const int my_tiles = blockIdx.x < ntiles ? (int)((ntiles - blockIdx.x + gridDim.x - 1) / gridDim.x) : 0;
         uint32_t tile = blockIdx.x, st = 0, ph = 0;
-        // the global loads run TWO tiles ahead of the conversion (one tile, ~0.9 us, does not cover DRAM latency under load:
+        // the global loads run kAhead tiles ahead of the conversion (one tile, ~0.9 us, does not cover DRAM latency under load:
         // the producers sat on the scoreboard, ncu long-scoreboard 6.1 per issue)
-        uint32_t cur[8], nxt[8], nx2[8];
+        constexpr int kAhead = STM_C1_AHEAD;
+        uint32_t cur[8], pre[kAhead][8];
         auto load_next = [&](uint32_t *w) {
             const uint32_t v = tile * kTileM + r;
             const bool ok = v < M_total && !(debug & 1);
@@ -684,8 +688,8 @@ stm_cnn_conv1_window_kernel(const uint8_t *__restrict__ in, const __nv_bfloat16 
                     w[cc * 4 + iy] = ok ? __ldg(reinterpret_cast<const uint32_t *>(p + cc * (84 * 84) + iy * 84)) : 0u;
             tile += gridDim.x;
         };
-        if (my_tiles > 0) load_next(nxt);
-        if (my_tiles > 1) load_next(nx2);
+        #pragma unroll
+        for (int d = 0; d < kAhead; d++) if (my_tiles > d) load_next(pre[d]);
         const __half2 k1024 = __half2half2(__ushort_as_half((unsigned short)0x6400));
         auto widen = [&](uint32_t w, uint32_t sel) -> uint32_t {
             uint32_t biased = __byte_perm(w, 0x64646464u, sel);
@@ -694,8 +698,12 @@ stm_cnn_conv1_window_kernel(const uint8_t *__restrict__ in, const __nv_bfloat16 
         };
         for (int i = 0; i < my_tiles; i++) {
             #pragma unroll
-            for (int k = 0; k < 8; k++) { cur[k] = nxt[k]; nxt[k] = nx2[k]; }
-            if (i + 2 < my_tiles) load_next(nx2);
+            for (int k = 0; k < 8; k++) {
+                cur[k] = pre[0][k];
+                #pragma unroll
+                for (int d = 0; d + 1 < kAhead; d++) pre[d][k] = pre[d + 1][k];
+            }
+            if (i + kAhead < my_tiles) load_next(pre[kAhead - 1]);
             mbar_wait(&empty[st], ph ^ 1);
             uint8_t *wbase = sW + st * kWinBytes;
             if (!(debug & 16)) {
