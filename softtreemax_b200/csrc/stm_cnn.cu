@@ -628,11 +628,17 @@ stm_cnn_window_kernel(const __grid_constant__ CUtensorMap in_map, const __nv_bfl
 // flight while this one is converted.  320 of the 384 producer threads work (160 window rows x 2 halves).
 // ---------------------------------------------------------------------------------------------------------
 constexpr int kC1Threads = 12 * 32 + 128 + 32;
+#ifndef STM_C1_STAGES
+#define STM_C1_STAGES 4     /* window tiles (20 KB each) in the shared-memory ring: 4 x 2 blocks per SM measured 2.78 ms per 65 536 images, 6 x 1 2.86, 10 x 1 2.95 */
+#endif
+#ifndef STM_C1_PER_SM
+#define STM_C1_PER_SM 2     /* persistent blocks per SM (each 8 x 32 TMEM columns, 56 registers x 544 threads) */
+#endif
 #ifndef STM_C1_AHEAD
 #define STM_C1_AHEAD 2      /* tiles the producers' global loads run ahead of the conversion */
 #endif
 template <int kStages>
-__global__ void __launch_bounds__(kC1Threads, 1)
+__global__ void __launch_bounds__(kC1Threads, STM_C1_PER_SM)
 stm_cnn_conv1_window_kernel(const uint8_t *__restrict__ in, const __nv_bfloat16 *__restrict__ wt, const float *__restrict__ bias,
                             __nv_bfloat16 *__restrict__ out, uint32_t M_total, int debug)
 {
@@ -985,7 +991,7 @@ int launch_window(stm_ctx *ctx, const __nv_bfloat16 *in, const __nv_bfloat16 *w,
 int launch_conv1_window(stm_ctx *ctx, const uint8_t *obs, const __nv_bfloat16 *w, const float *b, __nv_bfloat16 *out,
                         long long n_images, int debug, cudaStream_t st)
 {
-    constexpr int kStages = 6;
+    constexpr int kStages = STM_C1_STAGES;
     static bool attr_done = false;
     if (!attr_done) {
         cudaFuncSetAttribute(stm_cnn_conv1_window_kernel<kStages>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 2048);
@@ -996,7 +1002,7 @@ int launch_conv1_window(stm_ctx *ctx, const uint8_t *obs, const __nv_bfloat16 *w
     if (M >= (1LL << 31) - kTileM) return stm_internal_fail(ctx, STM_ERR_ARG, "stm_cnn: too many rows for one pass");
     const size_t smem = (size_t)kStages * kWinBytes + 4 * 32 * kChunkK * 2 + 1024;
     const long long tiles = (M + kTileM - 1) / kTileM;
-    const long long grid = tiles < 148 ? tiles : 148;
+    const long long grid = tiles < 148 * STM_C1_PER_SM ? tiles : 148 * STM_C1_PER_SM;
     stm_cnn_conv1_window_kernel<kStages><<<(unsigned)grid, kC1Threads, smem, st>>>(obs, w, b, out, (uint32_t)M, debug);
     stm_internal_count_launch(ctx);
     cudaError_t e = cudaGetLastError();
