@@ -475,7 +475,7 @@ template <int kConv> __host__ __device__ constexpr int win_taps() { return kConv
 template <int kConv> __host__ __device__ constexpr int win_off(int kc) { return kConv == 2 ? (kc >> 1) * 10 + (kc & 1) : (kc / 3) * 9 + kc % 3; }
 
 template <int kStages, int kConv>
-__global__ void __launch_bounds__(288, 1)
+__global__ void __launch_bounds__(288, 2)
 stm_cnn_window_kernel(const __grid_constant__ CUtensorMap in_map, const __nv_bfloat16 *__restrict__ wt, const float *__restrict__ bias,
                       __nv_bfloat16 *__restrict__ out, uint32_t M_total, WinGeom g)
 {
@@ -486,13 +486,13 @@ stm_cnn_window_kernel(const __grid_constant__ CUtensorMap in_map, const __nv_bfl
     uint8_t *sB = smem + kStages * kWinBytes;              // nchunks x 8 KB, resident
     // kAcc accumulators in tensor memory (64 columns each): the MMA thread may run kAcc tiles ahead of the epilogue,
     // which hides the latency of the tfull -> epilogue -> tempty hand-off (measured: ~1.5 us per round trip)
-    constexpr int kAcc = 8;
+    constexpr int kAcc = kStages <= 3 ? 4 : 8;            // a short ring = the two-blocks-per-SM configuration: half the tensor memory each
     __shared__ __align__(8) uint64_t full[kStages], empty[kStages], tfull[kAcc], tempty[kAcc];
     __shared__ uint32_t tmem_base_s;
     __shared__ __align__(16) float sbias[N];
     const int tid = threadIdx.x, warp = tid >> 5;
     const uint32_t ntiles = (M_total + kTileM - 1) / kTileM;
-    constexpr uint32_t kCols = kAcc * N;                  // 512: the whole tensor memory of the SM (one CTA per SM)
+    constexpr uint32_t kCols = kAcc * N;                  // 512 (the whole tensor memory of the SM: one block per SM) or 256
     if (tid < N) sbias[tid] = bias[tid];
 
     if (warp == 8) {
@@ -628,6 +628,12 @@ stm_cnn_window_kernel(const __grid_constant__ CUtensorMap in_map, const __nv_bfl
 // flight while this one is converted.  320 of the 384 producer threads work (160 window rows x 2 halves).
 // ---------------------------------------------------------------------------------------------------------
 constexpr int kC1Threads = 12 * 32 + 128 + 32;
+#ifndef STM_W2_STAGES
+#define STM_W2_STAGES 2     /* conv2: window tiles in the ring; 2 x 2 blocks per SM measured 2.62 ms per 65 536 images for K4, 6 x 1 2.77 */
+#endif
+#ifndef STM_W2_PER_SM
+#define STM_W2_PER_SM 2
+#endif
 #ifndef STM_C1_STAGES
 #define STM_C1_STAGES 4     /* window tiles (20 KB each) in the shared-memory ring: 4 x 2 blocks per SM measured 2.78 ms per 65 536 images, 6 x 1 2.86, 10 x 1 2.95 */
 #endif
@@ -944,7 +950,8 @@ template <int kConv>
 int launch_window(stm_ctx *ctx, const __nv_bfloat16 *in, const __nv_bfloat16 *w, const float *b, __nv_bfloat16 *out,
                   long long n_images, const WinGeom &g, cudaStream_t st)
 {
-    constexpr int kStages = 6;
+    // conv2 (64 KB of resident weights) fits two blocks per SM with a short window ring; conv3 (72 KB) does not
+    constexpr int kStages = kConv == 2 ? STM_W2_STAGES : 6, kPerSm = kConv == 2 ? STM_W2_PER_SM : 1;
     static bool attr_done = false;
     if (!attr_done) {
         cudaFuncSetAttribute(stm_cnn_window_kernel<kStages, kConv>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 2048);
@@ -960,7 +967,7 @@ int launch_window(stm_ctx *ctx, const __nv_bfloat16 *in, const __nv_bfloat16 *w,
         if (g.off[c] != win_off<kConv>(c) || g.off[c] + kTileM > kWinRows) return stm_internal_fail(ctx, STM_ERR_ARG, "stm_cnn: tap offsets");
     const size_t smem = (size_t)kStages * kWinBytes + (size_t)g.nchunks * 64 * kChunkK * 2 + 1024;
     const long long tiles = (M + kTileM - 1) / kTileM;
-    const long long grid = tiles < 148 ? tiles : 148;
+    const long long grid = tiles < 148 * kPerSm ? tiles : 148 * kPerSm;
     // the activation matrix [M rows][64 bf16] as a 2-D tensor map; box = one window (64 x 160), 128-byte swizzle
     CUtensorMap map;
     {
