@@ -206,7 +206,10 @@ stm_cnn_gemm_kernel(const void *__restrict__ in, const __nv_bfloat16 *__restrict
     const int kc0 = g.split_chunks > 0 ? (int)blockIdx.y * g.split_chunks : 0;
     const int nchunks = g.split_chunks > 0 ? min(g.split_chunks, g.K / kChunkK - kc0) : g.K / kChunkK;
     const long long ntiles = nchunks > 0 ? (M_total + kTileM - 1) / kTileM : 0;
-    constexpr uint32_t kCols = (2 * N < 32) ? 32 : 2 * N;             // two accumulators
+    // two accumulators (the epilogue of tile i overlaps the MMAs of tile i + 1) — or ONE for the wide tile with a short ring:
+    // that block needs half the tensor memory and half the shared memory, so two of them share an SM and overlap each other
+    constexpr int kAccG = (N == 256 && kStages <= 2) ? 1 : 2;
+    constexpr uint32_t kCols = (kAccG * N < 32) ? 32 : kAccG * N;
     if (g.split_chunks > 0) out = reinterpret_cast<float *>(out) + (size_t)blockIdx.y * (size_t)M_total * (size_t)g.n_real;
 
     if (warp == kMmaWarp) {
@@ -365,8 +368,8 @@ stm_cnn_gemm_kernel(const void *__restrict__ in, const __nv_bfloat16 *__restrict
             const uint32_t a_lo0 = desc_lo(smem_u32(sA)), b_lo0 = desc_lo(smem_u32(sB));          // + start address in 16-byte units
             uint32_t it = 0, t = 0;
             for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x, t++) {
-                const uint32_t buf = t & 1;
-                mbar_wait(&tempty[buf], ((t >> 1) & 1) ^ 1);        // the epilogue has drained this accumulator
+                const uint32_t buf = t % kAccG;
+                mbar_wait(&tempty[buf], ((t / kAccG) & 1) ^ 1);     // the epilogue has drained this accumulator
                 asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
                 const uint32_t tmem_d = tmem_base + buf * N;
                 for (int kc = 0; kc < nchunks; kc++, it++) {
@@ -394,8 +397,8 @@ stm_cnn_gemm_kernel(const void *__restrict__ in, const __nv_bfloat16 *__restrict
         const int ew = et >> 5;
         uint32_t t = 0;
         for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x, t++) {
-            const uint32_t buf = t & 1;
-            mbar_wait(&tfull[buf], (t >> 1) & 1);
+            const uint32_t buf = t % kAccG;
+            mbar_wait(&tfull[buf], (t / kAccG) & 1);
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
             const long long m = tile * kTileM + et;
             const bool row_ok = m < M_total;
@@ -469,6 +472,9 @@ struct WinGeom {
     int debug;               // timing experiments only (STM_CNN_DEBUG): 1 no loads, 2 no MMAs, 4 no epilogue math/stores, 32 no TMEM loads
 };
 constexpr int kWinRows = 160, kWinBytes = kWinRows * 128;          // 128 virtual rows + 32 rows of halo
+// rows of the window tile of conv<kConv> (a multiple of 8: whole swizzle atoms): conv3 needs 128 + 20, and the 1 KB a stage
+// saves is what lets two blocks with its 72 KB of weights share an SM
+template <int kConv> __host__ __device__ constexpr int win_rows() { return kConv == 3 ? 152 : kWinRows; }
 
 // tap -> input-row offset, known at compile time so that the issue loop adds immediates (kConv = 2: conv2, 3: conv3)
 template <int kConv> __host__ __device__ constexpr int win_taps() { return kConv == 2 ? 8 : 9; }
@@ -480,9 +486,10 @@ stm_cnn_window_kernel(const __grid_constant__ CUtensorMap in_map, const __nv_bfl
                       __nv_bfloat16 *__restrict__ out, uint32_t M_total, WinGeom g)
 {
     constexpr int N = 64, kBBytes = N * kChunkK * 2;
+    constexpr int kWinBytes = win_rows<kConv>() * 128;     // shadows the 160-row default: conv3's taps reach 20 rows, its window is 152
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     uint8_t *smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
-    uint8_t *sW = smem;                                    // kStages windows of 20 KB
+    uint8_t *sW = smem;                                    // kStages windows of 19 / 20 KB
     uint8_t *sB = smem + kStages * kWinBytes;              // nchunks x 8 KB, resident
     // kAcc accumulators in tensor memory (64 columns each): the MMA thread may run kAcc tiles ahead of the epilogue,
     // which hides the latency of the tfull -> epilogue -> tempty hand-off (measured: ~1.5 us per round trip)
@@ -633,6 +640,15 @@ constexpr int kC1Threads = 12 * 32 + 128 + 32;
 #endif
 #ifndef STM_W2_PER_SM
 #define STM_W2_PER_SM 2
+#endif
+#ifndef STM_FC_STAGES
+#define STM_FC_STAGES 2     /* fc: stages of the A/B ring; <= 2 selects the one-accumulator block that fits an SM twice (K4 2.56 -> 2.48 ms per 65 536 images against 4 stages, two accumulators, one block per SM) */
+#endif
+#ifndef STM_W3_STAGES
+#define STM_W3_STAGES 2     /* conv3: 2 x 2 blocks per SM (152-row windows, 72 KB of weights each): K4 2.62 -> 2.57 ms per 65 536 images */
+#endif
+#ifndef STM_W3_PER_SM
+#define STM_W3_PER_SM 2
 #endif
 #ifndef STM_C1_STAGES
 #define STM_C1_STAGES 4     /* window tiles (20 KB each) in the shared-memory ring: 4 x 2 blocks per SM measured 2.78 ms per 65 536 images, 6 x 1 2.86, 10 x 1 2.95 */
@@ -951,7 +967,7 @@ int launch_window(stm_ctx *ctx, const __nv_bfloat16 *in, const __nv_bfloat16 *w,
                   long long n_images, const WinGeom &g, cudaStream_t st)
 {
     // conv2 (64 KB of resident weights) fits two blocks per SM with a short window ring; conv3 (72 KB) does not
-    constexpr int kStages = kConv == 2 ? STM_W2_STAGES : 6, kPerSm = kConv == 2 ? STM_W2_PER_SM : 1;
+    constexpr int kStages = kConv == 2 ? STM_W2_STAGES : STM_W3_STAGES, kPerSm = kConv == 2 ? STM_W2_PER_SM : STM_W3_PER_SM;
     static bool attr_done = false;
     if (!attr_done) {
         cudaFuncSetAttribute(stm_cnn_window_kernel<kStages, kConv>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 2048);
@@ -964,8 +980,8 @@ int launch_window(stm_ctx *ctx, const __nv_bfloat16 *in, const __nv_bfloat16 *w,
         if (((q * g.recip_vw) >> 16) != q / g.VW) return stm_internal_fail(ctx, STM_ERR_ARG, "stm_cnn: reciprocal of VW is not exact");
     if (g.nchunks != win_taps<kConv>()) return stm_internal_fail(ctx, STM_ERR_ARG, "stm_cnn: tap count");
     for (int c = 0; c < g.nchunks; c++)
-        if (g.off[c] != win_off<kConv>(c) || g.off[c] + kTileM > kWinRows) return stm_internal_fail(ctx, STM_ERR_ARG, "stm_cnn: tap offsets");
-    const size_t smem = (size_t)kStages * kWinBytes + (size_t)g.nchunks * 64 * kChunkK * 2 + 1024;
+        if (g.off[c] != win_off<kConv>(c) || g.off[c] + kTileM > win_rows<kConv>()) return stm_internal_fail(ctx, STM_ERR_ARG, "stm_cnn: tap offsets");
+    const size_t smem = (size_t)kStages * win_rows<kConv>() * 128 + (size_t)g.nchunks * 64 * kChunkK * 2 + 1024;
     const long long tiles = (M + kTileM - 1) / kTileM;
     const long long grid = tiles < 148 * kPerSm ? tiles : 148 * kPerSm;
     // the activation matrix [M rows][64 bf16] as a 2-D tensor map; box = one window (64 x 160), 128-byte swizzle
@@ -983,7 +999,7 @@ int launch_window(stm_ctx *ctx, const __nv_bfloat16 *in, const __nv_bfloat16 *w,
             encode = reinterpret_cast<EncodeFn>(fn);
         }
         const cuuint64_t dims[2] = { 64, (cuuint64_t)M }, strides[1] = { 128 };
-        const cuuint32_t box[2] = { 64, (cuuint32_t)kWinRows }, estr[2] = { 1, 1 };
+        const cuuint32_t box[2] = { 64, (cuuint32_t)win_rows<kConv>() }, estr[2] = { 1, 1 };
         if (encode(&map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<__nv_bfloat16 *>(in), dims, strides, box, estr,
                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
@@ -1432,7 +1448,7 @@ static int forward_chunk(stm_ctx *ctx, CnnState *s, const uint8_t *obs, long lon
     if (dbg & 512) return STM_OK;                                 // timing experiments: conv2 + conv3 alone (with bit 9: no conv1 either)
     LayerGeom g4 = { MODE_NHWC, 1, 1, 1, 1, 3136, 3136, 1, 3136, 512, 1, 0, 1.0f, 65536, 0, dbg };
     for (int half = 0; half < 2; half++)
-        if ((rc = launch_layer<256, false, 4, 4>(ctx, act3, s->w[3], s->b[3], feat, c, g4, half * 256, 512, st))) return rc;
+        if ((rc = launch_layer<256, false, STM_FC_STAGES, 4>(ctx, act3, s->w[3], s->b[3], feat, c, g4, half * 256, 512, st))) return rc;
     LayerGeom g5 = { MODE_NHWC, 1, 1, 1, 1, 512, 512, 1, 512, A1, 0, 1, 1.0f, 65536, 0, dbg };
     return launch_layer<32, true, 4, 4>(ctx, feat, s->w[4], s->b[4], heads, c, g5, 0, 32, st);
 }
